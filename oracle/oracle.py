@@ -1,0 +1,199 @@
+"""ctypes front-end of the CPU oracle (TEST INFRASTRUCTURE -- see oracle/tfhe_oracle.h).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import this.
+Parameter sets restate /root/reference/tfhe/src/shortint/parameters/mod.rs:613-627,703-717,853-867
+and boolean/parameters/mod.rs:123-134.
+"""
+import ctypes as C
+import os
+import subprocess
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = os.path.join(_HERE, "liboracle.so")
+
+
+class OrcParams(C.Structure):
+    _fields_ = [("n", C.c_int), ("k", C.c_int), ("N", C.c_int), ("pbs_base_log", C.c_int),
+                ("pbs_level", C.c_int), ("ks_base_log", C.c_int), ("ks_level", C.c_int),
+                ("bits", C.c_int), ("lwe_std", C.c_double), ("glwe_std", C.c_double)]
+
+
+# name -> (n, k, N, pbs_base_log, pbs_level, ks_base_log, ks_level, bits, lwe_std, glwe_std, msg_mod*carry_mod, order)
+PARAMS = {
+    "BOOLEAN_DEFAULT": (722, 2, 512, 6, 3, 3, 4, 32, 0.000013071021089943935, 0.00000004990272175010415, 0, "pbs_ks"),
+    "MESSAGE_1_CARRY_1": (684, 3, 512, 18, 1, 4, 3, 64, 0.00002043784477291318, 0.0000000000034525330484572114, 4, "ks_pbs"),
+    "MESSAGE_2_CARRY_2": (742, 1, 2048, 23, 1, 3, 5, 64, 0.000007069849454709433, 0.00000000000000029403601535432533, 16, "ks_pbs"),
+    "MESSAGE_3_CARRY_3": (864, 1, 8192, 15, 2, 3, 6, 64, 0.000000757998020150446, 0.0000000000000000002168404344971009, 64, "ks_pbs"),
+    # toy sets for fast CPU tests (same role as the reference's FFT_WOPBS_N512_PARAMS toy set, test/mod.rs:276-289)
+    "TOY_U64": (16, 1, 256, 12, 2, 4, 4, 64, 1e-9, 1e-15, 4, "ks_pbs"),
+    "TOY_U32": (20, 2, 128, 6, 3, 3, 4, 32, 1e-7, 1e-8, 0, "pbs_ks"),
+}
+
+
+def build(force=False):
+    if force or not os.path.exists(_LIB) or any(
+            os.path.getmtime(os.path.join(_HERE, f)) > os.path.getmtime(_LIB)
+            for f in os.listdir(_HERE) if f.endswith((".c", ".h"))):
+        subprocess.check_call(["make", "-C", _HERE, "-s"])
+    return _LIB
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = C.CDLL(build())
+        _lib.orc_closest_representable.restype = C.c_uint64
+        _lib.orc_closest_representable.argtypes = [C.c_uint64, C.c_int, C.c_int, C.c_int]
+        _lib.orc_modswitch.restype = C.c_uint64
+        _lib.orc_modswitch.argtypes = [C.c_uint64, C.c_int, C.c_int]
+        _lib.orc_lwe_phase.restype = C.c_uint64
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def u64(a):
+    return np.ascontiguousarray(a, dtype=np.uint64)
+
+
+class Oracle:
+    """One parameter set + one deterministic key set, in the reference's standard-domain layouts."""
+
+    def __init__(self, name, seed=0xB2000001, nthreads=None):
+        t = PARAMS[name]
+        self.name = name
+        self.p = OrcParams(*t[:10])
+        self.n, self.k, self.N = t[0], t[1], t[2]
+        self.l, self.b, self.l_ks, self.b_ks, self.bits = t[4], t[3], t[6], t[5], t[7]
+        self.pmod, self.order = t[10], t[11]
+        self.seed = seed
+        self.nthreads = nthreads or os.cpu_count()
+        self.big = self.k * self.N
+        self.glwe_len = (self.k + 1) * self.N
+        self.small_key = self.glwe_key = self.ksk = self.bsk = self.fbsk = None
+
+    # ---- keys -------------------------------------------------------------------------------
+    def keygen(self, fourier=True):
+        L = lib()
+        cache = os.path.join(os.environ.get("ORACLE_KEY_CACHE", "/tmp/b200tfhe_keys"), f"{self.name}_{self.seed:x}.npz")
+        if os.path.exists(cache):
+            z = np.load(cache)
+            self.small_key, self.glwe_key, self.ksk, self.bsk = z["s"], z["g"], z["ksk"], z["bsk"]
+        else:
+            self.small_key = np.zeros(self.n, np.uint64)
+            self.glwe_key = np.zeros(self.big, np.uint64)
+            L.orc_gen_binary_key(C.c_uint64(self.seed), self.n, _p(self.small_key))
+            L.orc_gen_binary_key(C.c_uint64(self.seed + 1), self.big, _p(self.glwe_key))
+            self.ksk = np.zeros(self.big * self.l_ks * (self.n + 1), np.uint64)
+            self.bsk = np.zeros(self.n * self.l * (self.k + 1) ** 2 * self.N, np.uint64)
+            L.orc_gen_ksk(C.byref(self.p), _p(self.glwe_key), _p(self.small_key), C.c_uint64(self.seed + 2), _p(self.ksk), self.nthreads)
+            L.orc_gen_bsk(C.byref(self.p), _p(self.small_key), _p(self.glwe_key), C.c_uint64(self.seed + 3), _p(self.bsk), self.nthreads)
+            try:
+                os.makedirs(os.path.dirname(cache), exist_ok=True)
+                np.savez(cache, s=self.small_key, g=self.glwe_key, ksk=self.ksk, bsk=self.bsk)
+            except OSError:
+                pass
+        if fourier:
+            self.fbsk = np.zeros(self.bsk.size, np.float64)
+            L.orc_bsk_to_fourier(C.byref(self.p), _p(self.bsk), _p(self.fbsk), self.nthreads)
+        return self
+
+    # ---- ciphertexts ------------------------------------------------------------------------
+    def encrypt(self, plaintexts, under="big", seed=0xB2000002, std=None):
+        key, dim = (self.glwe_key, self.big) if under == "big" else (self.small_key, self.n)
+        if std is None:
+            std = self.p.glwe_std if under == "big" else self.p.lwe_std
+        pts = u64(plaintexts)
+        out = np.zeros((pts.size, dim + 1), np.uint64)
+        for i, pt in enumerate(pts):
+            lib().orc_lwe_encrypt(dim, self.bits, _p(key), C.c_uint64(int(pt)), C.c_double(std), C.c_uint64(seed + i), _p(out[i]))
+        return out
+
+    def phase(self, cts, under="big"):
+        key, dim = (self.glwe_key, self.big) if under == "big" else (self.small_key, self.n)
+        cts = u64(cts).reshape(-1, dim + 1)
+        return np.array([lib().orc_lwe_phase(dim, self.bits, _p(key), _p(c)) for c in cts], np.uint64)
+
+    def glwe_phase(self, glwe):
+        """body - sum_j A_j*S_j of a GLWE ciphertext, exact (binary key)."""
+        glwe = u64(glwe).reshape(self.k + 1, self.N)
+        ph = glwe[self.k].copy()
+        tmp = np.zeros(self.N, np.uint64)
+        for j in range(self.k):
+            lib().orc_negacyclic_mul_binary(self.N, _p(u64(glwe[j])), _p(u64(self.glwe_key[j * self.N:(j + 1) * self.N])), _p(tmp), self.bits)
+            ph = ph - tmp
+        return ph & np.uint64((1 << self.bits) - 1 if self.bits < 64 else 0xFFFFFFFFFFFFFFFF)
+
+    # shortint encode / decode: shortint/engine/mod.rs:101 (delta = 2^63 / p), client_key/mod.rs:281-301
+    def delta(self):
+        return (1 << (self.bits - 1)) // self.pmod
+
+    def encode(self, msgs):
+        return (u64(msgs) * np.uint64(self.delta()))
+
+    def decode(self, phases):
+        d = np.uint64(self.delta())
+        ph = u64(phases)
+        rounded = ph + ((ph & (d >> np.uint64(1))) << np.uint64(1))
+        return (rounded // d) % np.uint64(2 * self.pmod)
+
+    def decode_bool(self, phases):
+        return u64(phases) < np.uint64(1 << 31)  # boolean/engine/mod.rs:353-375
+
+    # ---- LUTs -------------------------------------------------------------------------------
+    def lut(self, f):
+        table = u64([f(i) for i in range(self.pmod)])
+        out = np.zeros(self.glwe_len, np.uint64)
+        lib().orc_fill_accumulator(C.byref(self.p), _p(table), self.pmod, _p(out))
+        return out
+
+    def boolean_lut(self):
+        out = np.zeros(self.glwe_len, np.uint64)
+        lib().orc_boolean_lut(C.byref(self.p), _p(out))
+        return out
+
+    # ---- the path ---------------------------------------------------------------------------
+    def keyswitch(self, cts):
+        cts = u64(cts).reshape(-1, self.big + 1)
+        out = np.zeros((cts.shape[0], self.n + 1), np.uint64)
+        for i in range(cts.shape[0]):
+            lib().orc_keyswitch(C.byref(self.p), _p(self.ksk), _p(cts[i]), _p(out[i]))
+        return out
+
+    def _batch(self, fn, cts, luts, lut_idx, in_dim, out_dim):
+        cts = u64(cts).reshape(-1, in_dim)
+        luts = u64(luts).reshape(-1, self.glwe_len)
+        B = cts.shape[0]
+        idx = np.ascontiguousarray(lut_idx if lut_idx is not None else np.zeros(B), dtype=np.uint32)
+        out = np.zeros((B, out_dim), np.uint64)
+        fn(_p(cts), _p(luts), _p(idx), _p(out), B, self.nthreads)
+        return out
+
+    def ks_pbs(self, cts, luts, lut_idx=None):
+        L = lib()
+        return self._batch(lambda *a: L.orc_ks_pbs_batch(C.byref(self.p), _p(self.ksk), _p(self.fbsk), *a),
+                           cts, luts, lut_idx, self.big + 1, self.big + 1)
+
+    def pbs_ks(self, cts, luts, lut_idx=None):
+        L = lib()
+        return self._batch(lambda *a: L.orc_pbs_ks_batch(C.byref(self.p), _p(self.ksk), _p(self.fbsk), *a),
+                           cts, luts, lut_idx, self.n + 1, self.n + 1)
+
+    def pbs(self, cts, luts, lut_idx=None, sample_extract=True):
+        L = lib()
+        od = self.big + 1 if sample_extract else self.glwe_len
+        return self._batch(lambda *a: L.orc_pbs_batch(C.byref(self.p), _p(self.fbsk), *a, 1 if sample_extract else 0),
+                           cts, luts, lut_idx, self.n + 1, od)
+
+    def gate_prologue(self, gate, a, b):
+        a, b = u64(a).reshape(-1, self.n + 1), u64(b).reshape(-1, self.n + 1)
+        out = np.zeros_like(a)
+        for i in range(a.shape[0]):
+            lib().orc_boolean_gate_prologue(gate, self.n + 1, _p(a[i]), _p(b[i]), _p(out[i]))
+        return out

@@ -1,0 +1,159 @@
+/* orc_bootstrap.c -- external product, blind rotation, PBS, batched KS+PBS
+ * (TEST INFRASTRUCTURE, see tfhe_oracle.h). */
+#include "tfhe_oracle.h"
+#include <stdlib.h>
+#include <string.h>
+#include <pthread.h>
+
+static inline uint64_t maskw(int bits) { return bits == 64 ? ~0ULL : ((1ULL << bits) - 1); }
+
+/* generic "run fn(i) for i in [0,count) over nthreads" helper (rayon par_iter stand-in) */
+typedef struct { void (*fn)(void *, int); void *ctx; int count; int next; pthread_mutex_t mu; } pool_t;
+static void *pool_worker(void *arg) {
+    pool_t *p = (pool_t *)arg;
+    for (;;) {
+        pthread_mutex_lock(&p->mu);
+        int i = p->next++;
+        pthread_mutex_unlock(&p->mu);
+        if (i >= p->count) break;
+        p->fn(p->ctx, i);
+    }
+    return NULL;
+}
+void orc_parallel_for(void (*fn)(void *, int), void *ctx, int count, int nthreads) {
+    if (nthreads <= 1 || count <= 1) { for (int i = 0; i < count; i++) fn(ctx, i); return; }
+    pool_t p; p.fn = fn; p.ctx = ctx; p.count = count; p.next = 0;
+    pthread_mutex_init(&p.mu, NULL);
+    if (nthreads > 256) nthreads = 256;
+    pthread_t th[256];
+    for (int t = 0; t < nthreads; t++) pthread_create(&th[t], NULL, pool_worker, &p);
+    for (int t = 0; t < nthreads; t++) pthread_join(th[t], NULL);
+    pthread_mutex_destroy(&p.mu);
+}
+
+/* ---- BSK conversion: fft64/crypto/bootstrap.rs:197-209 -> fft/mod.rs:719-764 ---- */
+typedef struct { const orc_params *p; const uint64_t *bsk; double *f; } conv_ctx;
+static void conv_one(void *c, int poly) {
+    conv_ctx *x = (conv_ctx *)c;
+    int N = x->p->N;
+    orc_fft_forward_torus(N, x->bsk + (size_t)poly * N, x->p->bits, x->f + (size_t)poly * N);
+}
+void orc_bsk_to_fourier(const orc_params *p, const uint64_t *bsk, double *fbsk, int nthreads) {
+    conv_ctx c = { p, bsk, fbsk };
+    int polys = p->n * p->pbs_level * (p->k + 1) * (p->k + 1);
+    orc_parallel_for(conv_one, &c, polys, nthreads);
+}
+
+/* fft64/crypto/ggsw.rs:477-598.  ggsw_f: [level 1..l][row][col][M] c64 (levels stored 1->l, consumed l->1). */
+void orc_add_external_product(const orc_params *p, uint64_t *acc, const double *ggsw_f, const uint64_t *glwe) {
+    int N = p->N, M = N / 2, k1 = p->k + 1, L = p->pbs_level, b = p->pbs_base_log, bits = p->bits;
+    uint64_t m = maskw(bits), mb = (1ULL << b) - 1;
+    size_t tot = (size_t)k1 * N;
+    uint64_t *states = (uint64_t *)malloc(sizeof(uint64_t) * tot);
+    uint64_t *digits = (uint64_t *)malloc(sizeof(uint64_t) * N);
+    double *fourier = (double *)malloc(sizeof(double) * N);
+    double *outf = (double *)calloc((size_t)k1 * N, sizeof(double));
+    int shift = bits - b * L;
+    for (size_t t = 0; t < tot; t++) states[t] = orc_closest_representable(glwe[t], b, L, bits) >> shift;
+    for (int lvl = L; lvl >= 1; lvl--) {
+        const double *mat = ggsw_f + (size_t)(lvl - 1) * k1 * k1 * N;
+        for (int r = 0; r < k1; r++) {
+            /* collect_next_term: ggsw.rs:601-613 ; decompose_one_level: decomposition.rs:79-86 */
+            for (int j = 0; j < N; j++) {
+                uint64_t *st = &states[(size_t)r * N + j];
+                uint64_t res = *st & mb;
+                *st >>= b;
+                uint64_t carry = (((res - 1) & m) | *st) & res;
+                carry >>= (b - 1);
+                *st = (*st + carry) & m;
+                digits[j] = (res - (carry << b)) & m;
+            }
+            orc_fft_forward_integer(N, digits, bits, fourier);
+            /* update_with_fmadd: ggsw.rs:616-697 */
+            const double *row = mat + (size_t)r * k1 * N;
+            for (int j = 0; j < k1; j++) {
+                const double *g = row + (size_t)j * N;
+                double *o = outf + (size_t)j * N;
+                for (int f = 0; f < M; f++) {
+                    double gr = g[2 * f], gi = g[2 * f + 1], dr = fourier[2 * f], di = fourier[2 * f + 1];
+                    o[2 * f] += gr * dr - gi * di;
+                    o[2 * f + 1] += gr * di + gi * dr;
+                }
+            }
+        }
+    }
+    for (int j = 0; j < k1; j++) orc_fft_add_backward_torus(N, acc + (size_t)j * N, bits, outf + (size_t)j * N);
+    free(states); free(digits); free(fourier); free(outf);
+}
+
+/* fft64/crypto/bootstrap.rs:243-344 */
+void orc_blind_rotate(const orc_params *p, const double *fbsk, const uint64_t *lwe, uint64_t *acc) {
+    int N = p->N, k1 = p->k + 1, n = p->n, bits = p->bits;
+    int log2N = 0; while ((1 << log2N) < N) log2N++;
+    size_t tot = (size_t)k1 * N;
+    uint64_t *tmp = (uint64_t *)malloc(sizeof(uint64_t) * tot);
+    uint64_t bhat = orc_modswitch(lwe[n], log2N, bits);
+    memcpy(tmp, acc, sizeof(uint64_t) * tot);
+    for (int j = 0; j < k1; j++) orc_monomial_div(acc + (size_t)j * N, tmp + (size_t)j * N, N, bhat, bits);
+    size_t ggsw_sz = (size_t)p->pbs_level * k1 * k1 * N; /* doubles */
+    for (int i = 0; i < n; i++) {
+        if ((lwe[i] & maskw(bits)) == 0) continue; /* bootstrap.rs:285 */
+        uint64_t ahat = orc_modswitch(lwe[i], log2N, bits);
+        for (int j = 0; j < k1; j++) orc_monomial_mul_sub(tmp + (size_t)j * N, acc + (size_t)j * N, N, ahat, bits);
+        orc_add_external_product(p, acc, fbsk + (size_t)i * ggsw_sz, tmp);
+    }
+    free(tmp);
+}
+
+/* bootstrap.rs:346-380 */
+void orc_pbs(const orc_params *p, const double *fbsk, const uint64_t *lwe_in, const uint64_t *lut, uint64_t *lwe_out) {
+    size_t tot = (size_t)(p->k + 1) * p->N;
+    uint64_t *acc = (uint64_t *)malloc(sizeof(uint64_t) * tot);
+    memcpy(acc, lut, sizeof(uint64_t) * tot);
+    orc_blind_rotate(p, fbsk, lwe_in, acc);
+    orc_sample_extract0(lwe_out, acc, p->k, p->N, p->bits);
+    free(acc);
+}
+
+typedef struct {
+    const orc_params *p; const uint64_t *ksk; const double *fbsk; const uint64_t *in; const uint64_t *luts;
+    const uint32_t *lut_idx; uint64_t *out; int mode; /* 0 ks->pbs, 1 pbs->ks, 2 pbs, 3 blind rotate only */
+} batch_ctx;
+static void batch_one(void *c, int i) {
+    batch_ctx *x = (batch_ctx *)c;
+    const orc_params *p = x->p;
+    size_t big = (size_t)p->k * p->N + 1, small = (size_t)p->n + 1, glwe = (size_t)(p->k + 1) * p->N;
+    const uint64_t *lut = x->luts + (x->lut_idx ? (size_t)x->lut_idx[i] * glwe : 0);
+    if (x->mode == 0) {
+        uint64_t *mid = (uint64_t *)malloc(sizeof(uint64_t) * small);
+        orc_keyswitch(p, x->ksk, x->in + (size_t)i * big, mid);
+        orc_pbs(p, x->fbsk, mid, lut, x->out + (size_t)i * big);
+        free(mid);
+    } else if (x->mode == 1) {
+        uint64_t *mid = (uint64_t *)malloc(sizeof(uint64_t) * big);
+        orc_pbs(p, x->fbsk, x->in + (size_t)i * small, lut, mid);
+        orc_keyswitch(p, x->ksk, mid, x->out + (size_t)i * small);
+        free(mid);
+    } else if (x->mode == 2) {
+        orc_pbs(p, x->fbsk, x->in + (size_t)i * small, lut, x->out + (size_t)i * big);
+    } else {
+        uint64_t *acc = x->out + (size_t)i * glwe;
+        memcpy(acc, lut, sizeof(uint64_t) * glwe);
+        orc_blind_rotate(p, x->fbsk, x->in + (size_t)i * small, acc);
+    }
+}
+void orc_ks_pbs_batch(const orc_params *p, const uint64_t *ksk, const double *fbsk, const uint64_t *in,
+                      const uint64_t *luts, const uint32_t *lut_idx, uint64_t *out, int batch, int nthreads) {
+    batch_ctx c = { p, ksk, fbsk, in, luts, lut_idx, out, 0 };
+    orc_parallel_for(batch_one, &c, batch, nthreads);
+}
+void orc_pbs_ks_batch(const orc_params *p, const uint64_t *ksk, const double *fbsk, const uint64_t *in,
+                      const uint64_t *luts, const uint32_t *lut_idx, uint64_t *out, int batch, int nthreads) {
+    batch_ctx c = { p, ksk, fbsk, in, luts, lut_idx, out, 1 };
+    orc_parallel_for(batch_one, &c, batch, nthreads);
+}
+void orc_pbs_batch(const orc_params *p, const double *fbsk, const uint64_t *in, const uint64_t *luts,
+                   const uint32_t *lut_idx, uint64_t *out, int batch, int nthreads, int sample_extract) {
+    batch_ctx c = { p, NULL, fbsk, in, luts, lut_idx, out, sample_extract ? 2 : 3 };
+    orc_parallel_for(batch_one, &c, batch, nthreads);
+}
