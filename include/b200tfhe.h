@@ -1,0 +1,165 @@
+/*
+ * b200tfhe.h -- C ABI of the B200-native batched keyswitch + programmable-bootstrap library.
+ *
+ * This is the drop-in boundary for ONE path of TFHE-rs (reference: nicolasbon38/tfhe-rs-odd, a TFHE-rs
+ * v0.5.0 fork): what a Rust `extern "C"` sys-crate would bind in place of the generic functions below.
+ * Citations are relative to the reference's tfhe/src/.  Conventions mirror the reference's own C API
+ * (c_api/utils.rs:3-27): every function returns int, 0 = success, non-zero = failure (the reference
+ * turns panics into 1; here argument checks replace its assert!s); handles are opaque, allocated by the
+ * library and freed by the matching *_destroy; out-handles are set to NULL before any work.
+ *
+ * Containers are the reference's flat layouts, passed as plain pointers:
+ *   LWE ciphertext   [mask 0..dim-1, body]                         core_crypto/entities/lwe_ciphertext.rs:598-609
+ *   LWE list         batch x (dim+1), contiguous                   entities/lwe_ciphertext_list.rs:10-17
+ *   GLWE ciphertext  (k+1) polynomials of N coefficients, body last entities/glwe_ciphertext.rs:210-223
+ *   LweBootstrapKey  [n][level 1..l][row 0..k][poly 0..k][N]        entities/lwe_bootstrap_key.rs:99-106,
+ *                    (standard domain)                              entities/ggsw_ciphertext.rs:185-197
+ *   LweKeyswitchKey  [n_in][l_ks (level l_ks first)][n_out+1]       entities/lwe_keyswitch_key.rs:77-108,
+ *                                                                   algorithms/lwe_keyswitch_key_generation.rs:109-120
+ * Only native power-of-two moduli (2^64: *_u64, 2^32: *_u32) are accepted, as the reference asserts
+ * (fft_impl/fft64/crypto/bootstrap.rs:254, algorithms/lwe_keyswitch.rs:136-141).
+ *
+ * Pointer flavours: plain entry points take HOST pointers and stage host<->device copies themselves on the
+ * context's stream (synchronous on return); *_dev entry points take DEVICE pointers, enqueue on the
+ * context's stream and return without synchronising (call b200tfhe_synchronize).
+ *
+ * There is no CPU fallback: every compute entry point fails with a non-zero code if no CUDA device is usable.
+ */
+#ifndef B200TFHE_H
+#define B200TFHE_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b200tfhe_context b200tfhe_context;
+typedef struct b200tfhe_bsk b200tfhe_bsk; /* Fourier bootstrap key resident on the device: FourierLweBootstrapKey,
+                                             fft_impl/fft64/crypto/bootstrap.rs:27-33 */
+typedef struct b200tfhe_ksk b200tfhe_ksk; /* LweKeyswitchKey resident on the device */
+
+/* parameter newtypes of core_crypto/commons/parameters.rs:40-236, flattened */
+typedef struct {
+    int32_t lwe_dimension;    /* n   */
+    int32_t glwe_dimension;   /* k   */
+    int32_t polynomial_size;  /* N   */
+    int32_t pbs_base_log;
+    int32_t pbs_level;
+    int32_t ks_base_log;
+    int32_t ks_level;
+    int32_t torus_bits;       /* 64 or 32 */
+} b200tfhe_params;
+
+/* boolean binary gates, boolean/engine/mod.rs:607-798 */
+enum { B200TFHE_GATE_AND = 0, B200TFHE_GATE_NAND = 1, B200TFHE_GATE_OR = 2, B200TFHE_GATE_NOR = 3,
+       B200TFHE_GATE_XOR = 4, B200TFHE_GATE_XNOR = 5 };
+
+/* ---- context ------------------------------------------------------------------------------------------ */
+/* One context = one CUDA device + one stream + a private workspace pool (the per-thread ShortintEngine /
+ * ComputationBuffers of shortint/engine/mod.rs:23-69).  Calls on one context are serialised internally. */
+int b200tfhe_context_create(int device, b200tfhe_context **out);
+int b200tfhe_context_destroy(b200tfhe_context *ctx);
+int b200tfhe_synchronize(b200tfhe_context *ctx);
+/* last error text of this context (or of context creation when ctx == NULL); never NULL */
+const char *b200tfhe_last_error(const b200tfhe_context *ctx);
+/* the context's CUDA stream as a cudaStream_t cast to void* (for callers that interleave their own work) */
+void *b200tfhe_context_stream(b200tfhe_context *ctx);
+/* 1 if blind rotation is implemented for this parameter set on this build, else 0 */
+int b200tfhe_params_supported(const b200tfhe_params *p);
+
+/* ---- keys --------------------------------------------------------------------------------------------- */
+/* Replaces par_convert_standard_lwe_bootstrap_key_to_fourier (algorithms/lwe_bootstrap_key_conversion.rs:99-152):
+ * uploads a standard-domain LweBootstrapKey and runs the forward negacyclic FFT on the device into the
+ * device's own Fourier layout.  uses p->{lwe_dimension, glwe_dimension, polynomial_size, pbs_*, torus_bits}. */
+int b200tfhe_bsk_upload_u64(b200tfhe_context *ctx, const b200tfhe_params *p, const uint64_t *std_bsk, b200tfhe_bsk **out);
+int b200tfhe_bsk_upload_u32(b200tfhe_context *ctx, const b200tfhe_params *p, const uint32_t *std_bsk, b200tfhe_bsk **out);
+/* same, standard-domain key already on the device */
+int b200tfhe_bsk_convert_dev(b200tfhe_context *ctx, const b200tfhe_params *p, const void *d_std_bsk, b200tfhe_bsk **out);
+/* allocate an uninitialised device Fourier key (to be filled by a peer copy / NCCL broadcast of another
+ * GPU's key: the Fourier layout is identical on every B200) */
+int b200tfhe_bsk_alloc(b200tfhe_context *ctx, const b200tfhe_params *p, b200tfhe_bsk **out);
+/* device address and size in bytes of the Fourier key ( n*l*(k+1)^2*(N/2) complex f64 ) */
+int b200tfhe_bsk_device_buffer(const b200tfhe_bsk *bsk, void **d_ptr, size_t *bytes);
+int b200tfhe_bsk_destroy(b200tfhe_bsk *bsk);
+
+/* uploads an LweKeyswitchKey (input dim k*N, output dim n); uses p->{lwe_dimension, glwe_dimension,
+ * polynomial_size, ks_*, torus_bits} */
+int b200tfhe_ksk_upload_u64(b200tfhe_context *ctx, const b200tfhe_params *p, const uint64_t *ksk, b200tfhe_ksk **out);
+int b200tfhe_ksk_upload_u32(b200tfhe_context *ctx, const b200tfhe_params *p, const uint32_t *ksk, b200tfhe_ksk **out);
+int b200tfhe_ksk_alloc(b200tfhe_context *ctx, const b200tfhe_params *p, b200tfhe_ksk **out);
+/* device address/size of the key rows; after filling it from a peer call b200tfhe_ksk_finalize */
+int b200tfhe_ksk_device_buffer(const b200tfhe_ksk *ksk, void **d_ptr, size_t *bytes);
+int b200tfhe_ksk_finalize(b200tfhe_context *ctx, b200tfhe_ksk *ksk);
+int b200tfhe_ksk_destroy(b200tfhe_ksk *ksk);
+
+/* ---- batched operations, host pointers ------------------------------------------------------------------ */
+/* keyswitch_lwe_ciphertext (algorithms/lwe_keyswitch.rs:96-170) over a list:
+ * in: batch x (kN+1), out: batch x (n+1).  Bit-exact. */
+int b200tfhe_keyswitch_batch_u64(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const uint64_t *in, uint64_t *out, uint32_t batch);
+int b200tfhe_keyswitch_batch_u32(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const uint32_t *in, uint32_t *out, uint32_t batch);
+
+/* programmable_bootstrap_lwe_ciphertext(_mem_optimized) (algorithms/lwe_programmable_bootstrapping.rs:1017-1113)
+ * over a list: in: batch x (n+1) under the small key, out: batch x (kN+1).
+ * luts: n_luts accumulators, each a GLWE of (k+1)N scalars; lut_idx[b] selects ciphertext b's accumulator
+ * (NULL = all use accumulator 0). */
+int b200tfhe_pbs_batch_u64(b200tfhe_context *ctx, const b200tfhe_bsk *bsk, const uint64_t *in, uint64_t *out,
+                           const uint64_t *luts, uint32_t n_luts, const uint32_t *lut_idx, uint32_t batch);
+int b200tfhe_pbs_batch_u32(b200tfhe_context *ctx, const b200tfhe_bsk *bsk, const uint32_t *in, uint32_t *out,
+                           const uint32_t *luts, uint32_t n_luts, const uint32_t *lut_idx, uint32_t batch);
+
+/* programmable_bootstrap_lwe_ciphertext_without_sample_extract_mem_optimized (fork entry,
+ * lwe_programmable_bootstrapping.rs:1115-1162) / blind_rotate_assign (:232-289): out: batch x (k+1)N GLWE */
+int b200tfhe_blind_rotate_batch_u64(b200tfhe_context *ctx, const b200tfhe_bsk *bsk, const uint64_t *in, uint64_t *out_glwe,
+                                    const uint64_t *luts, uint32_t n_luts, const uint32_t *lut_idx, uint32_t batch);
+int b200tfhe_blind_rotate_batch_u32(b200tfhe_context *ctx, const b200tfhe_bsk *bsk, const uint32_t *in, uint32_t *out_glwe,
+                                    const uint32_t *luts, uint32_t n_luts, const uint32_t *lut_idx, uint32_t batch);
+
+/* shortint keyswitch_programmable_bootstrap_assign core (shortint/server_key/mod.rs:783-857):
+ * KS then PBS; in/out: batch x (kN+1) */
+int b200tfhe_ks_pbs_batch_u64(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, const uint64_t *in,
+                              uint64_t *out, const uint64_t *luts, uint32_t n_luts, const uint32_t *lut_idx, uint32_t batch);
+int b200tfhe_ks_pbs_batch_u32(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, const uint32_t *in,
+                              uint32_t *out, const uint32_t *luts, uint32_t n_luts, const uint32_t *lut_idx, uint32_t batch);
+/* programmable_bootstrap_keyswitch_assign core (:859-933) / boolean bootstrap_keyswitch
+ * (boolean/engine/bootstrapping.rs:299-344): PBS then KS; in/out: batch x (n+1) */
+int b200tfhe_pbs_ks_batch_u64(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, const uint64_t *in,
+                              uint64_t *out, const uint64_t *luts, uint32_t n_luts, const uint32_t *lut_idx, uint32_t batch);
+int b200tfhe_pbs_ks_batch_u32(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, const uint32_t *in,
+                              uint32_t *out, const uint32_t *luts, uint32_t n_luts, const uint32_t *lut_idx, uint32_t batch);
+
+/* boolean binary gate over a list (boolean/engine/mod.rs:607-798 + Bootstrapper::apply_bootstrapping_pattern,
+ * engine/bootstrapping.rs:392-401): linear combination, then PBS->KS (pbs_first != 0, DEFAULT_PARAMETERS) or
+ * KS->PBS (pbs_first == 0, *_KS_PBS parameters) with the constant accumulator of bootstrapping.rs:59-60.
+ * a, b, out: batch x (dim+1), dim = n when pbs_first else kN */
+int b200tfhe_gate_batch_u32(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, int gate, int pbs_first,
+                            const uint32_t *a, const uint32_t *b, uint32_t *out, uint32_t batch);
+
+/* stand-alone bit-exact stages (fused inside the PBS; exposed for parity checks and custom chains) */
+/* fast_pbs_modulus_switch, fft_impl/common.rs:26-43 (offset 0, lut_count_log 0): out[i] in [0, 2N] */
+int b200tfhe_modulus_switch_u64(b200tfhe_context *ctx, const uint64_t *in, uint32_t *out, size_t count, uint32_t log2_poly_size);
+int b200tfhe_modulus_switch_u32(b200tfhe_context *ctx, const uint32_t *in, uint32_t *out, size_t count, uint32_t log2_poly_size);
+/* extract_lwe_sample_from_glwe_ciphertext with MonomialDegree(0), algorithms/glwe_sample_extraction.rs:91-147 */
+int b200tfhe_sample_extract_batch_u64(b200tfhe_context *ctx, const uint64_t *glwe, uint64_t *lwe, uint32_t glwe_dimension,
+                                      uint32_t polynomial_size, uint32_t batch);
+int b200tfhe_sample_extract_batch_u32(b200tfhe_context *ctx, const uint32_t *glwe, uint32_t *lwe, uint32_t glwe_dimension,
+                                      uint32_t polynomial_size, uint32_t batch);
+
+/* ---- batched operations, device pointers (asynchronous on the context's stream) ---------------------------- */
+int b200tfhe_keyswitch_batch_dev(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const void *d_in, void *d_out, uint32_t batch);
+int b200tfhe_pbs_batch_dev(b200tfhe_context *ctx, const b200tfhe_bsk *bsk, const void *d_in, void *d_out, const void *d_luts,
+                           const uint32_t *d_lut_idx, uint32_t batch);
+int b200tfhe_blind_rotate_batch_dev(b200tfhe_context *ctx, const b200tfhe_bsk *bsk, const void *d_in, void *d_out_glwe,
+                                    const void *d_luts, const uint32_t *d_lut_idx, uint32_t batch);
+int b200tfhe_ks_pbs_batch_dev(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, const void *d_in,
+                              void *d_out, const void *d_luts, const uint32_t *d_lut_idx, uint32_t batch);
+int b200tfhe_pbs_ks_batch_dev(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, const void *d_in,
+                              void *d_out, const void *d_luts, const uint32_t *d_lut_idx, uint32_t batch);
+
+/* number of kernel launches issued through this context so far (bench.py's gpu_launches) */
+uint64_t b200tfhe_launch_count(const b200tfhe_context *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -25,9 +25,12 @@ PARAMS = {
     "MESSAGE_1_CARRY_1": (684, 3, 512, 18, 1, 4, 3, 64, 0.00002043784477291318, 0.0000000000034525330484572114, 4, "ks_pbs"),
     "MESSAGE_2_CARRY_2": (742, 1, 2048, 23, 1, 3, 5, 64, 0.000007069849454709433, 0.00000000000000029403601535432533, 16, "ks_pbs"),
     "MESSAGE_3_CARRY_3": (864, 1, 8192, 15, 2, 3, 6, 64, 0.000000757998020150446, 0.0000000000000000002168404344971009, 64, "ks_pbs"),
-    # toy sets for fast CPU tests (same role as the reference's FFT_WOPBS_N512_PARAMS toy set, test/mod.rs:276-289)
-    "TOY_U64": (16, 1, 256, 12, 2, 4, 4, 64, 1e-9, 1e-15, 4, "ks_pbs"),
-    "TOY_U32": (20, 2, 128, 6, 3, 3, 4, 32, 1e-7, 1e-8, 0, "pbs_ks"),
+    # toy sets for fast CPU tests (same role as the reference's FFT_WOPBS_N512_PARAMS toy set, test/mod.rs:276-289):
+    # the polynomial sizes / decompositions of the named sets with a tiny LWE dimension
+    "TOY_U64": (16, 1, 512, 12, 2, 4, 4, 64, 1e-9, 1e-15, 4, "ks_pbs"),
+    "TOY_U32": (20, 2, 512, 6, 3, 3, 4, 32, 1e-7, 1e-8, 0, "pbs_ks"),
+    "TOY_2_2": (12, 1, 2048, 23, 1, 3, 5, 64, 1e-9, 0.00000000000000029403601535432533, 16, "ks_pbs"),
+    "TOY_1_1": (12, 3, 512, 18, 1, 4, 3, 64, 1e-9, 0.0000000000034525330484572114, 4, "ks_pbs"),
 }
 
 
@@ -81,7 +84,7 @@ class Oracle:
     # ---- keys -------------------------------------------------------------------------------
     def keygen(self, fourier=True):
         L = lib()
-        cache = os.path.join(os.environ.get("ORACLE_KEY_CACHE", "/tmp/b200tfhe_keys"), f"{self.name}_{self.seed:x}.npz")
+        cache = os.path.join(os.environ.get("ORACLE_KEY_CACHE", "/tmp/b200tfhe_keys"), f"{self.name}_{self.n}_{self.k}_{self.N}_{self.b}_{self.l}_{self.b_ks}_{self.l_ks}_{self.bits}_{self.seed:x}.npz")
         if os.path.exists(cache):
             z = np.load(cache)
             self.small_key, self.glwe_key, self.ksk, self.bsk = z["s"], z["g"], z["ksk"], z["bsk"]

@@ -1,0 +1,112 @@
+// emul.cpp -- CPU lane emulator of the CUDA blind-rotation stages (TEST INFRASTRUCTURE).
+// Compiles tfhe-rs-odd_b200/csrc/{fft_reg,br_core}.cuh as host code and runs the stage sequence of
+// blind_rotate.cu with the R lanes of every team executed one after another; "syncs" are loop boundaries.
+// Lets the no-GPU test-suite check the kernel's mathematics against the oracle.
+#include "br_core.cuh"
+#include "twiddles.hpp"
+#include <vector>
+#include <cstring>
+#include <type_traits>
+using namespace b200tfhe;
+
+template <typename T, int R, int K, int L, int BL>
+static void convert_bsk(const uint64_t *bsk_std, int n, std::vector<cplx> &out) {
+    typedef BRCore<T, R, K, L, BL> C;
+    static TwTables<R> tw; fill_tw_tables(tw);
+    const int N = C::N, M = C::M, K1 = C::K1;
+    size_t npoly = (size_t)n * L * K1 * K1;
+    out.assign(npoly * M, cplx{0, 0});
+    std::vector<cplx> region(C::REGION);
+    std::vector<T> poly(N);
+    cplx x[R][R];
+    for (size_t pi = 0; pi < npoly; pi++) {
+        for (int c = 0; c < N; c++) poly[c] = (T)bsk_std[pi * N + c];
+        for (int lane = 0; lane < R; lane++) C::key_fwd_pass1(lane, poly.data(), region.data(), tw.fwd);
+        for (int lane = 0; lane < R; lane++) C::fwd_pass2_load(lane, x[lane], region.data());
+        for (int lane = 0; lane < R; lane++) {
+            TeamFFT<R>::fwd_pass2_compute(x[lane]);
+            for (int p = 0; p < R; p++) out[pi * M + p * R + lane] = x[lane][p];
+        }
+    }
+}
+
+template <typename T, int R, int K, int L, int BL>
+static void blind_rotate(const std::vector<cplx> &fbsk, int n, const uint64_t *lwe, const uint64_t *lut, uint64_t *out_glwe) {
+    typedef BRCore<T, R, K, L, BL> C;
+    static TwTables<R> tw; fill_tw_tables(tw);
+    const int N = C::N, K1 = C::K1;
+    std::vector<T> acc((size_t)K1 * N), lutT((size_t)K1 * N);
+    for (size_t c = 0; c < lutT.size(); c++) lutT[c] = (T)lut[c];
+    int bhat = (int)(modswitch<T>((T)lwe[n], C::LOGN) & (2 * N - 1));
+    int a0 = (2 * N - bhat) & (2 * N - 1);
+    for (int r = 0; r < K1; r++)
+        for (int c = 0; c < N; c++) acc[(size_t)r * N + c] = rot_read<T, N>(&lutT[(size_t)r * N], c, a0);
+    std::vector<cplx> fbuf((size_t)K1 * L * C::REGION);
+    static cplx x[R][R];
+    static cplx F[K + 1][R][R];
+    for (int i = 0; i < n; i++) {
+        int a = (int)(modswitch<T>((T)lwe[i], C::LOGN) & (2 * N - 1));
+        if (a == 0) continue;
+        for (int r = 0; r < K1; r++)
+            for (int lane = 0; lane < R; lane++)
+                C::digits_fwd_pass1(lane, &acc[(size_t)r * N], a, &fbuf[(size_t)r * L * C::REGION], tw.fwd);
+        for (int r = 0; r < K1; r++)
+            for (int t = 0; t < L; t++) {
+                cplx *reg = &fbuf[(size_t)(r * L + t) * C::REGION];
+                for (int lane = 0; lane < R; lane++) C::fwd_pass2_load(lane, x[lane], reg);
+                for (int lane = 0; lane < R; lane++) C::fwd_pass2_store(lane, x[lane], reg);
+            }
+        const cplx *ggsw = &fbsk[(size_t)i * C::GGSW_CPLX];
+        for (int j = 0; j < K1; j++)
+            for (int lane = 0; lane < R; lane++) C::mac(lane, j, ggsw, fbuf.data(), F[j][lane]);
+        for (int j = 0; j < K1; j++)
+            for (int lane = 0; lane < R; lane++) C::inv_pass1(lane, F[j][lane], &fbuf[(size_t)j * L * C::REGION], tw.inv);
+        for (int j = 0; j < K1; j++)
+            for (int lane = 0; lane < R; lane++) C::inv_pass2_accumulate(lane, &fbuf[(size_t)j * L * C::REGION], &acc[(size_t)j * N]);
+    }
+    for (size_t c = 0; c < acc.size(); c++) out_glwe[c] = (uint64_t)acc[c];
+}
+
+template <typename T, int R, int K, int L, int BL>
+static int run(const uint64_t *bsk_std, int n, const uint64_t *lwe, int batch, const uint64_t *lut, uint64_t *out) {
+    std::vector<cplx> f;
+    convert_bsk<T, R, K, L, BL>(bsk_std, n, f);
+    const size_t glwe = (size_t)(K + 1) * 2 * R * R;
+    for (int b = 0; b < batch; b++) blind_rotate<T, R, K, L, BL>(f, n, lwe + (size_t)b * (n + 1), lut, out + b * glwe);
+    return 0;
+}
+
+// all arrays carried as uint64_t like the oracle's; bits selects the torus width
+extern "C" int emul_blind_rotate(int n, int k, int N, int base_log, int level, int bits, const uint64_t *bsk_std,
+                                 const uint64_t *lwe, int batch, const uint64_t *lut, uint64_t *out_glwe) {
+#define CASE(T, R, K, L, BL) \
+    if (bits == (int)sizeof(T) * 8 && N == 2 * R * R && k == K && level == L && base_log == BL) \
+        return run<T, R, K, L, BL>(bsk_std, n, lwe, batch, lut, out_glwe);
+    CASE(uint64_t, 16, 1, 2, 12)
+    CASE(uint32_t, 16, 2, 3, 6)
+    CASE(uint64_t, 32, 1, 1, 23)
+    CASE(uint64_t, 16, 3, 1, 18)
+#undef CASE
+    return 1;
+}
+
+// forward FFT of one integer polynomial then backward-add into zero: roundtrip / product helpers for FFT unit tests
+extern "C" int emul_fft_roundtrip(int N, const uint64_t *poly, uint64_t *out) {
+    if (N == 2048) {
+        typedef BRCore<uint64_t, 32, 1, 1, 23> C; constexpr int R = 32;
+        static TwTables<R> tw; fill_tw_tables(tw);
+        std::vector<cplx> region(C::REGION); std::vector<uint64_t> acc(N, 0);
+        static cplx x[R][R];
+        for (int lane = 0; lane < R; lane++) C::key_fwd_pass1(lane, poly, region.data(), tw.fwd);
+        for (int lane = 0; lane < R; lane++) C::fwd_pass2_load(lane, x[lane], region.data());
+        for (int lane = 0; lane < R; lane++) TeamFFT<R>::fwd_pass2_compute(x[lane]);
+        // registers hold position p natural; inverse wants register pp = position brev(pp)
+        static cplx y[R][R];
+        for (int lane = 0; lane < R; lane++) for (int pp = 0; pp < R; pp++) y[lane][pp] = x[lane][brev(pp, 5)];
+        for (int lane = 0; lane < R; lane++) C::inv_pass1(lane, y[lane], region.data(), tw.inv);
+        for (int lane = 0; lane < R; lane++) C::inv_pass2_accumulate(lane, region.data(), acc.data());
+        memcpy(out, acc.data(), sizeof(uint64_t) * N);
+        return 0;
+    }
+    return 1;
+}

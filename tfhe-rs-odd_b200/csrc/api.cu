@@ -1,0 +1,550 @@
+// api.cu -- the extern "C" boundary declared in include/b200tfhe.h.
+// Host-side logic only: argument validation (the reference's assert!s, lwe_keyswitch.rs:106-141,
+// lwe_programmable_bootstrapping.rs:1083-1097), workspace management, H2D/D2H staging and kernel launches.
+#include "../../include/b200tfhe.h"
+#include "kernels.h"
+#include "twiddles.hpp"
+#include <mutex>
+#include <string>
+#include <vector>
+#include <cstdio>
+#include <cstring>
+
+using namespace b200tfhe;
+
+static thread_local std::string g_global_err = "";
+
+struct Workspace {
+    enum { IN = 0, OUT, MID, LUTS, IDX, A, B, NSLOTS };
+    void *ptr[NSLOTS] = {};
+    size_t cap[NSLOTS] = {};
+    cudaError_t get(int slot, size_t bytes, void **out) {
+        if (bytes == 0) bytes = 16;
+        if (cap[slot] < bytes) {
+            if (ptr[slot]) cudaFree(ptr[slot]);
+            ptr[slot] = nullptr;
+            cap[slot] = 0;
+            cudaError_t e = cudaMalloc(&ptr[slot], bytes);
+            if (e != cudaSuccess) return e;
+            cap[slot] = bytes;
+        }
+        *out = ptr[slot];
+        return cudaSuccess;
+    }
+    void release() {
+        for (int i = 0; i < NSLOTS; i++) {
+            if (ptr[i]) cudaFree(ptr[i]);
+            ptr[i] = nullptr;
+            cap[i] = 0;
+        }
+    }
+};
+
+struct b200tfhe_context {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::mutex mu;
+    std::string err;
+    void *tw16 = nullptr, *tw32 = nullptr;  // TwTables<R> on the device
+    Workspace ws;
+    uint64_t launches = 0;
+};
+struct b200tfhe_bsk {
+    b200tfhe_context *ctx;
+    Params p;
+    void *d_fourier;
+    size_t bytes;
+};
+struct b200tfhe_ksk {
+    b200tfhe_context *ctx;
+    Params p;
+    void *d_ksk, *d_colsum;
+    size_t bytes;
+    bool finalized;
+};
+
+static int fail(b200tfhe_context *ctx, const std::string &msg) {
+    if (ctx) ctx->err = msg; else g_global_err = msg;
+    return 1;
+}
+static int fail_cuda(b200tfhe_context *ctx, const char *what, cudaError_t e) {
+    return fail(ctx, std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define CK(call)                                                   \
+    do {                                                           \
+        cudaError_t e_ = (call);                                   \
+        if (e_ != cudaSuccess) return fail_cuda(ctx, #call, e_);   \
+    } while (0)
+#define REQUIRE(cond, msg)                       \
+    do {                                         \
+        if (!(cond)) return fail(ctx, (msg));    \
+    } while (0)
+
+static Params to_params(const b200tfhe_params *p) {
+    Params q;
+    q.n = p->lwe_dimension; q.k = p->glwe_dimension; q.N = p->polynomial_size;
+    q.pbs_base_log = p->pbs_base_log; q.pbs_level = p->pbs_level;
+    q.ks_base_log = p->ks_base_log; q.ks_level = p->ks_level; q.bits = p->torus_bits;
+    return q;
+}
+static bool is_pow2(int v) { return v > 0 && (v & (v - 1)) == 0; }
+static size_t sz(const Params &p) { return (size_t)p.bits / 8; }
+static size_t big_len(const Params &p) { return (size_t)p.k * p.N + 1; }
+static size_t small_len(const Params &p) { return (size_t)p.n + 1; }
+static size_t glwe_len(const Params &p) { return (size_t)(p.k + 1) * p.N; }
+
+static const void *tw_fwd(const b200tfhe_context *ctx, int R) {
+    return R == 32 ? (const void *)((TwTables<32> *)ctx->tw32)->fwd : (const void *)((TwTables<16> *)ctx->tw16)->fwd;
+}
+static const void *tw_inv(const b200tfhe_context *ctx, int R) {
+    return R == 32 ? (const void *)((TwTables<32> *)ctx->tw32)->inv : (const void *)((TwTables<16> *)ctx->tw16)->inv;
+}
+
+extern "C" {
+
+const char *b200tfhe_last_error(const b200tfhe_context *ctx) { return ctx ? ctx->err.c_str() : g_global_err.c_str(); }
+
+int b200tfhe_context_create(int device, b200tfhe_context **out) {
+    b200tfhe_context *ctx = nullptr;
+    if (!out) return fail(nullptr, "context_create: null out pointer");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(nullptr, std::string("context_create: no CUDA device (") + cudaGetErrorString(e) + "); this library has no CPU fallback");
+    if (device < 0 || device >= count) return fail(nullptr, "context_create: device index out of range");
+    e = cudaSetDevice(device);
+    if (e != cudaSuccess) return fail_cuda(nullptr, "cudaSetDevice", e);
+    cudaDeviceProp prop;
+    e = cudaGetDeviceProperties(&prop, device);
+    if (e != cudaSuccess) return fail_cuda(nullptr, "cudaGetDeviceProperties", e);
+    if (prop.major != 10) return fail(nullptr, std::string("context_create: built for sm_100a only, device is ") + prop.name);
+    ctx = new b200tfhe_context();
+    ctx->device = device;
+    e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) { delete ctx; return fail_cuda(nullptr, "cudaStreamCreate", e); }
+    {
+        static TwTables<16> t16;
+        static TwTables<32> t32;
+        static std::once_flag once;
+        std::call_once(once, [] { fill_tw_tables(t16); fill_tw_tables(t32); });
+        if ((e = cudaMalloc(&ctx->tw16, sizeof(t16))) != cudaSuccess || (e = cudaMalloc(&ctx->tw32, sizeof(t32))) != cudaSuccess ||
+            (e = cudaMemcpy(ctx->tw16, &t16, sizeof(t16), cudaMemcpyHostToDevice)) != cudaSuccess ||
+            (e = cudaMemcpy(ctx->tw32, &t32, sizeof(t32), cudaMemcpyHostToDevice)) != cudaSuccess) {
+            delete ctx;
+            return fail_cuda(nullptr, "twiddle upload", e);
+        }
+    }
+    *out = ctx;
+    return 0;
+}
+
+int b200tfhe_context_destroy(b200tfhe_context *ctx) {
+    if (!ctx) return 0;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    ctx->ws.release();
+    cudaFree(ctx->tw16);
+    cudaFree(ctx->tw32);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return 0;
+}
+
+int b200tfhe_synchronize(b200tfhe_context *ctx) {
+    REQUIRE(ctx, "synchronize: null context");
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+void *b200tfhe_context_stream(b200tfhe_context *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
+uint64_t b200tfhe_launch_count(const b200tfhe_context *ctx) { return ctx ? ctx->launches : 0; }
+
+int b200tfhe_params_supported(const b200tfhe_params *p) {
+    if (!p) return 0;
+    return br_supported(to_params(p)) != 0;
+}
+
+// ---- keys ------------------------------------------------------------------------------------------------
+static int check_pbs_params(b200tfhe_context *ctx, const Params &p) {
+    REQUIRE(p.bits == 64 || p.bits == 32, "only native 2^64 / 2^32 ciphertext moduli are supported");
+    REQUIRE(p.n > 0 && p.k > 0 && is_pow2(p.N), "invalid dimensions");
+    REQUIRE(p.pbs_level > 0 && p.pbs_base_log > 0 && p.pbs_level * p.pbs_base_log < p.bits, "invalid PBS decomposition");
+    REQUIRE(br_supported(p) != 0, "blind rotation is not built for this (N, k, level, base_log, bits) set");
+    return 0;
+}
+static int check_ks_params(b200tfhe_context *ctx, const Params &p) {
+    REQUIRE(p.bits == 64 || p.bits == 32, "only native 2^64 / 2^32 ciphertext moduli are supported");
+    REQUIRE(p.n > 0 && p.k > 0 && p.N > 0, "invalid dimensions");
+    REQUIRE(p.ks_level > 0 && p.ks_base_log > 0 && p.ks_base_log <= 7 && p.ks_level * p.ks_base_log < p.bits,
+            "invalid keyswitch decomposition (base_log must be <= 7)");
+    return 0;
+}
+static size_t bsk_polys(const Params &p) { return (size_t)p.n * p.pbs_level * (p.k + 1) * (p.k + 1); }
+
+int b200tfhe_bsk_alloc(b200tfhe_context *ctx, const b200tfhe_params *pp, b200tfhe_bsk **out) {
+    REQUIRE(ctx && pp && out, "bsk_alloc: null argument");
+    *out = nullptr;
+    Params p = to_params(pp);
+    if (check_pbs_params(ctx, p)) return 1;
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    b200tfhe_bsk *k = new b200tfhe_bsk{ctx, p, nullptr, bsk_polys(p) * (p.N / 2) * sizeof(cplx)};
+    cudaError_t e = cudaMalloc(&k->d_fourier, k->bytes);
+    if (e != cudaSuccess) { delete k; return fail_cuda(ctx, "cudaMalloc(bsk)", e); }
+    *out = k;
+    return 0;
+}
+
+int b200tfhe_bsk_convert_dev(b200tfhe_context *ctx, const b200tfhe_params *pp, const void *d_std, b200tfhe_bsk **out) {
+    REQUIRE(ctx && pp && out && d_std, "bsk_convert_dev: null argument");
+    if (b200tfhe_bsk_alloc(ctx, pp, out)) return 1;
+    std::lock_guard<std::mutex> g(ctx->mu);
+    Params p = (*out)->p;
+    int rc = bsk_convert_launch(p, d_std, (*out)->d_fourier, tw_fwd(ctx, br_supported(p)), ctx->stream);
+    ctx->launches++;
+    if (rc) { b200tfhe_bsk_destroy(*out); *out = nullptr; return fail(ctx, "bsk_convert launch failed: " + std::to_string(rc)); }
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) { b200tfhe_bsk_destroy(*out); *out = nullptr; return fail_cuda(ctx, "bsk_convert", e); }
+    return 0;
+}
+
+static int bsk_upload(b200tfhe_context *ctx, const b200tfhe_params *pp, const void *std_bsk, int bits, b200tfhe_bsk **out) {
+    REQUIRE(ctx && pp && out && std_bsk, "bsk_upload: null argument");
+    *out = nullptr;
+    REQUIRE(pp->torus_bits == bits, "bsk_upload: torus_bits does not match the entry point");
+    Params p = to_params(pp);
+    if (check_pbs_params(ctx, p)) return 1;
+    void *d_std = nullptr;
+    size_t bytes = bsk_polys(p) * p.N * sz(p);
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMalloc(&d_std, bytes));
+    cudaError_t e = cudaMemcpy(d_std, std_bsk, bytes, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) { cudaFree(d_std); return fail_cuda(ctx, "cudaMemcpy(bsk)", e); }
+    int rc = b200tfhe_bsk_convert_dev(ctx, pp, d_std, out);
+    cudaFree(d_std);
+    return rc;
+}
+int b200tfhe_bsk_upload_u64(b200tfhe_context *ctx, const b200tfhe_params *p, const uint64_t *s, b200tfhe_bsk **out) { return bsk_upload(ctx, p, s, 64, out); }
+int b200tfhe_bsk_upload_u32(b200tfhe_context *ctx, const b200tfhe_params *p, const uint32_t *s, b200tfhe_bsk **out) { return bsk_upload(ctx, p, s, 32, out); }
+
+int b200tfhe_bsk_device_buffer(const b200tfhe_bsk *bsk, void **d_ptr, size_t *bytes) {
+    if (!bsk || !d_ptr || !bytes) return 1;
+    *d_ptr = bsk->d_fourier;
+    *bytes = bsk->bytes;
+    return 0;
+}
+int b200tfhe_bsk_destroy(b200tfhe_bsk *bsk) {
+    if (!bsk) return 0;
+    cudaSetDevice(bsk->ctx->device);
+    cudaFree(bsk->d_fourier);
+    delete bsk;
+    return 0;
+}
+
+int b200tfhe_ksk_alloc(b200tfhe_context *ctx, const b200tfhe_params *pp, b200tfhe_ksk **out) {
+    REQUIRE(ctx && pp && out, "ksk_alloc: null argument");
+    *out = nullptr;
+    Params p = to_params(pp);
+    if (check_ks_params(ctx, p)) return 1;
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    size_t bytes = (size_t)p.k * p.N * p.ks_level * small_len(p) * sz(p);
+    b200tfhe_ksk *k = new b200tfhe_ksk{ctx, p, nullptr, nullptr, bytes, false};
+    cudaError_t e = cudaMalloc(&k->d_ksk, bytes);
+    if (e == cudaSuccess) e = cudaMalloc(&k->d_colsum, small_len(p) * sz(p));
+    if (e != cudaSuccess) { cudaFree(k->d_ksk); delete k; return fail_cuda(ctx, "cudaMalloc(ksk)", e); }
+    *out = k;
+    return 0;
+}
+int b200tfhe_ksk_finalize(b200tfhe_context *ctx, b200tfhe_ksk *k) {
+    REQUIRE(ctx && k, "ksk_finalize: null argument");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    int rc = ks_colsum_launch(k->d_ksk, k->d_colsum, k->p.k * k->p.N, k->p.n, k->p.ks_level, k->p.ks_base_log, k->p.bits, ctx->stream);
+    ctx->launches++;
+    if (rc) return fail(ctx, "ks_colsum launch failed: " + std::to_string(rc));
+    CK(cudaStreamSynchronize(ctx->stream));
+    k->finalized = true;
+    return 0;
+}
+static int ksk_upload(b200tfhe_context *ctx, const b200tfhe_params *pp, const void *ksk, int bits, b200tfhe_ksk **out) {
+    REQUIRE(ctx && pp && out && ksk, "ksk_upload: null argument");
+    *out = nullptr;
+    REQUIRE(pp->torus_bits == bits, "ksk_upload: torus_bits does not match the entry point");
+    if (b200tfhe_ksk_alloc(ctx, pp, out)) return 1;
+    cudaError_t e = cudaMemcpy((*out)->d_ksk, ksk, (*out)->bytes, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) { b200tfhe_ksk_destroy(*out); *out = nullptr; return fail_cuda(ctx, "cudaMemcpy(ksk)", e); }
+    if (b200tfhe_ksk_finalize(ctx, *out)) { b200tfhe_ksk_destroy(*out); *out = nullptr; return 1; }
+    return 0;
+}
+int b200tfhe_ksk_upload_u64(b200tfhe_context *ctx, const b200tfhe_params *p, const uint64_t *k, b200tfhe_ksk **out) { return ksk_upload(ctx, p, k, 64, out); }
+int b200tfhe_ksk_upload_u32(b200tfhe_context *ctx, const b200tfhe_params *p, const uint32_t *k, b200tfhe_ksk **out) { return ksk_upload(ctx, p, k, 32, out); }
+int b200tfhe_ksk_device_buffer(const b200tfhe_ksk *ksk, void **d_ptr, size_t *bytes) {
+    if (!ksk || !d_ptr || !bytes) return 1;
+    *d_ptr = ksk->d_ksk;
+    *bytes = ksk->bytes;
+    return 0;
+}
+int b200tfhe_ksk_destroy(b200tfhe_ksk *ksk) {
+    if (!ksk) return 0;
+    cudaSetDevice(ksk->ctx->device);
+    cudaFree(ksk->d_ksk);
+    cudaFree(ksk->d_colsum);
+    delete ksk;
+    return 0;
+}
+
+}  // extern "C"
+
+// ---- device-pointer operations (caller holds ctx->mu) ---------------------------------------------------------
+static int ks_dev_locked(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const void *d_in, void *d_out, uint32_t batch) {
+    REQUIRE(ksk->finalized, "keyswitch: key not finalized (call b200tfhe_ksk_finalize after filling the device buffer)");
+    const Params &p = ksk->p;
+    KSLaunch a{d_in, big_len(p), d_out, small_len(p), ksk->d_ksk, ksk->d_colsum, p.k * p.N, p.n, p.ks_level, p.ks_base_log, p.bits, (int)batch};
+    int rc = ks_launch(a, ctx->stream);
+    ctx->launches++;
+    if (rc) return fail(ctx, "keyswitch launch failed: " + std::to_string(rc));
+    return 0;
+}
+static int br_dev_locked(b200tfhe_context *ctx, const b200tfhe_bsk *bsk, const void *d_in, void *d_out, const void *d_luts,
+                         const uint32_t *d_idx, uint32_t batch, int mode) {
+    const Params &p = bsk->p;
+    int R = br_supported(p);
+    BRLaunch a{d_in, small_len(p), d_luts, d_idx, bsk->d_fourier, d_out, mode == BR_MODE_GLWE ? glwe_len(p) : big_len(p),
+               p.n, (int)batch, mode, tw_fwd(ctx, R), tw_inv(ctx, R)};
+    int rc = br_launch(p, a, ctx->stream);
+    ctx->launches++;
+    if (rc) return fail(ctx, "blind_rotate launch failed: " + std::to_string(rc));
+    return 0;
+}
+static int check_pair(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk) {
+    REQUIRE(ksk && bsk, "null key handle");
+    REQUIRE(ksk->ctx == ctx && bsk->ctx == ctx, "key handle belongs to another context");
+    const Params &a = ksk->p, &b = bsk->p;
+    // the reference asserts matching dimensions / moduli: lwe_programmable_bootstrapping.rs:1083-1097
+    REQUIRE(a.n == b.n && a.k == b.k && a.N == b.N && a.bits == b.bits, "keyswitch key and bootstrap key dimensions differ");
+    return 0;
+}
+
+extern "C" {
+
+int b200tfhe_keyswitch_batch_dev(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const void *d_in, void *d_out, uint32_t batch) {
+    REQUIRE(ctx && ksk && (batch == 0 || (d_in && d_out)), "keyswitch_batch_dev: null argument");
+    REQUIRE(ksk->ctx == ctx, "key handle belongs to another context");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    return ks_dev_locked(ctx, ksk, d_in, d_out, batch);
+}
+int b200tfhe_pbs_batch_dev(b200tfhe_context *ctx, const b200tfhe_bsk *bsk, const void *d_in, void *d_out, const void *d_luts,
+                           const uint32_t *d_idx, uint32_t batch) {
+    REQUIRE(ctx && bsk && (batch == 0 || (d_in && d_out && d_luts)), "pbs_batch_dev: null argument");
+    REQUIRE(bsk->ctx == ctx, "key handle belongs to another context");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    return br_dev_locked(ctx, bsk, d_in, d_out, d_luts, d_idx, batch, BR_MODE_LWE);
+}
+int b200tfhe_blind_rotate_batch_dev(b200tfhe_context *ctx, const b200tfhe_bsk *bsk, const void *d_in, void *d_out, const void *d_luts,
+                                    const uint32_t *d_idx, uint32_t batch) {
+    REQUIRE(ctx && bsk && (batch == 0 || (d_in && d_out && d_luts)), "blind_rotate_batch_dev: null argument");
+    REQUIRE(bsk->ctx == ctx, "key handle belongs to another context");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    return br_dev_locked(ctx, bsk, d_in, d_out, d_luts, d_idx, batch, BR_MODE_GLWE);
+}
+int b200tfhe_ks_pbs_batch_dev(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, const void *d_in, void *d_out,
+                              const void *d_luts, const uint32_t *d_idx, uint32_t batch) {
+    REQUIRE(ctx && (batch == 0 || (d_in && d_out && d_luts)), "ks_pbs_batch_dev: null argument");
+    if (check_pair(ctx, ksk, bsk)) return 1;
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    void *d_mid;
+    CK(ctx->ws.get(Workspace::MID, (size_t)batch * small_len(bsk->p) * sz(bsk->p), &d_mid));
+    if (ks_dev_locked(ctx, ksk, d_in, d_mid, batch)) return 1;
+    return br_dev_locked(ctx, bsk, d_mid, d_out, d_luts, d_idx, batch, BR_MODE_LWE);
+}
+int b200tfhe_pbs_ks_batch_dev(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, const void *d_in, void *d_out,
+                              const void *d_luts, const uint32_t *d_idx, uint32_t batch) {
+    REQUIRE(ctx && (batch == 0 || (d_in && d_out && d_luts)), "pbs_ks_batch_dev: null argument");
+    if (check_pair(ctx, ksk, bsk)) return 1;
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    void *d_mid;
+    CK(ctx->ws.get(Workspace::MID, (size_t)batch * big_len(bsk->p) * sz(bsk->p), &d_mid));
+    if (br_dev_locked(ctx, bsk, d_in, d_mid, d_luts, d_idx, batch, BR_MODE_LWE)) return 1;
+    return ks_dev_locked(ctx, ksk, d_mid, d_out, batch);
+}
+
+}  // extern "C"
+
+// ---- host-pointer operations ---------------------------------------------------------------------------------
+enum Op { OP_KS, OP_PBS, OP_BR, OP_KS_PBS, OP_PBS_KS };
+
+static int host_op(b200tfhe_context *ctx, Op op, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, int bits, const void *in,
+                   void *out, const void *luts, uint32_t n_luts, const uint32_t *lut_idx, uint32_t batch) {
+    REQUIRE(ctx, "null context");
+    const bool need_ksk = (op == OP_KS || op == OP_KS_PBS || op == OP_PBS_KS), need_bsk = (op != OP_KS);
+    REQUIRE(!need_ksk || ksk, "null keyswitch key");
+    REQUIRE(!need_bsk || bsk, "null bootstrap key");
+    if (need_ksk && need_bsk && check_pair(ctx, ksk, bsk)) return 1;
+    REQUIRE(!need_ksk || ksk->ctx == ctx, "key handle belongs to another context");
+    REQUIRE(!need_bsk || bsk->ctx == ctx, "key handle belongs to another context");
+    const Params &p = need_bsk ? bsk->p : ksk->p;
+    REQUIRE(p.bits == bits, "torus width of the key does not match the entry point");
+    if (batch == 0) return 0;
+    REQUIRE(in && out, "null ciphertext buffer");
+    REQUIRE(!need_bsk || (luts && n_luts > 0), "null / empty accumulator list");
+    if (need_bsk && lut_idx)
+        for (uint32_t i = 0; i < batch; i++) REQUIRE(lut_idx[i] < n_luts, "lut_idx out of range");
+
+    const size_t s = sz(p);
+    const size_t in_len = (op == OP_KS || op == OP_KS_PBS) ? big_len(p) : small_len(p);
+    const size_t out_len = (op == OP_KS || op == OP_PBS_KS) ? small_len(p) : (op == OP_BR ? glwe_len(p) : big_len(p));
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    void *d_in, *d_out, *d_mid = nullptr, *d_luts = nullptr, *d_idx = nullptr;
+    CK(ctx->ws.get(Workspace::IN, batch * in_len * s, &d_in));
+    CK(ctx->ws.get(Workspace::OUT, batch * out_len * s, &d_out));
+    CK(cudaMemcpyAsync(d_in, in, batch * in_len * s, cudaMemcpyHostToDevice, ctx->stream));
+    if (need_bsk) {
+        CK(ctx->ws.get(Workspace::LUTS, (size_t)n_luts * glwe_len(p) * s, &d_luts));
+        CK(cudaMemcpyAsync(d_luts, luts, (size_t)n_luts * glwe_len(p) * s, cudaMemcpyHostToDevice, ctx->stream));
+        if (lut_idx) {
+            CK(ctx->ws.get(Workspace::IDX, (size_t)batch * 4, &d_idx));
+            CK(cudaMemcpyAsync(d_idx, lut_idx, (size_t)batch * 4, cudaMemcpyHostToDevice, ctx->stream));
+        }
+    }
+    int rc = 0;
+    switch (op) {
+        case OP_KS: rc = ks_dev_locked(ctx, ksk, d_in, d_out, batch); break;
+        case OP_PBS: rc = br_dev_locked(ctx, bsk, d_in, d_out, d_luts, (const uint32_t *)d_idx, batch, BR_MODE_LWE); break;
+        case OP_BR: rc = br_dev_locked(ctx, bsk, d_in, d_out, d_luts, (const uint32_t *)d_idx, batch, BR_MODE_GLWE); break;
+        case OP_KS_PBS:
+            CK(ctx->ws.get(Workspace::MID, batch * small_len(p) * s, &d_mid));
+            rc = ks_dev_locked(ctx, ksk, d_in, d_mid, batch);
+            if (!rc) rc = br_dev_locked(ctx, bsk, d_mid, d_out, d_luts, (const uint32_t *)d_idx, batch, BR_MODE_LWE);
+            break;
+        case OP_PBS_KS:
+            CK(ctx->ws.get(Workspace::MID, batch * big_len(p) * s, &d_mid));
+            rc = br_dev_locked(ctx, bsk, d_in, d_mid, d_luts, (const uint32_t *)d_idx, batch, BR_MODE_LWE);
+            if (!rc) rc = ks_dev_locked(ctx, ksk, d_mid, d_out, batch);
+            break;
+    }
+    if (rc) return 1;
+    CK(cudaMemcpyAsync(out, d_out, batch * out_len * s, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+extern "C" {
+
+#define HOST_OPS(SUF, T, BITS)                                                                                                          \
+    int b200tfhe_keyswitch_batch_##SUF(b200tfhe_context *c, const b200tfhe_ksk *k, const T *in, T *out, uint32_t b) {                   \
+        return host_op(c, OP_KS, k, nullptr, BITS, in, out, nullptr, 0, nullptr, b);                                                    \
+    }                                                                                                                                   \
+    int b200tfhe_pbs_batch_##SUF(b200tfhe_context *c, const b200tfhe_bsk *k, const T *in, T *out, const T *l, uint32_t nl,              \
+                                 const uint32_t *li, uint32_t b) {                                                                      \
+        return host_op(c, OP_PBS, nullptr, k, BITS, in, out, l, nl, li, b);                                                             \
+    }                                                                                                                                   \
+    int b200tfhe_blind_rotate_batch_##SUF(b200tfhe_context *c, const b200tfhe_bsk *k, const T *in, T *out, const T *l, uint32_t nl,     \
+                                          const uint32_t *li, uint32_t b) {                                                             \
+        return host_op(c, OP_BR, nullptr, k, BITS, in, out, l, nl, li, b);                                                              \
+    }                                                                                                                                   \
+    int b200tfhe_ks_pbs_batch_##SUF(b200tfhe_context *c, const b200tfhe_ksk *ks, const b200tfhe_bsk *k, const T *in, T *out,            \
+                                    const T *l, uint32_t nl, const uint32_t *li, uint32_t b) {                                          \
+        return host_op(c, OP_KS_PBS, ks, k, BITS, in, out, l, nl, li, b);                                                               \
+    }                                                                                                                                   \
+    int b200tfhe_pbs_ks_batch_##SUF(b200tfhe_context *c, const b200tfhe_ksk *ks, const b200tfhe_bsk *k, const T *in, T *out,            \
+                                    const T *l, uint32_t nl, const uint32_t *li, uint32_t b) {                                          \
+        return host_op(c, OP_PBS_KS, ks, k, BITS, in, out, l, nl, li, b);                                                               \
+    }
+HOST_OPS(u64, uint64_t, 64)
+HOST_OPS(u32, uint32_t, 32)
+#undef HOST_OPS
+
+int b200tfhe_gate_batch_u32(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, int gate, int pbs_first,
+                            const uint32_t *a, const uint32_t *b, uint32_t *out, uint32_t batch) {
+    REQUIRE(ctx, "null context");
+    if (check_pair(ctx, ksk, bsk)) return 1;
+    REQUIRE(gate >= 0 && gate <= 5, "unknown gate");
+    const Params &p = bsk->p;
+    REQUIRE(p.bits == 32, "boolean gates are defined on the 2^32 torus");
+    if (batch == 0) return 0;
+    REQUIRE(a && b && out, "null ciphertext buffer");
+    const size_t len = pbs_first ? small_len(p) : big_len(p);
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    void *d_a, *d_b, *d_in, *d_mid, *d_out, *d_lut;
+    CK(ctx->ws.get(Workspace::A, batch * len * 4, &d_a));
+    CK(ctx->ws.get(Workspace::B, batch * len * 4, &d_b));
+    CK(ctx->ws.get(Workspace::IN, batch * len * 4, &d_in));
+    CK(ctx->ws.get(Workspace::OUT, batch * len * 4, &d_out));
+    CK(ctx->ws.get(Workspace::MID, batch * (pbs_first ? big_len(p) : small_len(p)) * 4, &d_mid));
+    CK(ctx->ws.get(Workspace::LUTS, glwe_len(p) * 4, &d_lut));
+    CK(cudaMemcpyAsync(d_a, a, batch * len * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d_b, b, batch * len * 4, cudaMemcpyHostToDevice, ctx->stream));
+    {
+        // constant accumulator: mask 0, body all PLAINTEXT_TRUE (boolean/engine/bootstrapping.rs:59-60)
+        std::vector<uint32_t> lut(glwe_len(p), 0u);
+        for (int j = 0; j < p.N; j++) lut[(size_t)p.k * p.N + j] = 1u << 29;
+        CK(cudaMemcpyAsync(d_lut, lut.data(), lut.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));  // lut is a stack-lifetime host buffer
+    }
+    int rc = gate_prologue_launch(gate, (const uint32_t *)d_a, (const uint32_t *)d_b, (uint32_t *)d_in, (int)len, (int)batch, ctx->stream);
+    ctx->launches++;
+    if (rc) return fail(ctx, "gate prologue launch failed: " + std::to_string(rc));
+    if (pbs_first) {
+        rc = br_dev_locked(ctx, bsk, d_in, d_mid, d_lut, nullptr, batch, BR_MODE_LWE);
+        if (!rc) rc = ks_dev_locked(ctx, ksk, d_mid, d_out, batch);
+    } else {
+        rc = ks_dev_locked(ctx, ksk, d_in, d_mid, batch);
+        if (!rc) rc = br_dev_locked(ctx, bsk, d_mid, d_out, d_lut, nullptr, batch, BR_MODE_LWE);
+    }
+    if (rc) return 1;
+    CK(cudaMemcpyAsync(out, d_out, batch * len * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+static int modswitch_host(b200tfhe_context *ctx, const void *in, uint32_t *out, size_t count, uint32_t log2N, int bits) {
+    REQUIRE(ctx, "null context");
+    if (count == 0) return 0;
+    REQUIRE(in && out, "null buffer");
+    REQUIRE(log2N >= 1 && (int)log2N + 2 <= bits, "invalid polynomial size");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    void *d_in, *d_out;
+    CK(ctx->ws.get(Workspace::IN, count * (bits / 8), &d_in));
+    CK(ctx->ws.get(Workspace::OUT, count * 4, &d_out));
+    CK(cudaMemcpyAsync(d_in, in, count * (bits / 8), cudaMemcpyHostToDevice, ctx->stream));
+    int rc = modswitch_launch(d_in, (uint32_t *)d_out, count, (int)log2N, bits, ctx->stream);
+    ctx->launches++;
+    if (rc) return fail(ctx, "modswitch launch failed");
+    CK(cudaMemcpyAsync(out, d_out, count * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+int b200tfhe_modulus_switch_u64(b200tfhe_context *ctx, const uint64_t *in, uint32_t *out, size_t count, uint32_t l) { return modswitch_host(ctx, in, out, count, l, 64); }
+int b200tfhe_modulus_switch_u32(b200tfhe_context *ctx, const uint32_t *in, uint32_t *out, size_t count, uint32_t l) { return modswitch_host(ctx, in, out, count, l, 32); }
+
+static int sample_extract_host(b200tfhe_context *ctx, const void *glwe, void *lwe, uint32_t k, uint32_t N, uint32_t batch, int bits) {
+    REQUIRE(ctx, "null context");
+    if (batch == 0) return 0;
+    REQUIRE(glwe && lwe && k > 0 && N > 0, "invalid argument");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    const size_t s = bits / 8, in_b = (size_t)batch * (k + 1) * N * s, out_b = (size_t)batch * ((size_t)k * N + 1) * s;
+    void *d_in, *d_out;
+    CK(ctx->ws.get(Workspace::IN, in_b, &d_in));
+    CK(ctx->ws.get(Workspace::OUT, out_b, &d_out));
+    CK(cudaMemcpyAsync(d_in, glwe, in_b, cudaMemcpyHostToDevice, ctx->stream));
+    int rc = sample_extract_launch(d_in, d_out, (int)k, (int)N, (int)batch, bits, ctx->stream);
+    ctx->launches++;
+    if (rc) return fail(ctx, "sample_extract launch failed");
+    CK(cudaMemcpyAsync(lwe, d_out, out_b, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+int b200tfhe_sample_extract_batch_u64(b200tfhe_context *ctx, const uint64_t *g, uint64_t *l, uint32_t k, uint32_t N, uint32_t b) { return sample_extract_host(ctx, g, l, k, N, b, 64); }
+int b200tfhe_sample_extract_batch_u32(b200tfhe_context *ctx, const uint32_t *g, uint32_t *l, uint32_t k, uint32_t N, uint32_t b) { return sample_extract_host(ctx, g, l, k, N, b, 32); }
+
+}  // extern "C"

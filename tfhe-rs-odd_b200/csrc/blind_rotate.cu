@@ -1,0 +1,197 @@
+// blind_rotate.cu -- batched blind rotation / programmable bootstrap kernels for sm_100a.
+//
+// One launch per ciphertext batch.  A CTA owns CTS ciphertexts for all n CMUX iterations: their
+// accumulators live in shared memory as integer torus polynomials, one team of R threads per GLWE
+// polynomial.  Stage sequence per iteration (br_core.cuh): rotate-subtract + signed decomposition ->
+// register/shared-memory forward FFT -> Fourier multiply-accumulate against this iteration's GGSW
+// (read straight from L2: every CTA of a wave walks i in step) -> inverse FFT -> torus rounding.
+// Modulus switch (prologue), LUT rotation by -b_hat (prologue) and sample extraction (epilogue) are fused.
+//
+// Replaces FourierLweBootstrapKeyView::{blind_rotate_assign, bootstrap, bootstrap_without_sample_extract}
+// (tfhe/src/core_crypto/fft_impl/fft64/crypto/bootstrap.rs:243-412) and
+// par_convert_standard_lwe_bootstrap_key_to_fourier (algorithms/lwe_bootstrap_key_conversion.rs:99-152).
+#include "br_core.cuh"
+#include "kernels.h"
+
+namespace b200tfhe {
+
+template <typename T, int R, int K, int L, int BL, int CTS> struct BRConfig {
+    typedef BRCore<T, R, K, L, BL> C;
+    static constexpr int K1 = K + 1;
+    static constexpr int THREADS = CTS * K1 * R;
+    static_assert(THREADS % 32 == 0, "teams must fill whole warps");
+    static constexpr size_t FBUF_BYTES = (size_t)K1 * L * C::REGION * sizeof(cplx);   // per ciphertext
+    static constexpr size_t ACC_BYTES = (size_t)K1 * C::N * sizeof(T);
+    static size_t smem_bytes(int n) {
+        size_t ahat = (((size_t)(n + 1) * sizeof(uint16_t)) + 15) & ~(size_t)15;
+        return CTS * (FBUF_BYTES + ACC_BYTES + ahat);
+    }
+};
+
+template <typename T, int R, int K, int L, int BL, int CTS>
+__global__ void __launch_bounds__(CTS *(K + 1) * R)
+blind_rotate_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const T *__restrict__ luts,
+                    const uint32_t *__restrict__ lut_idx, const cplx *__restrict__ bsk, T *__restrict__ out,
+                    size_t out_stride, int n, int batch, int mode, const cplx *__restrict__ tw_fwd_,
+                    const cplx *__restrict__ tw_inv_) {
+    typedef BRConfig<T, R, K, L, BL, CTS> CFG;
+    typedef typename CFG::C C;
+    constexpr int K1 = K + 1, N = C::N, REGION = C::REGION;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+
+    const int team = threadIdx.x / R, lane = threadIdx.x % R;
+    const int ct_local = team / K1, r = team % K1;
+    int ct = blockIdx.x * CTS + ct_local;
+    const bool live = ct < batch;
+    if (!live) ct = batch - 1;  // ghost ciphertext: same work, no output (keeps barriers uniform)
+
+    const size_t ahat_bytes = (((size_t)(n + 1) * sizeof(uint16_t)) + 15) & ~(size_t)15;
+    cplx *fbuf_all = reinterpret_cast<cplx *>(smem_raw);
+    T *acc_all = reinterpret_cast<T *>(smem_raw + CTS * CFG::FBUF_BYTES);
+    uint16_t *ahat_all = reinterpret_cast<uint16_t *>(smem_raw + CTS * (CFG::FBUF_BYTES + CFG::ACC_BYTES));
+    cplx *fbuf_ct = fbuf_all + (size_t)ct_local * K1 * L * REGION;
+    cplx *fbuf_r = fbuf_ct + (size_t)r * L * REGION;
+    T *acc_ct = acc_all + (size_t)ct_local * K1 * N;
+    T *acc_r = acc_ct + (size_t)r * N;
+    uint16_t *ahat = reinterpret_cast<uint16_t *>(reinterpret_cast<unsigned char *>(ahat_all) + ct_local * ahat_bytes);
+
+    const cplx(*twf)[R] = reinterpret_cast<const cplx(*)[R]>(tw_fwd_);
+    const cplx(*twi)[R] = reinterpret_cast<const cplx(*)[R]>(tw_inv_);
+
+    // ---- prologue: modulus switch of the whole input LWE (fft_impl/common.rs:26-43) --------------------
+    const T *lwe = lwe_in + (size_t)ct * lwe_stride;
+    for (int i = r * R + lane; i <= n; i += K1 * R) ahat[i] = (uint16_t)(modswitch<T>(lwe[i], C::LOGN) & (2 * N - 1));
+    __syncthreads();
+    // acc <- LUT * X^{-b_hat}  (polynomial_algorithms.rs:315-354), as a rotation by 2N - b_hat
+    {
+        const T *lut = luts + (size_t)(lut_idx ? lut_idx[ct] : 0) * K1 * N + (size_t)r * N;
+        const int a0 = (2 * N - (int)ahat[n]) & (2 * N - 1);
+        for (int c = lane; c < N; c += R) acc_r[c] = rot_read<T, N>(lut, c, a0);
+    }
+    __syncwarp();
+
+    // ---- n CMUX iterations -----------------------------------------------------------------------------
+    for (int i = 0; i < n; i++) {
+        const int a = ahat[i];
+        C::digits_fwd_pass1(lane, acc_r, a, fbuf_r, twf);
+        __syncwarp();
+#pragma unroll
+        for (int t = 0; t < L; t++) {
+            cplx x[R];
+            C::fwd_pass2_load(lane, x, fbuf_r + t * REGION);
+            __syncwarp();
+            C::fwd_pass2_store(lane, x, fbuf_r + t * REGION);
+        }
+        __syncthreads();
+        cplx F[R];
+        C::mac(lane, r, bsk + (size_t)i * C::GGSW_CPLX, fbuf_ct, F);
+        __syncthreads();
+        C::inv_pass1(lane, F, fbuf_r, twi);
+        __syncwarp();
+        C::inv_pass2_accumulate(lane, fbuf_r, acc_r);
+        __syncwarp();
+    }
+
+    // ---- epilogue ---------------------------------------------------------------------------------------
+    if (!live) return;
+    T *o = out + (size_t)ct * out_stride;
+    if (mode == BR_MODE_GLWE) {
+        for (int c = lane; c < N; c += R) o[(size_t)r * N + c] = acc_r[c];
+    } else {
+        // sample extract, coefficient 0 (algorithms/glwe_sample_extraction.rs:91-147)
+        if (r < K) {
+            for (int t = lane; t < N; t += R) o[(size_t)r * N + t] = (t == 0) ? acc_r[0] : (T)(0 - acc_r[N - t]);
+        } else if (lane == 0) {
+            o[(size_t)K * N] = acc_r[0];
+        }
+    }
+}
+
+// Standard-domain bootstrap key [n][l][k+1][k+1][N] -> device Fourier layout [n][l][k+1][k+1][p][lane]
+template <typename T, int R>
+__global__ void __launch_bounds__(R * (64 / R) * (R == 32 ? 1 : 2)) bsk_convert_kernel(const T *__restrict__ std_bsk, cplx *__restrict__ out,
+                                                           size_t npoly, const cplx *__restrict__ tw_fwd_) {
+    typedef BRCore<T, R, 1, 1, 1> C;
+    constexpr int TEAMS = (R == 32) ? 2 : 8;  // 64 or 128 threads; keeps static smem < 48 KB
+    __shared__ __align__(16) cplx regions[TEAMS][C::REGION];
+    const int team = threadIdx.x / R, lane = threadIdx.x % R;
+    const cplx(*twf)[R] = reinterpret_cast<const cplx(*)[R]>(tw_fwd_);
+    size_t per_cta = (npoly + gridDim.x - 1) / gridDim.x;
+    per_cta = (per_cta + TEAMS - 1) / TEAMS * TEAMS;
+    size_t begin = (size_t)blockIdx.x * per_cta;
+    for (size_t base = begin; base < begin + per_cta; base += TEAMS) {
+        size_t pi = base + team;
+        bool ok = pi < npoly;
+        size_t pc = ok ? pi : npoly - 1;
+        C::key_fwd_pass1(lane, std_bsk + pc * C::N, regions[team], twf);
+        __syncwarp();
+        cplx x[R];
+        C::fwd_pass2_load(lane, x, regions[team]);
+        __syncwarp();
+        TeamFFT<R>::fwd_pass2_compute(x);
+        if (ok) {
+            cplx *o = out + pc * C::M;
+            static_for<0, R>([&](auto p) { o[decltype(p)::value * R + lane] = x[decltype(p)::value]; });
+        }
+        __syncwarp();
+    }
+}
+
+// ---- launch wrappers ----------------------------------------------------------------------------------------
+template <typename T, int R, int K, int L, int BL, int CTS>
+static int launch_br(const BRLaunch &a, cudaStream_t st) {
+    typedef BRConfig<T, R, K, L, BL, CTS> CFG;
+    auto kern = blind_rotate_kernel<T, R, K, L, BL, CTS>;
+    size_t smem = CFG::smem_bytes(a.n);
+    static bool configured = false;  // per instantiation
+    static size_t configured_smem = 0;
+    if (!configured || smem > configured_smem) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return (int)e;
+        configured = true;
+        configured_smem = smem;
+    }
+    int grid = (a.batch + CTS - 1) / CTS;
+    kern<<<grid, CFG::THREADS, smem, st>>>((const T *)a.lwe_in, a.lwe_stride, (const T *)a.luts, a.lut_idx,
+                                           (const cplx *)a.bsk, (T *)a.out, a.out_stride, a.n, a.batch, a.mode,
+                                           (const cplx *)a.tw_fwd, (const cplx *)a.tw_inv);
+    return (int)cudaGetLastError();
+}
+
+#define BR_INSTANCES(X)              \
+    X(uint64_t, 32, 1, 1, 23, 1)     \
+    X(uint32_t, 16, 2, 3, 6, 2)      \
+    X(uint64_t, 16, 3, 1, 18, 1)     \
+    X(uint64_t, 16, 1, 2, 12, 1)
+
+int br_supported(const Params &p) {
+#define X(T, R, K, L, BL, CTS) \
+    if (p.bits == (int)sizeof(T) * 8 && p.N == 2 * R * R && p.k == K && p.pbs_level == L && p.pbs_base_log == BL) return R;
+    BR_INSTANCES(X)
+#undef X
+    return 0;
+}
+
+int br_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
+    if (a.batch <= 0) return 0;
+#define X(T, R, K, L, BL, CTS) \
+    if (p.bits == (int)sizeof(T) * 8 && p.N == 2 * R * R && p.k == K && p.pbs_level == L && p.pbs_base_log == BL) \
+        return launch_br<T, R, K, L, BL, CTS>(a, st);
+    BR_INSTANCES(X)
+#undef X
+    return -1;
+}
+
+int bsk_convert_launch(const Params &p, const void *std_bsk, void *out, const void *tw_fwd, cudaStream_t st) {
+    size_t npoly = (size_t)p.n * p.pbs_level * (p.k + 1) * (p.k + 1);
+    int R = br_supported(p);
+    int grid = 148 * 4;
+    if (R == 32 && p.bits == 64) bsk_convert_kernel<uint64_t, 32><<<grid, 64, 0, st>>>((const uint64_t *)std_bsk, (cplx *)out, npoly, (const cplx *)tw_fwd);
+    else if (R == 16 && p.bits == 64) bsk_convert_kernel<uint64_t, 16><<<grid, 128, 0, st>>>((const uint64_t *)std_bsk, (cplx *)out, npoly, (const cplx *)tw_fwd);
+    else if (R == 32 && p.bits == 32) bsk_convert_kernel<uint32_t, 32><<<grid, 64, 0, st>>>((const uint32_t *)std_bsk, (cplx *)out, npoly, (const cplx *)tw_fwd);
+    else if (R == 16 && p.bits == 32) bsk_convert_kernel<uint32_t, 16><<<grid, 128, 0, st>>>((const uint32_t *)std_bsk, (cplx *)out, npoly, (const cplx *)tw_fwd);
+    else return -1;
+    return (int)cudaGetLastError();
+}
+
+}  // namespace b200tfhe

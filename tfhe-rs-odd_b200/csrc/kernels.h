@@ -1,0 +1,43 @@
+// kernels.h -- internal launch interface between the C-ABI layer (api.cu) and the kernel translation units.
+#pragma once
+#include "common.cuh"
+#include <cuda_runtime.h>
+
+namespace b200tfhe {
+
+enum { BR_MODE_LWE = 0, BR_MODE_GLWE = 1 };
+
+struct BRLaunch {
+    const void *lwe_in;    // [batch][lwe_stride] small-key LWE ciphertexts (device)
+    size_t lwe_stride;     // in scalars, >= n+1
+    const void *luts;      // [n_lut][(k+1)N] accumulators (device)
+    const uint32_t *lut_idx;  // [batch] or nullptr (all use LUT 0)
+    const void *bsk;       // device Fourier bootstrap key
+    void *out;             // [batch][out_stride]
+    size_t out_stride;
+    int n, batch, mode;
+    const void *tw_fwd, *tw_inv;
+};
+
+// blind_rotate.cu
+int br_supported(const Params &p);  // returns team radix R (16/32) or 0
+int br_launch(const Params &p, const BRLaunch &a, cudaStream_t st);
+int bsk_convert_launch(const Params &p, const void *std_bsk, void *out, const void *tw_fwd, cudaStream_t st);
+
+// keyswitch.cu
+struct KSLaunch {
+    const void *in;   size_t in_stride;    // [batch][in_stride], n_in+1 used
+    void *out;        size_t out_stride;   // [batch][out_stride], n_out+1 written
+    const void *ksk;                       // device copy of the reference layout [n_in][l_ks][n_out+1]
+    const void *colsum;                    // [n_out+1]  2^(b-1) * sum of all key rows (digit offset correction)
+    int n_in, n_out, level, base_log, bits, batch;
+};
+int ks_launch(const KSLaunch &a, cudaStream_t st);
+int ks_colsum_launch(const void *ksk, void *colsum, int n_in, int n_out, int level, int base_log, int bits, cudaStream_t st);
+
+// misc_kernels.cu
+int modswitch_launch(const void *in, uint32_t *out, size_t count, int log2N, int bits, cudaStream_t st);
+int sample_extract_launch(const void *glwe, void *lwe, int k, int N, int batch, int bits, cudaStream_t st);
+int gate_prologue_launch(int gate, const uint32_t *a, const uint32_t *b, uint32_t *out, int len, int batch, cudaStream_t st);
+
+}  // namespace b200tfhe

@@ -1,0 +1,129 @@
+// keyswitch.cu -- batched LWE keyswitch, bit-exact wrapping integer arithmetic.
+//
+// Replaces keyswitch_lwe_ciphertext (tfhe/src/core_crypto/algorithms/lwe_keyswitch.rs:96-170; inner op
+// slice_wrapping_sub_scalar_mul_assign, slice_algorithms.rs:363-459):
+//     out = (0,...,0,b_in) - sum_i sum_t digit_t(a_i) * KSK[i][t]
+// with the key kept in the reference's own layout [n_in][l_ks][n_out+1] (levels stored l_ks -> 1, the order
+// the decomposition iterator emits them, lwe_keyswitch_key_generation.rs:109-120).
+//
+// Batched, this is an integer "GEMM" over Z/2^W:  [batch x (n_in*l)] digits  x  [(n_in*l) x (n_out+1)] key.
+// Tiling: a CTA owns BT ciphertexts x JT output columns and walks all key rows; a thread owns a 4x4
+// register tile.  Digits are made non-negative (d' = d + B/2 in [0, B]) so one multiply-add is
+// IMAD.WIDE.U32 + IMAD (u64) or a single IMAD (u32); the offset is undone with a per-key column sum:
+//     sum (d' - B/2) K = sum d' K - (B/2) * colsum,   colsum[j] = sum_{i,t} KSK[i][t][j]   (computed at upload).
+// All arithmetic wraps mod 2^W, so the result is bit-identical to the serial reference loop.
+#include "kernels.h"
+
+namespace b200tfhe {
+
+constexpr int KS_BT = 32;     // ciphertexts per CTA
+constexpr int KS_JT = 128;    // output columns per CTA
+constexpr int KS_IC = 32;     // input coefficients per digit chunk
+constexpr int KS_THREADS = 256;
+
+template <typename T>
+__global__ void __launch_bounds__(KS_THREADS)
+ks_kernel(const T *__restrict__ in, size_t in_stride, T *__restrict__ out, size_t out_stride,
+          const T *__restrict__ ksk, const T *__restrict__ colsum, int n_in, int n_out, int level, int base_log,
+          int batch) {
+    // digits of the current chunk: dig[(ii*level + t)][b] as bytes, 4 ciphertexts packed per 32-bit word
+    extern __shared__ __align__(16) unsigned char dig[];
+    const int tid = threadIdx.x;
+    const int cg = tid % 32, bg = tid / 32;          // column group (4 columns), ciphertext group (4 cts)
+    const int b0 = blockIdx.x * KS_BT, j0 = blockIdx.y * KS_JT + cg * 4;
+    const int width = n_out + 1;
+    const uint32_t half_b = 1u << (base_log - 1);
+
+    T acc[4][4];
+#pragma unroll
+    for (int x = 0; x < 4; x++)
+#pragma unroll
+        for (int y = 0; y < 4; y++) acc[x][y] = 0;
+
+    const bool col_ok[4] = {j0 + 0 < width, j0 + 1 < width, j0 + 2 < width, j0 + 3 < width};
+    const bool vec_ok = (j0 + 3 < width) && ((((size_t)width * sizeof(T)) % 16) == 0);
+
+    for (int i0 = 0; i0 < n_in; i0 += KS_IC) {
+        __syncthreads();
+        // ---- decompose KS_BT x KS_IC input coefficients into `level` digits each ----
+        for (int e = tid; e < KS_BT * KS_IC; e += KS_THREADS) {
+            const int b = e / KS_IC, ii = e % KS_IC;
+            const int gb = b0 + b, gi = i0 + ii;
+            T v = (gb < batch && gi < n_in) ? in[(size_t)gb * in_stride + gi] : (T)0;
+            T state = decomp_init_state<T>(v, base_log, level);
+            for (int t = 0; t < level; t++) {
+                int d = (int)decomp_next_digit<T>(state, base_log);
+                dig[(size_t)(ii * level + t) * KS_BT + b] = (unsigned char)(d + (int)half_b);
+            }
+        }
+        __syncthreads();
+        // ---- rows of this chunk ----
+        const int rows = min(KS_IC, n_in - i0) * level;
+        const T *krow = ksk + (size_t)i0 * level * width + j0;
+#pragma unroll 4
+        for (int rr = 0; rr < rows; rr++, krow += width) {
+            T kv[4];
+#pragma unroll
+            for (int y = 0; y < 4; y++) kv[y] = col_ok[y] ? krow[y] : (T)0;
+            const uint32_t packed = *reinterpret_cast<const uint32_t *>(dig + (size_t)rr * KS_BT + bg * 4);
+#pragma unroll
+            for (int x = 0; x < 4; x++) {
+                const uint32_t d = (packed >> (8 * x)) & 0xFFu;
+#pragma unroll
+                for (int y = 0; y < 4; y++) acc[x][y] += (T)d * kv[y];
+            }
+        }
+    }
+    (void)vec_ok;
+    // ---- epilogue: out = [body] - (acc - B/2 * colsum) ----
+#pragma unroll
+    for (int x = 0; x < 4; x++) {
+        const int gb = b0 + bg * 4 + x;
+        if (gb >= batch) continue;
+#pragma unroll
+        for (int y = 0; y < 4; y++) {
+            const int j = j0 + y;
+            if (j >= width) continue;
+            T v = (T)half_b * colsum[j] - acc[x][y];
+            if (j == n_out) v += in[(size_t)gb * in_stride + n_in];
+            out[(size_t)gb * out_stride + j] = v;
+        }
+    }
+}
+
+template <typename T>
+__global__ void ks_colsum_kernel(const T *__restrict__ ksk, T *__restrict__ colsum, size_t rows, int width) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= width) return;
+    T s = 0;
+    for (size_t r = 0; r < rows; r++) s += ksk[r * width + j];
+    colsum[j] = s;
+}
+
+int ks_colsum_launch(const void *ksk, void *colsum, int n_in, int n_out, int level, int base_log, int bits,
+                     cudaStream_t st) {
+    (void)base_log;
+    const int width = n_out + 1;
+    const size_t rows = (size_t)n_in * level;
+    if (bits == 64) ks_colsum_kernel<uint64_t><<<(width + 127) / 128, 128, 0, st>>>((const uint64_t *)ksk, (uint64_t *)colsum, rows, width);
+    else ks_colsum_kernel<uint32_t><<<(width + 127) / 128, 128, 0, st>>>((const uint32_t *)ksk, (uint32_t *)colsum, rows, width);
+    return (int)cudaGetLastError();
+}
+
+int ks_launch(const KSLaunch &a, cudaStream_t st) {
+    if (a.batch <= 0) return 0;
+    if (a.base_log < 1 || a.base_log > 7 || a.level < 1 || a.level * a.base_log >= a.bits) return -1;
+    dim3 grid((a.batch + KS_BT - 1) / KS_BT, (a.n_out + 1 + KS_JT - 1) / KS_JT);
+    size_t smem = (size_t)KS_IC * a.level * KS_BT;
+    if (a.bits == 64)
+        ks_kernel<uint64_t><<<grid, KS_THREADS, smem, st>>>((const uint64_t *)a.in, a.in_stride, (uint64_t *)a.out, a.out_stride,
+                                                            (const uint64_t *)a.ksk, (const uint64_t *)a.colsum, a.n_in, a.n_out,
+                                                            a.level, a.base_log, a.batch);
+    else
+        ks_kernel<uint32_t><<<grid, KS_THREADS, smem, st>>>((const uint32_t *)a.in, a.in_stride, (uint32_t *)a.out, a.out_stride,
+                                                            (const uint32_t *)a.ksk, (const uint32_t *)a.colsum, a.n_in, a.n_out,
+                                                            a.level, a.base_log, a.batch);
+    return (int)cudaGetLastError();
+}
+
+}  // namespace b200tfhe

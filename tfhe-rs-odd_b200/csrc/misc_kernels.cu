@@ -1,0 +1,88 @@
+// misc_kernels.cu -- the small bit-exact integer stages, as stand-alone coalesced kernels.
+//   modswitch        fast_pbs_modulus_switch            tfhe/src/core_crypto/fft_impl/common.rs:26-43
+//   sample extract   extract_lwe_sample_from_glwe (nth=0) algorithms/glwe_sample_extraction.rs:91-147
+//   gate prologue    boolean binary-gate linear combos  tfhe/src/boolean/engine/mod.rs:607-798
+// (Inside the PBS both modswitch and sample extract are fused into blind_rotate_kernel; these entry points
+//  exist so each stage can be checked bit-for-bit and for callers that chain stages themselves.)
+#include "kernels.h"
+
+namespace b200tfhe {
+
+template <typename T> __global__ void modswitch_kernel(const T *__restrict__ in, uint32_t *__restrict__ out, size_t count, int log2N) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (; i < count; i += stride) out[i] = modswitch<T>(in[i], log2N);
+}
+
+int modswitch_launch(const void *in, uint32_t *out, size_t count, int log2N, int bits, cudaStream_t st) {
+    if (count == 0) return 0;
+    int grid = (int)((count + 255) / 256);
+    if (grid > 148 * 16) grid = 148 * 16;
+    if (bits == 64) modswitch_kernel<uint64_t><<<grid, 256, 0, st>>>((const uint64_t *)in, out, count, log2N);
+    else modswitch_kernel<uint32_t><<<grid, 256, 0, st>>>((const uint32_t *)in, out, count, log2N);
+    return (int)cudaGetLastError();
+}
+
+// lwe[b][p*N + t] = (t == 0) ? glwe[b][p][0] : -glwe[b][p][N - t];  lwe[b][k*N] = glwe[b][k][0]
+template <typename T> __global__ void sample_extract_kernel(const T *__restrict__ glwe, T *__restrict__ lwe, int k, int N, int batch) {
+    const size_t per_in = (size_t)(k + 1) * N, per_out = (size_t)k * N + 1;
+    const size_t total = per_out * (size_t)batch;
+    size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (; e < total; e += stride) {
+        const size_t b = e / per_out, o = e % per_out;
+        const T *g = glwe + b * per_in;
+        T v;
+        if (o == (size_t)k * N) v = g[(size_t)k * N];
+        else {
+            const size_t p = o / N, t = o % N;
+            v = (t == 0) ? g[p * N] : (T)(0 - g[p * N + (N - t)]);
+        }
+        lwe[e] = v;
+    }
+}
+
+int sample_extract_launch(const void *glwe, void *lwe, int k, int N, int batch, int bits, cudaStream_t st) {
+    if (batch <= 0) return 0;
+    size_t total = ((size_t)k * N + 1) * batch;
+    int grid = (int)((total + 255) / 256);
+    if (grid > 148 * 16) grid = 148 * 16;
+    if (bits == 64) sample_extract_kernel<uint64_t><<<grid, 256, 0, st>>>((const uint64_t *)glwe, (uint64_t *)lwe, k, N, batch);
+    else sample_extract_kernel<uint32_t><<<grid, 256, 0, st>>>((const uint32_t *)glwe, (uint32_t *)lwe, k, N, batch);
+    return (int)cudaGetLastError();
+}
+
+// gate: 0 AND 1 NAND 2 OR 3 NOR 4 XOR 5 XNOR.  PLAINTEXT_TRUE = 1<<29, FALSE = 7<<29 (boolean/mod.rs:74-80).
+__global__ void gate_prologue_kernel(int gate, const uint32_t *__restrict__ a, const uint32_t *__restrict__ b,
+                                     uint32_t *__restrict__ out, int len, int batch) {
+    const size_t total = (size_t)len * batch;
+    size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    const uint32_t T_ = 1u << 29, F_ = 7u << 29, Q_ = 1u << 30;
+    for (; e < total; e += stride) {
+        const uint32_t s = a[e] + b[e];
+        uint32_t v, cst;
+        switch (gate) {
+            case 0: v = s; cst = F_; break;                   // AND  : a + b - 1/8      engine/mod.rs:620-640
+            case 1: v = 0u - s; cst = T_; break;              // NAND : -(a + b) + 1/8   :646-682
+            case 2: v = s; cst = T_; break;                   // OR   : a + b + 1/8
+            case 3: v = 0u - s; cst = F_; break;              // NOR  : -(a + b) - 1/8
+            case 4: v = 2u * s; cst = Q_; break;              // XOR  : 2(a + b) + 1/4   :760-798
+            default: v = 0u - 2u * s; cst = 0u - Q_; break;   // XNOR : -2(a + b) - 1/4
+        }
+        if ((int)(e % len) == len - 1) v += cst;
+        out[e] = v;
+    }
+}
+
+int gate_prologue_launch(int gate, const uint32_t *a, const uint32_t *b, uint32_t *out, int len, int batch, cudaStream_t st) {
+    if (batch <= 0) return 0;
+    if (gate < 0 || gate > 5) return -1;
+    size_t total = (size_t)len * batch;
+    int grid = (int)((total + 255) / 256);
+    if (grid > 148 * 16) grid = 148 * 16;
+    gate_prologue_kernel<<<grid, 256, 0, st>>>(gate, a, b, out, len, batch);
+    return (int)cudaGetLastError();
+}
+
+}  // namespace b200tfhe
