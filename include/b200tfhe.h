@@ -156,6 +156,10 @@ int b200tfhe_ks_pbs_batch_dev(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, co
 int b200tfhe_pbs_ks_batch_dev(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, const void *d_in,
                               void *d_out, const void *d_luts, const uint32_t *d_lut_idx, uint32_t batch);
 
+/* sustained FP64 FMA rate of the device in TFLOP/s (register-only probe kernel, best of repeated runs over
+ * about duration_ms): the measured denominator of the blind rotation's FP64 roofline */
+int b200tfhe_probe_fp64_tflops(b200tfhe_context *ctx, double duration_ms, double *tflops);
+
 /* number of kernel launches issued through this context so far (bench.py's gpu_launches) */
 uint64_t b200tfhe_launch_count(const b200tfhe_context *ctx);
 

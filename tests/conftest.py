@@ -1,0 +1,49 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a real B200 (run with -m gpu on the GPU box)")
+
+
+@pytest.fixture(scope="session")
+def ctx():
+    import tfhe_rs_odd_b200 as t
+    c = t.Context(0)   # raises on a box without a GPU / without the built library: no CPU fallback
+    yield c
+    c.close()
+
+
+_ORACLES = {}
+
+
+def get_oracle(name):
+    """Session-cached oracle with generated keys (test infrastructure)."""
+    from oracle.oracle import Oracle
+    if name not in _ORACLES:
+        _ORACLES[name] = Oracle(name).keygen()
+    return _ORACLES[name]
+
+
+def params_of(o):
+    import tfhe_rs_odd_b200 as t
+    return t.core_crypto.make_params(o.n, o.k, o.N, o.b, o.l, o.b_ks, o.l_ks, o.bits)
+
+
+def phase_bound(o):
+    """Bound on |phase_gpu - phase_oracle| (torus units) for one PBS.
+
+    Two f64 FFT implementations with different operation order differ by ~2^-25 of the torus after ONE external
+    product; from the first CMUX where that flips a rounding decision of the signed decomposition the two
+    accumulators are different (equally valid) ciphertexts and every later rounding is independent.  The phase
+    difference is then the difference of two independent draws of the decomposition-rounding noise, whose
+    variance per PBS is  (n/2) * (1 + kN/2) * 2^(-2 b l) / 12 .  We allow 8 sigma of the difference.
+    """
+    var = (o.n / 2.0) * (1.0 + o.k * o.N / 2.0) * 2.0 ** (-2 * o.b * o.l) / 12.0
+    return 8.0 * (2.0 * var) ** 0.5

@@ -48,6 +48,7 @@ _PROTOS = {
     "b200tfhe_ks_pbs_batch_dev": [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _U32],
     "b200tfhe_pbs_ks_batch_dev": [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _U32],
     "b200tfhe_launch_count": [_VP],
+    "b200tfhe_probe_fp64_tflops": [_VP, C.c_double, C.POINTER(C.c_double)],
 }
 for _s in ("u64", "u32"):
     _PROTOS[f"b200tfhe_keyswitch_batch_{_s}"] = [_VP, _VP, _VP, _VP, _U32]

@@ -1,0 +1,296 @@
+"""Host-side mirror of tfhe::core_crypto for the KS+PBS path, over the C ABI (include/b200tfhe.h).
+
+Names and argument meaning follow the reference (paths relative to /root/reference/tfhe/src/core_crypto):
+  keyswitch_lwe_ciphertext                     algorithms/lwe_keyswitch.rs:96-170
+  programmable_bootstrap_lwe_ciphertext        algorithms/lwe_programmable_bootstrapping.rs:1017-1113
+  blind_rotate_assign                          algorithms/lwe_programmable_bootstrapping.rs:232-289
+  programmable_bootstrap_..._without_sample_extract   :1115-1162 (fork)
+  convert_standard_lwe_bootstrap_key_to_fourier       algorithms/lwe_bootstrap_key_conversion.rs:21-152
+  extract_lwe_sample_from_glwe_ciphertext      algorithms/glwe_sample_extraction.rs:91-147
+  fast_pbs_modulus_switch                      fft_impl/common.rs:26-43
+The reference API is one ciphertext per call; every function here also accepts a list (2-D array), which is
+the unit the GPU works on.  Errors: the reference panics on dimension / modulus mismatch; here the C ABI
+returns non-zero and this layer raises B200TfheError with the library's message.
+"""
+import ctypes as C
+import numpy as np
+
+from . import _native
+from ._native import Params
+
+
+class B200TfheError(RuntimeError):
+    pass
+
+
+def _dtype(bits):
+    return np.uint64 if bits == 64 else np.uint32
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+class Context:
+    """One CUDA device + stream + workspace (the thread-local engine of shortint/engine/mod.rs:23-69)."""
+
+    def __init__(self, device=0):
+        self._lib = _native.lib()
+        h = C.c_void_p()
+        rc = self._lib.b200tfhe_context_create(int(device), C.byref(h))
+        if rc != 0:
+            raise B200TfheError(self._lib.b200tfhe_last_error(None).decode())
+        self._h = h
+        self.device = device
+
+    def check(self, rc):
+        if rc != 0:
+            raise B200TfheError(self._lib.b200tfhe_last_error(self._h).decode())
+
+    def synchronize(self):
+        self.check(self._lib.b200tfhe_synchronize(self._h))
+
+    @property
+    def stream(self):
+        return self._lib.b200tfhe_context_stream(self._h)
+
+    @property
+    def launch_count(self):
+        return int(self._lib.b200tfhe_launch_count(self._h))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.b200tfhe_context_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def make_params(n, k, N, pbs_base_log, pbs_level, ks_base_log, ks_level, bits):
+    return Params(n, k, N, pbs_base_log, pbs_level, ks_base_log, ks_level, bits)
+
+
+class FourierLweBootstrapKey:
+    """Device-resident Fourier bootstrap key (fft_impl/fft64/crypto/bootstrap.rs:27-33)."""
+
+    def __init__(self, ctx, params, handle):
+        self.ctx, self.params, self._h = ctx, params, handle
+
+    @property
+    def bits(self):
+        return self.params.torus_bits
+
+    def device_buffer(self):
+        p, n = C.c_void_p(), C.c_size_t()
+        self.ctx.check(self.ctx._lib.b200tfhe_bsk_device_buffer(self._h, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    @classmethod
+    def alloc(cls, ctx, params):
+        h = C.c_void_p()
+        ctx.check(ctx._lib.b200tfhe_bsk_alloc(ctx._h, C.byref(params), C.byref(h)))
+        return cls(ctx, params, h)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.ctx._lib.b200tfhe_bsk_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def convert_standard_lwe_bootstrap_key_to_fourier(ctx, params, std_bsk):
+    """std_bsk: flat [n][l][k+1][k+1][N] scalars (entities/lwe_bootstrap_key.rs:99-106) -> FourierLweBootstrapKey."""
+    dt = _dtype(params.torus_bits)
+    a = np.ascontiguousarray(std_bsk, dtype=dt).reshape(-1)
+    expect = params.lwe_dimension * params.pbs_level * (params.glwe_dimension + 1) ** 2 * params.polynomial_size
+    if a.size != expect:
+        raise B200TfheError(f"bootstrap key has {a.size} scalars, parameters imply {expect}")
+    h = C.c_void_p()
+    fn = ctx._lib.b200tfhe_bsk_upload_u64 if params.torus_bits == 64 else ctx._lib.b200tfhe_bsk_upload_u32
+    ctx.check(fn(ctx._h, C.byref(params), _ptr(a), C.byref(h)))
+    return FourierLweBootstrapKey(ctx, params, h)
+
+
+def convert_standard_lwe_bootstrap_key_to_fourier_dev(ctx, params, d_std_bsk_ptr):
+    h = C.c_void_p()
+    ctx.check(ctx._lib.b200tfhe_bsk_convert_dev(ctx._h, C.byref(params), C.c_void_p(d_std_bsk_ptr), C.byref(h)))
+    return FourierLweBootstrapKey(ctx, params, h)
+
+
+class LweKeyswitchKey:
+    """Device-resident keyswitch key in the reference layout (entities/lwe_keyswitch_key.rs:77-108)."""
+
+    def __init__(self, ctx, params, handle):
+        self.ctx, self.params, self._h = ctx, params, handle
+
+    @property
+    def bits(self):
+        return self.params.torus_bits
+
+    @classmethod
+    def upload(cls, ctx, params, ksk):
+        dt = _dtype(params.torus_bits)
+        a = np.ascontiguousarray(ksk, dtype=dt).reshape(-1)
+        expect = params.glwe_dimension * params.polynomial_size * params.ks_level * (params.lwe_dimension + 1)
+        if a.size != expect:
+            raise B200TfheError(f"keyswitch key has {a.size} scalars, parameters imply {expect}")
+        h = C.c_void_p()
+        fn = ctx._lib.b200tfhe_ksk_upload_u64 if params.torus_bits == 64 else ctx._lib.b200tfhe_ksk_upload_u32
+        ctx.check(fn(ctx._h, C.byref(params), _ptr(a), C.byref(h)))
+        return cls(ctx, params, h)
+
+    @classmethod
+    def alloc(cls, ctx, params):
+        h = C.c_void_p()
+        ctx.check(ctx._lib.b200tfhe_ksk_alloc(ctx._h, C.byref(params), C.byref(h)))
+        return cls(ctx, params, h)
+
+    def device_buffer(self):
+        p, n = C.c_void_p(), C.c_size_t()
+        self.ctx.check(self.ctx._lib.b200tfhe_ksk_device_buffer(self._h, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def finalize(self):
+        self.ctx.check(self.ctx._lib.b200tfhe_ksk_finalize(self.ctx._h, self._h))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.ctx._lib.b200tfhe_ksk_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+# ---- batched operations (host arrays in, host arrays out) ------------------------------------------------------
+def _suf(bits):
+    return "u64" if bits == 64 else "u32"
+
+
+def _as_list(a, width, bits, what):
+    a = np.ascontiguousarray(a, dtype=_dtype(bits))
+    single = a.ndim == 1
+    a = a.reshape(-1, a.shape[-1]) if a.size else a.reshape(0, width)
+    if a.shape[1] != width:
+        raise B200TfheError(f"{what}: ciphertext length {a.shape[1]} != expected {width}")
+    return a, single
+
+
+def _luts(acc, idx, p, batch):
+    glwe = (p.glwe_dimension + 1) * p.polynomial_size
+    luts = np.ascontiguousarray(acc, dtype=_dtype(p.torus_bits)).reshape(-1, glwe)
+    li = None
+    if idx is not None:
+        li = np.ascontiguousarray(idx, dtype=np.uint32).reshape(-1)
+        if li.size != batch:
+            raise B200TfheError("lut_idx must have one entry per ciphertext")
+    return luts, li
+
+
+def keyswitch_lwe_ciphertext(ksk, input_lwe, output_lwe=None):
+    """out = keyswitch(in).  in: [kN+1] or [B][kN+1]; returns / fills out: [n+1] or [B][n+1].  Bit-exact."""
+    p, ctx = ksk.params, ksk.ctx
+    a, single = _as_list(input_lwe, p.glwe_dimension * p.polynomial_size + 1, p.torus_bits, "keyswitch input")
+    out = np.empty((a.shape[0], p.lwe_dimension + 1), _dtype(p.torus_bits))
+    fn = getattr(ctx._lib, f"b200tfhe_keyswitch_batch_{_suf(p.torus_bits)}")
+    ctx.check(fn(ctx._h, ksk._h, _ptr(a), _ptr(out), a.shape[0]))
+    res = out[0] if single else out
+    if output_lwe is not None:
+        np.copyto(output_lwe, res)
+        return output_lwe
+    return res
+
+
+def programmable_bootstrap_lwe_ciphertext(input_lwe, accumulator, fourier_bsk, output_lwe=None, lut_idx=None):
+    """out = PBS(in, accumulator).  in: [n+1] or [B][n+1]; accumulator: GLWE [(k+1)N] or a list of them
+    selected per ciphertext by lut_idx; out: [kN+1] per ciphertext."""
+    p, ctx = fourier_bsk.params, fourier_bsk.ctx
+    a, single = _as_list(input_lwe, p.lwe_dimension + 1, p.torus_bits, "PBS input")
+    luts, li = _luts(accumulator, lut_idx, p, a.shape[0])
+    out = np.empty((a.shape[0], p.glwe_dimension * p.polynomial_size + 1), _dtype(p.torus_bits))
+    fn = getattr(ctx._lib, f"b200tfhe_pbs_batch_{_suf(p.torus_bits)}")
+    ctx.check(fn(ctx._h, fourier_bsk._h, _ptr(a), _ptr(out), _ptr(luts), luts.shape[0], _ptr(li), a.shape[0]))
+    res = out[0] if single else out
+    if output_lwe is not None:
+        np.copyto(output_lwe, res)
+        return output_lwe
+    return res
+
+
+def programmable_bootstrap_lwe_ciphertext_without_sample_extract(input_lwe, accumulator, fourier_bsk, lut_idx=None):
+    """Fork entry (lwe_programmable_bootstrapping.rs:1115-1162): returns the rotated GLWE [(k+1)N] per ciphertext."""
+    p, ctx = fourier_bsk.params, fourier_bsk.ctx
+    a, single = _as_list(input_lwe, p.lwe_dimension + 1, p.torus_bits, "blind-rotate input")
+    luts, li = _luts(accumulator, lut_idx, p, a.shape[0])
+    out = np.empty((a.shape[0], (p.glwe_dimension + 1) * p.polynomial_size), _dtype(p.torus_bits))
+    fn = getattr(ctx._lib, f"b200tfhe_blind_rotate_batch_{_suf(p.torus_bits)}")
+    ctx.check(fn(ctx._h, fourier_bsk._h, _ptr(a), _ptr(out), _ptr(luts), luts.shape[0], _ptr(li), a.shape[0]))
+    return out[0] if single else out
+
+
+def blind_rotate_assign(input_lwe, accumulator_glwe, fourier_bsk):
+    """acc <- blind rotation of acc by the (modulus-switched) input, in place (one accumulator per ciphertext)."""
+    p = fourier_bsk.params
+    glwe = (p.glwe_dimension + 1) * p.polynomial_size
+    acc = np.asarray(accumulator_glwe)
+    a, _ = _as_list(input_lwe, p.lwe_dimension + 1, p.torus_bits, "blind-rotate input")
+    luts = np.ascontiguousarray(acc, dtype=_dtype(p.torus_bits)).reshape(-1, glwe)
+    if luts.shape[0] != a.shape[0]:
+        raise B200TfheError("blind_rotate_assign needs one accumulator per ciphertext")
+    res = programmable_bootstrap_lwe_ciphertext_without_sample_extract(a, luts, fourier_bsk, np.arange(a.shape[0], dtype=np.uint32))
+    acc[...] = res.reshape(acc.shape)
+    return acc
+
+
+def keyswitch_programmable_bootstrap(ksk, fourier_bsk, input_lwe, accumulator, lut_idx=None):
+    """KS then PBS (shortint keyswitch_programmable_bootstrap_assign core, shortint/server_key/mod.rs:783-857)."""
+    p, ctx = fourier_bsk.params, fourier_bsk.ctx
+    w = p.glwe_dimension * p.polynomial_size + 1
+    a, single = _as_list(input_lwe, w, p.torus_bits, "KS+PBS input")
+    luts, li = _luts(accumulator, lut_idx, p, a.shape[0])
+    out = np.empty((a.shape[0], w), _dtype(p.torus_bits))
+    fn = getattr(ctx._lib, f"b200tfhe_ks_pbs_batch_{_suf(p.torus_bits)}")
+    ctx.check(fn(ctx._h, ksk._h, fourier_bsk._h, _ptr(a), _ptr(out), _ptr(luts), luts.shape[0], _ptr(li), a.shape[0]))
+    return out[0] if single else out
+
+
+def programmable_bootstrap_keyswitch(ksk, fourier_bsk, input_lwe, accumulator, lut_idx=None):
+    """PBS then KS (shortint :859-933; boolean bootstrap_keyswitch, boolean/engine/bootstrapping.rs:299-344)."""
+    p, ctx = fourier_bsk.params, fourier_bsk.ctx
+    w = p.lwe_dimension + 1
+    a, single = _as_list(input_lwe, w, p.torus_bits, "PBS+KS input")
+    luts, li = _luts(accumulator, lut_idx, p, a.shape[0])
+    out = np.empty((a.shape[0], w), _dtype(p.torus_bits))
+    fn = getattr(ctx._lib, f"b200tfhe_pbs_ks_batch_{_suf(p.torus_bits)}")
+    ctx.check(fn(ctx._h, ksk._h, fourier_bsk._h, _ptr(a), _ptr(out), _ptr(luts), luts.shape[0], _ptr(li), a.shape[0]))
+    return out[0] if single else out
+
+
+def fast_pbs_modulus_switch(ctx, scalars, polynomial_size, bits):
+    a = np.ascontiguousarray(scalars, dtype=_dtype(bits)).reshape(-1)
+    out = np.empty(a.size, np.uint32)
+    log2n = int(polynomial_size).bit_length() - 1
+    fn = getattr(ctx._lib, f"b200tfhe_modulus_switch_{_suf(bits)}")
+    ctx.check(fn(ctx._h, _ptr(a), _ptr(out), a.size, log2n))
+    return out
+
+
+def extract_lwe_sample_from_glwe_ciphertext(ctx, glwe, glwe_dimension, polynomial_size, bits):
+    """nth = MonomialDegree(0).  glwe: [(k+1)N] or [B][(k+1)N] -> [kN+1] per ciphertext.  Bit-exact."""
+    a, single = _as_list(glwe, (glwe_dimension + 1) * polynomial_size, bits, "sample-extract input")
+    out = np.empty((a.shape[0], glwe_dimension * polynomial_size + 1), _dtype(bits))
+    fn = getattr(ctx._lib, f"b200tfhe_sample_extract_batch_{_suf(bits)}")
+    ctx.check(fn(ctx._h, _ptr(a), _ptr(out), glwe_dimension, polynomial_size, a.shape[0]))
+    return out[0] if single else out

@@ -547,4 +547,40 @@ static int sample_extract_host(b200tfhe_context *ctx, const void *glwe, void *lw
 int b200tfhe_sample_extract_batch_u64(b200tfhe_context *ctx, const uint64_t *g, uint64_t *l, uint32_t k, uint32_t N, uint32_t b) { return sample_extract_host(ctx, g, l, k, N, b, 64); }
 int b200tfhe_sample_extract_batch_u32(b200tfhe_context *ctx, const uint32_t *g, uint32_t *l, uint32_t k, uint32_t N, uint32_t b) { return sample_extract_host(ctx, g, l, k, N, b, 32); }
 
+
+// Measures the sustained FP64 FMA rate of the device (TFLOP/s, 2 flop per FMA) with a register-only kernel:
+// the denominator of the blind rotation's FP64 roofline.  duration_ms: how long to run (>= 20).
+int b200tfhe_probe_fp64_tflops(b200tfhe_context *ctx, double duration_ms, double *tflops) {
+    REQUIRE(ctx && tflops, "probe: null argument");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    void *scratch;
+    CK(ctx->ws.get(Workspace::A, 64, &scratch));
+    int sms = 0;
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device));
+    const int grid = sms * 8, iters = 4096;
+    const double flop_per_launch = 2.0 * 64.0 * iters * 256.0 * grid;
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    for (int w = 0; w < 3; w++) dfma_probe_launch((double *)scratch, grid, iters, ctx->stream);
+    double best = 0.0, spent = 0.0;
+    while (spent < duration_ms) {
+        CK(cudaEventRecord(e0, ctx->stream));
+        for (int r = 0; r < 4; r++) dfma_probe_launch((double *)scratch, grid, iters, ctx->stream);
+        CK(cudaEventRecord(e1, ctx->stream));
+        CK(cudaEventSynchronize(e1));
+        float ms = 0;
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        ctx->launches += 4;
+        spent += ms;
+        double tf = 4.0 * flop_per_launch / (ms * 1e-3) / 1e12;
+        if (tf > best) best = tf;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *tflops = best;
+    return 0;
+}
+
 }  // extern "C"

@@ -38,6 +38,7 @@ int ks_colsum_launch(const void *ksk, void *colsum, int n_in, int n_out, int lev
 // misc_kernels.cu
 int modswitch_launch(const void *in, uint32_t *out, size_t count, int log2N, int bits, cudaStream_t st);
 int sample_extract_launch(const void *glwe, void *lwe, int k, int N, int batch, int bits, cudaStream_t st);
+int dfma_probe_launch(double *scratch, int grid, int iters, cudaStream_t st);
 int gate_prologue_launch(int gate, const uint32_t *a, const uint32_t *b, uint32_t *out, int len, int batch, cudaStream_t st);
 
 }  // namespace b200tfhe

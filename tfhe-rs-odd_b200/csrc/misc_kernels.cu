@@ -86,3 +86,23 @@ int gate_prologue_launch(int gate, const uint32_t *a, const uint32_t *b, uint32_
 }
 
 }  // namespace b200tfhe
+
+// ---- FP64 FMA peak probe: the roofline denominator for the blind rotation (MEASURED_PEAKS.json has no FP64 figure)
+namespace b200tfhe {
+__global__ void __launch_bounds__(256) dfma_probe_kernel(double *out, int iters, double a, double b) {
+    double x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            x0 = __fma_rn(x0, a, b); x1 = __fma_rn(x1, a, b); x2 = __fma_rn(x2, a, b); x3 = __fma_rn(x3, a, b);
+            x4 = __fma_rn(x4, a, b); x5 = __fma_rn(x5, a, b); x6 = __fma_rn(x6, a, b); x7 = __fma_rn(x7, a, b);
+        }
+    }
+    double s = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7;
+    if (s == 12345.678) out[0] = s;  // keep the chains alive
+}
+int dfma_probe_launch(double *scratch, int grid, int iters, cudaStream_t st) {
+    dfma_probe_kernel<<<grid, 256, 0, st>>>(scratch, iters, 0.999999, 1e-9);
+    return (int)cudaGetLastError();
+}
+}  // namespace b200tfhe
