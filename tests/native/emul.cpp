@@ -58,7 +58,7 @@ static void blind_rotate(const std::vector<cplx> &fbsk, int n, const uint64_t *l
             }
         const cplx *ggsw = &fbsk[(size_t)i * C::GGSW_CPLX];
         for (int j = 0; j < K1; j++)
-            for (int lane = 0; lane < R; lane++) C::mac(lane, j, ggsw, fbuf.data(), F[j][lane]);
+            for (int lane = 0; lane < R; lane++) { C::mac_prefetch(lane, j, ggsw, F[j][lane]); C::mac_finish(lane, j, ggsw, fbuf.data(), F[j][lane]); }
         for (int j = 0; j < K1; j++)
             for (int lane = 0; lane < R; lane++) C::inv_pass1(lane, F[j][lane], &fbuf[(size_t)j * L * C::REGION], tw.inv);
         for (int j = 0; j < K1; j++)
@@ -109,4 +109,18 @@ extern "C" int emul_fft_roundtrip(int N, const uint64_t *poly, uint64_t *out) {
         return 0;
     }
     return 1;
+}
+
+// closed-form single-level digit vs the generic recurrence (returns the number of mismatches)
+extern "C" int emul_check_single_level_digit(const uint64_t *xs, int count) {
+    int bad = 0;
+    for (int i = 0; i < count; i++) {
+        uint64_t st = decomp_init_state<uint64_t>(xs[i], 23, 1);
+        int32_t ref = (int32_t)decomp_next_digit<uint64_t>(st, 23);
+        if (BRCore<uint64_t, 32, 1, 1, 23>::single_level_digit(xs[i]) != ref) bad++;
+        uint64_t st2 = decomp_init_state<uint64_t>(xs[i], 18, 1);
+        int32_t ref2 = (int32_t)decomp_next_digit<uint64_t>(st2, 18);
+        if (BRCore<uint64_t, 16, 3, 1, 18>::single_level_digit(xs[i]) != ref2) bad++;
+    }
+    return bad;
 }

@@ -139,3 +139,14 @@ def test_kernel_single_cmux_matches_oracle_to_fft_precision(emul):
     out = np.zeros((1, o.glwe_len), np.uint64)
     assert emul.emul_blind_rotate(o.n, o.k, o.N, o.b, o.l, o.bits, _p(o.bsk), _p(ct), 1, _p(lut), _p(out)) == 0
     assert np.abs((out - ref).astype(np.int64)).max() < 2 ** 42      # 2^-22 of the torus
+
+
+def test_single_level_digit_closed_form(emul):
+    rng = np.random.default_rng(9)
+    xs = list(rng.integers(0, 2 ** 64, 20000, dtype=np.uint64))
+    for b in (23, 18):      # rounding and carry boundaries
+        for top in (0, 1, (1 << (b - 1)) - 1, 1 << (b - 1), (1 << (b - 1)) + 1, (1 << b) - 1):
+            for lo in (0, 1, (1 << (63 - b)) - 1, 1 << (63 - b), (1 << (63 - b)) + 1, (1 << (64 - b)) - 1):
+                xs.append(np.uint64(((top << (64 - b)) | lo) & (2 ** 64 - 1)))
+    xs = np.array(xs, dtype=np.uint64)
+    assert emul.emul_check_single_level_digit(_p(xs), xs.size) == 0

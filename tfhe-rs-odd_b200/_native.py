@@ -3,7 +3,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200tfhe.so")
+LIB_PATH = os.environ.get("B200TFHE_LIB") or os.path.join(_HERE, "libb200tfhe.so")  # env override: A/B builds of the kernels
 
 
 class Params(C.Structure):

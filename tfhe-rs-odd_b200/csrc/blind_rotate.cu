@@ -13,6 +13,10 @@
 #include "br_core.cuh"
 #include "kernels.h"
 
+#ifndef B200TFHE_REALIGN
+#define B200TFHE_REALIGN 1
+#endif
+
 namespace b200tfhe {
 
 template <typename T, int R, int K, int L, int BL, int CTS> struct BRConfig {
@@ -22,9 +26,10 @@ template <typename T, int R, int K, int L, int BL, int CTS> struct BRConfig {
     static_assert(THREADS % 32 == 0, "teams must fill whole warps");
     static constexpr size_t FBUF_BYTES = (size_t)K1 * L * C::REGION * sizeof(cplx);   // per ciphertext
     static constexpr size_t ACC_BYTES = (size_t)K1 * C::N * sizeof(T);
+    static constexpr size_t TW_BYTES = sizeof(TwTables<R>);   // both twiddle tables, staged once per CTA
     static size_t smem_bytes(int n) {
         size_t ahat = (((size_t)(n + 1) * sizeof(uint16_t)) + 15) & ~(size_t)15;
-        return CTS * (FBUF_BYTES + ACC_BYTES + ahat);
+        return CTS * (FBUF_BYTES + ACC_BYTES + ahat) + TW_BYTES;
     }
 };
 
@@ -37,6 +42,7 @@ blind_rotate_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const T *__
     typedef BRConfig<T, R, K, L, BL, CTS> CFG;
     typedef typename CFG::C C;
     constexpr int K1 = K + 1, N = C::N, REGION = C::REGION;
+    constexpr bool REALIGN = B200TFHE_REALIGN;
     extern __shared__ __align__(16) unsigned char smem_raw[];
 
     const int team = threadIdx.x / R, lane = threadIdx.x % R;
@@ -55,8 +61,15 @@ blind_rotate_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const T *__
     T *acc_r = acc_ct + (size_t)r * N;
     uint16_t *ahat = reinterpret_cast<uint16_t *>(reinterpret_cast<unsigned char *>(ahat_all) + ct_local * ahat_bytes);
 
-    const cplx(*twf)[R] = reinterpret_cast<const cplx(*)[R]>(tw_fwd_);
-    const cplx(*twi)[R] = reinterpret_cast<const cplx(*)[R]>(tw_inv_);
+    // twiddle tables: global -> shared once per CTA (short, fixed LDS latency instead of L1/L2 round trips)
+    cplx *tw_s = reinterpret_cast<cplx *>(smem_raw + CTS * (CFG::FBUF_BYTES + CFG::ACC_BYTES + ahat_bytes));
+    constexpr int TW_HALF = TwTables<R>::ENTRIES * R;
+    for (int e = threadIdx.x; e < TW_HALF; e += CFG::THREADS) {
+        tw_s[e] = tw_fwd_[e];
+        tw_s[TW_HALF + e] = tw_inv_[e];
+    }
+    const cplx(*twf)[R] = reinterpret_cast<const cplx(*)[R]>(tw_s);
+    const cplx(*twi)[R] = reinterpret_cast<const cplx(*)[R]>(tw_s + TW_HALF);
 
     // ---- prologue: modulus switch of the whole input LWE (fft_impl/common.rs:26-43) --------------------
     const T *lwe = lwe_in + (size_t)ct * lwe_stride;
@@ -70,11 +83,28 @@ blind_rotate_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const T *__
     }
     __syncwarp();
 
+    // ciphertext-wide barrier: only the K+1 teams of one ciphertext exchange data, so when they fill whole warps a
+    // named barrier per ciphertext lets the CTS ciphertexts of the CTA drift apart instead of waiting on each other
+    auto ct_barrier = [&]() {
+#if defined(__CUDA_ARCH__)
+        if constexpr (CTS > 1 && (K1 * R) % 32 == 0 && CTS <= 15) {
+            asm volatile("bar.sync %0, %1;" ::"r"(ct_local + 1), "n"(K1 * R) : "memory");
+        } else {
+            __syncthreads();
+        }
+#endif
+    };
+
     // ---- n CMUX iterations -----------------------------------------------------------------------------
     for (int i = 0; i < n; i++) {
+        if constexpr (CTS > 1 && REALIGN) __syncthreads();   // re-align the CTA's ciphertexts (instruction-cache sharing)
         const int a = ahat[i];
         C::digits_fwd_pass1(lane, acc_r, a, fbuf_r, twf);
         __syncwarp();
+        // bootstrap-key row 0 is fetched in parts across the second FFT pass and the barrier (L2 latency hiding)
+        const cplx *ggsw_i = bsk + (size_t)i * C::GGSW_CPLX;
+        cplx F[R];
+        C::template mac_prefetch_part<0>(lane, r, ggsw_i, F);
 #pragma unroll
         for (int t = 0; t < L; t++) {
             cplx x[R];
@@ -82,10 +112,10 @@ blind_rotate_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const T *__
             __syncwarp();
             C::fwd_pass2_store(lane, x, fbuf_r + t * REGION);
         }
-        __syncthreads();
-        cplx F[R];
-        C::mac(lane, r, bsk + (size_t)i * C::GGSW_CPLX, fbuf_ct, F);
-        __syncthreads();
+        if constexpr (R > C::CH) C::template mac_prefetch_part<1>(lane, r, ggsw_i, F);
+        ct_barrier();
+        C::mac_finish(lane, r, ggsw_i, fbuf_ct, F);
+        ct_barrier();
         C::inv_pass1(lane, F, fbuf_r, twi);
         __syncwarp();
         C::inv_pass2_accumulate(lane, fbuf_r, acc_r);
@@ -159,7 +189,7 @@ static int launch_br(const BRLaunch &a, cudaStream_t st) {
 }
 
 #define BR_INSTANCES(X)              \
-    X(uint64_t, 32, 1, 1, 23, 1)     \
+    X(uint64_t, 32, 1, 1, 23, 3)     \
     X(uint32_t, 16, 2, 3, 6, 2)      \
     X(uint64_t, 16, 3, 1, 18, 1)     \
     X(uint64_t, 16, 1, 2, 12, 1)

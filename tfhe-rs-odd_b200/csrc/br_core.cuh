@@ -20,8 +20,9 @@ namespace b200tfhe {
 
 // value of (P * X^a)[c] for a in [0, 2N): negacyclic rotation read
 template <typename T, int N> HD T rot_read(const T *poly, int c, int a) {
-    int s = c - a;
-    s += (s < 0) ? 2 * N : 0;
+    // s = c - a lies in (-2N, N); its low log2(2N) bits in two's complement are (c - a) mod 2N, so the index is
+    // s mod N and the sign flips when bit log2(N) of s is set (X^N = -1)
+    const int s = c - a;
     T v = poly[s & (N - 1)];
     return (s & N) ? (T)(0 - v) : v;
 }
@@ -33,6 +34,17 @@ template <typename T, int R, int K, int L, int BASE_LOG> struct BRCore {
     static constexpr int GGSW_CPLX = L * K1 * K1 * M;  // one Fourier GGSW, in cplx
     typedef typename TorusTraits<T>::Signed S;
 
+    // One-level decomposition in closed form (same values as decomp_init_state + decomp_next_digit, checked
+    // exhaustively around the rounding / carry boundaries by tests/test_host_cpu.py via the emulator): the state
+    // is the top BASE_LOG bits rounded to nearest, the digit is that state re-centred into (-B/2, B/2].
+    HD static int32_t single_level_digit(T x) {
+        constexpr int W = TorusTraits<T>::BITS;
+        constexpr uint32_t MASK = (1u << BASE_LOG) - 1, HALF = 1u << (BASE_LOG - 1);
+        const uint32_t top = (uint32_t)(x >> (W - BASE_LOG - 1));   // BASE_LOG + 1 bits (BASE_LOG <= 30)
+        const uint32_t res = ((top + 1) >> 1) & MASK;
+        return (int32_t)res - (int32_t)((res > HALF) ? (MASK + 1) : 0u);
+    }
+
     // Stage A1: for polynomial `acc_r`, rotation a (in [0,2N)): compute all L digit planes of
     // acc*X^a - acc at this lane's R folded points, run forward pass 1 for each level and leave the
     // transposed partial results in fbuf_r[t] (t = 0 is level L, the first one the recurrence emits).
@@ -43,11 +55,16 @@ template <typename T, int R, int K, int L, int BASE_LOG> struct BRCore {
             const int c = lane + R * m;
             T d0 = rot_read<T, N>(acc_r, c, a) - acc_r[c];
             T d1 = rot_read<T, N>(acc_r, c + M, a) - acc_r[c + M];
-            T s0 = decomp_init_state<T>(d0, BASE_LOG, L), s1 = decomp_init_state<T>(d1, BASE_LOG, L);
-            static_for<0, L>([&](auto t) {
-                dre[decltype(t)::value][decltype(p)::value] = (int32_t)decomp_next_digit<T>(s0, BASE_LOG);
-                dim[decltype(t)::value][decltype(p)::value] = (int32_t)decomp_next_digit<T>(s1, BASE_LOG);
-            });
+            if constexpr (L == 1) {
+                dre[0][decltype(p)::value] = single_level_digit(d0);
+                dim[0][decltype(p)::value] = single_level_digit(d1);
+            } else {
+                T s0 = decomp_init_state<T>(d0, BASE_LOG, L), s1 = decomp_init_state<T>(d1, BASE_LOG, L);
+                static_for<0, L>([&](auto t) {
+                    dre[decltype(t)::value][decltype(p)::value] = (int32_t)decomp_next_digit<T>(s0, BASE_LOG);
+                    dim[decltype(t)::value][decltype(p)::value] = (int32_t)decomp_next_digit<T>(s1, BASE_LOG);
+                });
+            }
         });
         static_for<0, L>([&](auto t) {
             cplx x[R];
@@ -67,28 +84,68 @@ template <typename T, int R, int K, int L, int BASE_LOG> struct BRCore {
         static_for<0, R>([&](auto p) { region[decltype(p)::value * R + lane] = x[decltype(p)::value]; });
     }
 
-    // Stage B1 (after a ciphertext-wide sync): Fourier multiply-accumulate for output polynomial j.
+    // Stage B1: Fourier multiply-accumulate for output polynomial j, in two calls so that the loads of the
+    // bootstrap key (L2 latency, the dominant stall of the first version of this kernel: profiles/r01_*) are in
+    // flight while the team waits at the ciphertext-wide barrier.
     // ggsw: this iteration's Fourier GGSW in device layout [lvl 0..L-1 = level 1..L][r][j][p][lane].
     // fbuf: the ciphertext's D buffers [r][t][...] with t = 0 <-> level L.
-    HD static void mac(int lane, int j, const cplx *ggsw, const cplx *fbuf, cplx (&F)[R]) {
-        static_for<0, R>([&](auto p) { F[decltype(p)::value] = cplx{0.0, 0.0}; });
-        for (int t = 0; t < L; t++) {          // level L down to 1, like ggsw.into_levels().rev()
-            const int lvl = L - 1 - t;
-            for (int r = 0; r < K1; r++) {
-                const cplx *g = ggsw + ((size_t)(lvl * K1 + r) * K1 + j) * M;
-                const cplx *d = fbuf + (size_t)(r * L + t) * REGION;
-                static_for<0, R>([&](auto pp) {
-                    // DIT wants register pp to hold position brev(pp)
-                    constexpr int pos = brev(decltype(pp)::value, FFT::LOGR);
-                    cplx gv = g[pos * R + lane], dv = d[pos * R + lane];
-                    cplx &f = F[decltype(pp)::value];
-                    f.re = fma_(gv.re, dv.re, f.re);
-                    f.re = fma_(-gv.im, dv.im, f.re);
-                    f.im = fma_(gv.re, dv.im, f.im);
-                    f.im = fma_(gv.im, dv.re, f.im);
-                });
-            }
-        }
+    // Rows are consumed in the reference's order (level L down to 1, r ascending: ggsw.rs:524-577).
+    static constexpr int NROWS = L * K1;
+    static constexpr int CH = 16;                 // positions per key chunk kept in registers
+    HD static const cplx *ggsw_row(const cplx *ggsw, int q, int j) {
+        const int t = q / K1, r = q % K1, lvl = L - 1 - t;
+        return ggsw + ((size_t)(lvl * K1 + r) * K1 + j) * M;
+    }
+    // (a) BEFORE the barrier: fetch key row 0 into F (register pp <-> position brev(pp), what the DIT wants), in
+    // R/CH parts so that the first part can be issued while the forward FFT's second pass still owns most registers
+    template <int PART> HD static void mac_prefetch_part(int lane, int j, const cplx *ggsw, cplx (&F)[R]) {
+        const cplx *g = ggsw_row(ggsw, 0, j);
+        static_for<PART * CH, PART * CH + CH>([&](auto pp) {
+            constexpr int pos = brev(decltype(pp)::value, FFT::LOGR);
+            F[decltype(pp)::value] = ldg_stream(g + pos * R + lane);
+        });
+    }
+    HD static void mac_prefetch(int lane, int j, const cplx *ggsw, cplx (&F)[R]) {
+        static_for<0, R / CH>([&](auto part) { mac_prefetch_part<decltype(part)::value>(lane, j, ggsw, F); });
+    }
+    // (b) AFTER the barrier: F = G_0 (.) D_0 in place, then F += G_q (.) D_q chunk by chunk; a chunk is CH
+    // positions of one key row, its loads are issued together (memory-level parallelism CH per thread) and the
+    // first one is issued before row 0 is consumed so that its latency overlaps that arithmetic.
+    static constexpr int HPR = R / CH;            // chunks per row
+    static constexpr int NCHUNK = NROWS * HPR;
+    template <int C_> HD static void load_chunk(int lane, int j, const cplx *ggsw, cplx (&h)[CH]) {
+        constexpr int q = C_ / HPR, half = C_ % HPR;
+        const cplx *g = ggsw_row(ggsw, q, j);
+        static_for<0, CH>([&](auto i) {
+            constexpr int pp = half * CH + decltype(i)::value;
+            h[decltype(i)::value] = ldg_stream(g + brev(pp, FFT::LOGR) * R + lane);
+        });
+    }
+    template <int C_> HD static void consume_chunk(int lane, const cplx *fbuf, cplx (&F)[R], const cplx (&h)[CH]) {
+        constexpr int q = C_ / HPR, half = C_ % HPR;
+        const cplx *d = fbuf + (size_t)((q % K1) * L + q / K1) * REGION;
+        static_for<0, CH>([&](auto i) {
+            constexpr int pp = half * CH + decltype(i)::value;
+            mac_one(F[pp], h[decltype(i)::value], d[brev(pp, FFT::LOGR) * R + lane]);
+        });
+    }
+    HD static void mac_finish(int lane, int j, const cplx *ggsw, const cplx *fbuf, cplx (&F)[R]) {
+        cplx h[CH];
+        if constexpr (NCHUNK > HPR) load_chunk<HPR>(lane, j, ggsw, h);
+        static_for<0, R>([&](auto pp) {   // row 0 = (t 0, r 0): first Fourier buffer of the ciphertext
+            constexpr int pos = brev(decltype(pp)::value, FFT::LOGR);
+            F[decltype(pp)::value] = cmul(F[decltype(pp)::value], fbuf[pos * R + lane]);
+        });
+        static_for<HPR, NCHUNK>([&](auto c) {
+            if constexpr (decltype(c)::value != HPR) load_chunk<decltype(c)::value>(lane, j, ggsw, h);
+            consume_chunk<decltype(c)::value>(lane, fbuf, F, h);
+        });
+    }
+    HD static void mac_one(cplx &f, cplx gv, cplx dv) {
+        f.re = fma_(gv.re, dv.re, f.re);
+        f.re = fma_(-gv.im, dv.im, f.re);
+        f.im = fma_(gv.re, dv.im, f.im);
+        f.im = fma_(gv.im, dv.re, f.im);
     }
 
     // Stage B2 (after a ciphertext-wide sync: every team finished reading D): inverse pass 1 into own region

@@ -72,6 +72,18 @@ template <int Q> HD cplx cmul_root(cplx x) {
     }
 }
 
+// streaming 16-byte load of read-only key data: non-coherent path, do not allocate in L1 (the Fourier key is
+// touched once per iteration per team; L1 is better spent on the twiddle tables)
+HD cplx ldg_stream(const cplx *p) {
+#if defined(__CUDA_ARCH__)
+    cplx v;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.f64 {%0, %1}, [%2];" : "=d"(v.re), "=d"(v.im) : "l"(p));
+    return v;
+#else
+    return *p;
+#endif
+}
+
 HD cplx cmul(cplx a, cplx b) { return cplx{fma_(-a.im, b.im, a.re * b.re), fma_(a.im, b.re, a.re * b.im)}; }
 
 // DIT butterfly (a, b) <- (a + W b, a - W b), W = e^{2 pi i Q/128}.  General twiddles use the
