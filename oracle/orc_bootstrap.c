@@ -44,15 +44,33 @@ void orc_bsk_to_fourier(const orc_params *p, const uint64_t *bsk, double *fbsk, 
     orc_parallel_for(conv_one, &c, polys, nthreads);
 }
 
-/* fft64/crypto/ggsw.rs:477-598.  ggsw_f: [level 1..l][row][col][M] c64 (levels stored 1->l, consumed l->1). */
+void orc_fourier_mac(int M, double *o, const double *g, const double *d);
+
+/* per-thread scratch (the reference's PodStack / ComputationBuffers, computation_buffers.rs:8-29) */
+typedef struct { size_t cap; uint64_t *states, *digits, *tmp; double *fourier, *outf; } scratch_t;
+static __thread scratch_t g_scr;
+static scratch_t *get_scratch(size_t tot, int N) {
+    if (g_scr.cap < tot) {
+        free(g_scr.states); free(g_scr.digits); free(g_scr.tmp); free(g_scr.fourier); free(g_scr.outf);
+        g_scr.states = (uint64_t *)aligned_alloc(64, sizeof(uint64_t) * tot);
+        g_scr.tmp = (uint64_t *)aligned_alloc(64, sizeof(uint64_t) * tot);
+        g_scr.digits = (uint64_t *)aligned_alloc(64, sizeof(uint64_t) * N);
+        g_scr.fourier = (double *)aligned_alloc(64, sizeof(double) * N);
+        g_scr.outf = (double *)aligned_alloc(64, sizeof(double) * tot);
+        g_scr.cap = tot;
+    }
+    return &g_scr;
+}
+
+/* fft64/crypto/ggsw.rs:477-598.  ggsw_f: [level 1..l][row][col][N doubles: re | im] (levels stored 1->l, consumed l->1). */
 void orc_add_external_product(const orc_params *p, uint64_t *acc, const double *ggsw_f, const uint64_t *glwe) {
     int N = p->N, M = N / 2, k1 = p->k + 1, L = p->pbs_level, b = p->pbs_base_log, bits = p->bits;
     uint64_t m = maskw(bits), mb = (1ULL << b) - 1;
     size_t tot = (size_t)k1 * N;
-    uint64_t *states = (uint64_t *)malloc(sizeof(uint64_t) * tot);
-    uint64_t *digits = (uint64_t *)malloc(sizeof(uint64_t) * N);
-    double *fourier = (double *)malloc(sizeof(double) * N);
-    double *outf = (double *)calloc((size_t)k1 * N, sizeof(double));
+    scratch_t *sc = get_scratch(tot, N);
+    uint64_t *states = sc->states, *digits = sc->digits;
+    double *fourier = sc->fourier, *outf = sc->outf;
+    memset(outf, 0, sizeof(double) * tot);
     int shift = bits - b * L;
     for (size_t t = 0; t < tot; t++) states[t] = orc_closest_representable(glwe[t], b, L, bits) >> shift;
     for (int lvl = L; lvl >= 1; lvl--) {
@@ -71,19 +89,10 @@ void orc_add_external_product(const orc_params *p, uint64_t *acc, const double *
             orc_fft_forward_integer(N, digits, bits, fourier);
             /* update_with_fmadd: ggsw.rs:616-697 */
             const double *row = mat + (size_t)r * k1 * N;
-            for (int j = 0; j < k1; j++) {
-                const double *g = row + (size_t)j * N;
-                double *o = outf + (size_t)j * N;
-                for (int f = 0; f < M; f++) {
-                    double gr = g[2 * f], gi = g[2 * f + 1], dr = fourier[2 * f], di = fourier[2 * f + 1];
-                    o[2 * f] += gr * dr - gi * di;
-                    o[2 * f + 1] += gr * di + gi * dr;
-                }
-            }
+            for (int j = 0; j < k1; j++) orc_fourier_mac(M, outf + (size_t)j * N, row + (size_t)j * N, fourier);
         }
     }
     for (int j = 0; j < k1; j++) orc_fft_add_backward_torus(N, acc + (size_t)j * N, bits, outf + (size_t)j * N);
-    free(states); free(digits); free(fourier); free(outf);
 }
 
 /* fft64/crypto/bootstrap.rs:243-344 */
@@ -91,7 +100,7 @@ void orc_blind_rotate(const orc_params *p, const double *fbsk, const uint64_t *l
     int N = p->N, k1 = p->k + 1, n = p->n, bits = p->bits;
     int log2N = 0; while ((1 << log2N) < N) log2N++;
     size_t tot = (size_t)k1 * N;
-    uint64_t *tmp = (uint64_t *)malloc(sizeof(uint64_t) * tot);
+    uint64_t *tmp = get_scratch(tot, N)->tmp;
     uint64_t bhat = orc_modswitch(lwe[n], log2N, bits);
     memcpy(tmp, acc, sizeof(uint64_t) * tot);
     for (int j = 0; j < k1; j++) orc_monomial_div(acc + (size_t)j * N, tmp + (size_t)j * N, N, bhat, bits);
@@ -102,7 +111,6 @@ void orc_blind_rotate(const orc_params *p, const double *fbsk, const uint64_t *l
         for (int j = 0; j < k1; j++) orc_monomial_mul_sub(tmp + (size_t)j * N, acc + (size_t)j * N, N, ahat, bits);
         orc_add_external_product(p, acc, fbsk + (size_t)i * ggsw_sz, tmp);
     }
-    free(tmp);
 }
 
 /* bootstrap.rs:346-380 */

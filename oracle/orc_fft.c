@@ -11,7 +11,11 @@
 #include <string.h>
 #include <pthread.h>
 
-typedef struct { int N; double *twist; double *w; } plan_t; /* twist[2M], w[2*(M/2)] = exp(-2 pi i t / M) */
+/* Fourier buffers are structure-of-arrays: M real parts followed by M imaginary parts (N doubles per polynomial), so
+ * that gcc vectorises the butterfly and pointwise loops (the reference gets its speed from pulp/AVX-512 intrinsics). */
+typedef struct { int N; double *twr, *twi;   /* twist e^{i pi j/N}, j < M */
+                 double *wr, *wi;            /* per-stage twiddles, stage `len` at offset len/2: exp(-2 pi i q/len), q < len/2 */
+               } plan_t;
 static plan_t g_plans[32];
 static pthread_mutex_t g_lock = PTHREAD_MUTEX_INITIALIZER;
 
@@ -22,18 +26,20 @@ static const plan_t *get_plan(int N) {
     pthread_mutex_lock(&g_lock);
     if (p->N != N) {
         int M = N / 2;
-        double *tw = (double *)malloc(sizeof(double) * 2 * M);
-        double *w = (double *)malloc(sizeof(double) * 2 * (M / 2 > 0 ? M / 2 : 1));
+        double *twr = (double *)aligned_alloc(64, sizeof(double) * (M + 8)), *twi = (double *)aligned_alloc(64, sizeof(double) * (M + 8));
+        double *wr = (double *)aligned_alloc(64, sizeof(double) * (M + 8)), *wi = (double *)aligned_alloc(64, sizeof(double) * (M + 8));
         const long double PI = 3.14159265358979323846264338327950288L;
         for (int j = 0; j < M; j++) {
             long double a = PI * (long double)j / (long double)N;
-            tw[2 * j] = (double)cosl(a); tw[2 * j + 1] = (double)sinl(a);
+            twr[j] = (double)cosl(a); twi[j] = (double)sinl(a);
         }
-        for (int t = 0; t < M / 2; t++) {
-            long double a = -2.0L * PI * (long double)t / (long double)M;
-            w[2 * t] = (double)cosl(a); w[2 * t + 1] = (double)sinl(a);
-        }
-        p->twist = tw; p->w = w;
+        wr[0] = 1.0; wi[0] = 0.0;
+        for (int len = 2; len <= M; len <<= 1)
+            for (int q = 0; q < len / 2; q++) {
+                long double a = -2.0L * PI * (long double)q / (long double)len;
+                wr[len / 2 + q] = (double)cosl(a); wi[len / 2 + q] = (double)sinl(a);
+            }
+        p->twr = twr; p->twi = twi; p->wr = wr; p->wi = wi;
         __atomic_store_n(&p->N, N, __ATOMIC_RELEASE);
     }
     pthread_mutex_unlock(&g_lock);
@@ -41,33 +47,34 @@ static const plan_t *get_plan(int N) {
 }
 
 /* in-place DIF radix-2, natural in -> bit-reversed out, kernel exp(-2 pi i jk/M) */
-static void fft_dif(double *x, int M, const double *w) {
+static void fft_dif(double *restrict xr, double *restrict xi, int M, const plan_t *p) {
     for (int len = M; len >= 2; len >>= 1) {
-        int half = len >> 1, step = M / len;
+        int half = len >> 1;
+        const double *restrict wr = p->wr + half, *restrict wi = p->wi + half;
         for (int b = 0; b < M; b += len) {
+            double *restrict ur = xr + b, *restrict ui = xi + b, *restrict vr = xr + b + half, *restrict vi = xi + b + half;
             for (int q = 0; q < half; q++) {
-                double *u = x + 2 * (b + q), *v = x + 2 * (b + q + half);
-                double ar = u[0], ai = u[1], br = v[0], bi = v[1];
-                double wr = w[2 * q * step], wi = w[2 * q * step + 1];
+                double ar = ur[q], ai = ui[q], br = vr[q], bi = vi[q];
                 double dr = ar - br, di = ai - bi;
-                u[0] = ar + br; u[1] = ai + bi;
-                v[0] = dr * wr - di * wi; v[1] = dr * wi + di * wr;
+                ur[q] = ar + br; ui[q] = ai + bi;
+                vr[q] = dr * wr[q] - di * wi[q]; vi[q] = dr * wi[q] + di * wr[q];
             }
         }
     }
 }
 /* in-place DIT radix-2 inverse (unnormalised), bit-reversed in -> natural out, kernel exp(+2 pi i jk/M) */
-static void fft_dit_inv(double *x, int M, const double *w) {
+static void fft_dit_inv(double *restrict xr, double *restrict xi, int M, const plan_t *p) {
     for (int len = 2; len <= M; len <<= 1) {
-        int half = len >> 1, step = M / len;
+        int half = len >> 1;
+        const double *restrict wr = p->wr + half, *restrict wi = p->wi + half;
         for (int b = 0; b < M; b += len) {
+            double *restrict ur = xr + b, *restrict ui = xi + b, *restrict vr = xr + b + half, *restrict vi = xi + b + half;
             for (int q = 0; q < half; q++) {
-                double *u = x + 2 * (b + q), *v = x + 2 * (b + q + half);
-                double wr = w[2 * q * step], wi = -w[2 * q * step + 1];
-                double br = v[0] * wr - v[1] * wi, bi = v[0] * wi + v[1] * wr;
-                double ar = u[0], ai = u[1];
-                u[0] = ar + br; u[1] = ai + bi;
-                v[0] = ar - br; v[1] = ai - bi;
+                double cr = wr[q], ci = -wi[q];
+                double br = vr[q] * cr - vi[q] * ci, bi = vr[q] * ci + vi[q] * cr;
+                double ar = ur[q], ai = ui[q];
+                ur[q] = ar + br; ui[q] = ai + bi;
+                vr[q] = ar - br; vi[q] = ai - bi;
             }
         }
     }
@@ -83,13 +90,13 @@ static inline double to_signed_f64(uint64_t v, int bits) {
 void orc_fft_forward_integer(int N, const uint64_t *poly, int bits, double *out) {
     const plan_t *p = get_plan(N);
     int M = N / 2;
+    double *restrict xr = out, *restrict xi = out + M;
     for (int j = 0; j < M; j++) {
         double re = to_signed_f64(poly[j], bits), im = to_signed_f64(poly[j + M], bits);
-        double wr = p->twist[2 * j], wi = p->twist[2 * j + 1];
-        out[2 * j] = re * wr - im * wi;
-        out[2 * j + 1] = re * wi + im * wr;
+        xr[j] = re * p->twr[j] - im * p->twi[j];
+        xi[j] = re * p->twi[j] + im * p->twr[j];
     }
-    fft_dif(out, M, p->w);
+    fft_dif(xr, xi, M, p);
 }
 
 /* fft/mod.rs:197-218 (convert_forward_torus: normalisation 2^-BITS) */
@@ -97,20 +104,22 @@ void orc_fft_forward_torus(int N, const uint64_t *poly, int bits, double *out) {
     const plan_t *p = get_plan(N);
     int M = N / 2;
     double norm = ldexp(1.0, -bits);
+    double *restrict xr = out, *restrict xi = out + M;
     for (int j = 0; j < M; j++) {
         double re = to_signed_f64(poly[j], bits) * norm, im = to_signed_f64(poly[j + M], bits) * norm;
-        double wr = p->twist[2 * j], wi = p->twist[2 * j + 1];
-        out[2 * j] = re * wr - im * wi;
-        out[2 * j + 1] = re * wi + im * wr;
+        xr[j] = re * p->twr[j] - im * p->twi[j];
+        xi[j] = re * p->twi[j] + im * p->twr[j];
     }
-    fft_dif(out, M, p->w);
+    fft_dif(xr, xi, M, p);
 }
 
 /* commons/math/torus/mod.rs:72-78 from_torus, followed by the signed cast of fft/mod.rs:285-304 */
 static inline uint64_t from_torus(double t, int bits) {
-    double fr = t - round(t);
+    /* rint (nearest-even) like the reference's AVX2/AVX-512 paths (fft/x86.rs:637-645); the scalar path's
+     * round-half-away (torus/mod.rs:72-78) differs only on exact ties, which have measure zero */
+    double fr = t - rint(t);
     fr *= ldexp(1.0, bits);
-    fr = round(fr);
+    fr = rint(fr);
     /* Rust `as i64` saturates; only reachable at the measure-zero tie fr == 2^63 */
     if (fr >= 9223372036854775807.0) return (uint64_t)INT64_MAX;
     if (fr <= -9223372036854775808.0) return (uint64_t)INT64_MIN;
@@ -122,14 +131,25 @@ void orc_fft_add_backward_torus(int N, uint64_t *poly, int bits, double *f) {
     const plan_t *p = get_plan(N);
     int M = N / 2;
     uint64_t m = bits == 64 ? ~0ULL : ((1ULL << bits) - 1);
-    fft_dit_inv(f, M, p->w);
+    double *restrict xr = f, *restrict xi = f + M;
+    fft_dit_inv(xr, xi, M, p);
     double inv = 1.0 / (double)M;
     for (int j = 0; j < M; j++) {
-        double wr = p->twist[2 * j], wi = -p->twist[2 * j + 1];
-        double re = (f[2 * j] * wr - f[2 * j + 1] * wi) * inv;
-        double im = (f[2 * j] * wi + f[2 * j + 1] * wr) * inv;
+        double wr = p->twr[j], wi = -p->twi[j];
+        double re = (xr[j] * wr - xi[j] * wi) * inv;
+        double im = (xr[j] * wi + xi[j] * wr) * inv;
         poly[j] = (poly[j] + from_torus(re, bits)) & m;
         poly[j + M] = (poly[j + M] + from_torus(im, bits)) & m;
+    }
+}
+
+/* pointwise complex multiply-accumulate o += g * d on structure-of-arrays Fourier polynomials (update_with_fmadd) */
+void orc_fourier_mac(int M, double *restrict o, const double *restrict g, const double *restrict d) {
+    double *restrict or_ = o, *restrict oi = o + M;
+    const double *restrict gr = g, *restrict gi = g + M, *restrict dr = d, *restrict di = d + M;
+    for (int f = 0; f < M; f++) {
+        or_[f] += gr[f] * dr[f] - gi[f] * di[f];
+        oi[f] += gr[f] * di[f] + gi[f] * dr[f];
     }
 }
 
@@ -160,16 +180,16 @@ void orc_negacyclic_mul_binary(int N, const uint64_t *a, const uint64_t *s, uint
         for (int j = 0; j < N; j++) limb[j] = (a[j] >> sh) & 0xFFFF;
         orc_fft_forward_integer(N, limb, 64, fa);
         for (int j = 0; j < M; j++) {
-            double r = fa[2 * j] * fs[2 * j] - fa[2 * j + 1] * fs[2 * j + 1];
-            double i = fa[2 * j] * fs[2 * j + 1] + fa[2 * j + 1] * fs[2 * j];
-            fa[2 * j] = r; fa[2 * j + 1] = i;
+            double r = fa[j] * fs[j] - fa[M + j] * fs[M + j];
+            double i = fa[j] * fs[M + j] + fa[M + j] * fs[j];
+            fa[j] = r; fa[M + j] = i;
         }
-        fft_dit_inv(fa, M, p->w);
+        fft_dit_inv(fa, fa + M, M, p);
         double inv = 1.0 / (double)M;
         for (int j = 0; j < M; j++) {
-            double wr = p->twist[2 * j], wi = -p->twist[2 * j + 1];
-            double re = (fa[2 * j] * wr - fa[2 * j + 1] * wi) * inv;
-            double im = (fa[2 * j] * wi + fa[2 * j + 1] * wr) * inv;
+            double wr = p->twr[j], wi = -p->twi[j];
+            double re = (fa[j] * wr - fa[M + j] * wi) * inv;
+            double im = (fa[j] * wi + fa[M + j] * wr) * inv;
             out[j] += (uint64_t)(int64_t)llround(re) << sh;
             out[j + M] += (uint64_t)(int64_t)llround(im) << sh;
         }

@@ -68,8 +68,10 @@ def test_fft_product_vs_schoolbook(N):
     fa, fb = np.zeros(N), np.zeros(N)
     lib().orc_fft_forward_torus(N, _p(a), 64, _p(fa))
     lib().orc_fft_forward_integer(N, _p(b), 64, _p(fb))
-    ca, cb = fa.view(np.complex128), fb.view(np.complex128)
-    prod = np.ascontiguousarray((ca * cb).view(np.float64))
+    M = N // 2      # oracle Fourier buffers are structure-of-arrays: M real parts then M imaginary parts
+    ca, cb = fa[:M] + 1j * fa[M:], fb[:M] + 1j * fb[M:]
+    pr = ca * cb
+    prod = np.ascontiguousarray(np.concatenate([pr.real, pr.imag]))
     out = np.zeros(N, np.uint64)
     lib().orc_fft_add_backward_torus(N, _p(out), 64, _p(prod))
     thr = 1 << (64 - (52 - 16 - (N.bit_length() - 1)))
