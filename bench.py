@@ -154,6 +154,9 @@ def main():
     if args.impl == "reference":
         return run_reference(args, rank, world)
     args.warmup = max(args.warmup, 3)
+    # libraries (NCCL's version banner, torchrun notices) write to fd 1: keep stdout for the ONE JSON line
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
 
     import numpy as np
     import torch
@@ -293,7 +296,8 @@ def main():
     }
     if not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_port_throughput(seconds_target=12.0)
-    print(json.dumps(out))
+    real_stdout.write(json.dumps(out) + "\n")
+    real_stdout.flush()
     if world > 1:
         dist.destroy_process_group()
 
