@@ -30,6 +30,7 @@ PARAMS = {
     "TOY_U64": (16, 1, 512, 12, 2, 4, 4, 64, 1e-9, 1e-15, 4, "ks_pbs"),
     "TOY_U32": (20, 2, 512, 6, 3, 3, 4, 32, 1e-7, 1e-8, 0, "pbs_ks"),
     "TOY_2_2": (12, 1, 2048, 23, 1, 3, 5, 64, 1e-9, 0.00000000000000029403601535432533, 16, "ks_pbs"),
+    "TOY_3_3": (6, 1, 8192, 15, 2, 3, 6, 64, 1e-9, 0.0000000000000000002168404344971009, 64, "ks_pbs"),
     "TOY_1_1": (12, 3, 512, 18, 1, 4, 3, 64, 1e-9, 0.0000000000034525330484572114, 4, "ks_pbs"),
 }
 

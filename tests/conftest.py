@@ -43,7 +43,8 @@ def phase_bound(o):
     product; from the first CMUX where that flips a rounding decision of the signed decomposition the two
     accumulators are different (equally valid) ciphertexts and every later rounding is independent.  The phase
     difference is then the difference of two independent draws of the decomposition-rounding noise, whose
-    variance per PBS is  (n/2) * (1 + kN/2) * 2^(-2 b l) / 12 .  We allow 8 sigma of the difference.
+    variance per PBS is at most  n * (1 + kN/2) * 2^(-2 b l) / 12  (n/2 for a balanced key).  We allow 8 sigma of the difference.
     """
-    var = (o.n / 2.0) * (1.0 + o.k * o.N / 2.0) * 2.0 ** (-2 * o.b * o.l) / 12.0
+    # n (not n/2): upper bound over the secret key's Hamming weight, which matters for the toy sets with n ~ 10
+    var = o.n * (1.0 + o.k * o.N / 2.0) * 2.0 ** (-2 * o.b * o.l) / 12.0
     return 8.0 * (2.0 * var) ** 0.5

@@ -124,3 +124,73 @@ extern "C" int emul_check_single_level_digit(const uint64_t *xs, int count) {
     }
     return bad;
 }
+
+// ---- N = 8192 (one 256-thread CTA per ciphertext): same stage sequence as blind_rotate_big.cu ----------------------
+#include "br_big.cuh"
+template <typename T, int K, int L, int BL>
+static int run_big(const uint64_t *bsk_std, int n, const uint64_t *lwe, int batch, const uint64_t *lut, uint64_t *out) {
+    typedef BigCore<T, K, L, BL> C;
+    constexpr int K1 = K + 1, N = C::N, M = C::M, P = C::P, TH = 256;
+    static BigTables tb; fill_big_tables(tb);
+    std::vector<cplx> S1(M);
+    static cplx x[TH][P];
+    static cplx F[K1][TH][P];
+    // key conversion
+    size_t npoly = (size_t)n * L * K1 * K1;
+    std::vector<cplx> fbsk(npoly * M);
+    std::vector<T> poly(N);
+    auto forward = [&]() {
+        for (int t = 0; t < TH; t++) C::fwdA(t, x[t], S1.data(), &tb);
+        for (int t = 0; t < TH; t++) C::fwdB_load(t, x[t], S1.data());
+        for (int t = 0; t < TH; t++) C::fwdB_pass1(t, x[t], S1.data(), &tb);
+        for (int t = 0; t < TH; t++) C::fwdB_pass2(t, x[t], S1.data());
+    };
+    for (size_t pi = 0; pi < npoly; pi++) {
+        for (int c = 0; c < N; c++) poly[c] = (T)bsk_std[pi * N + c];
+        for (int t = 0; t < TH; t++) C::key_input(t, poly.data(), x[t]);
+        forward();
+        for (int t = 0; t < TH; t++) for (int p = 0; p < P; p++) fbsk[pi * M + p * TH + t] = x[t][p];
+    }
+    std::vector<T> acc((size_t)K1 * N), lutT((size_t)K1 * N);
+    for (size_t c = 0; c < lutT.size(); c++) lutT[c] = (T)lut[c];
+    for (int b = 0; b < batch; b++) {
+        const uint64_t *ct = lwe + (size_t)b * (n + 1);
+        int bhat = (int)(modswitch<T>((T)ct[n], C::LOGN) & (2 * N - 1));
+        int a0 = (2 * N - bhat) & (2 * N - 1);
+        for (int r = 0; r < K1; r++)
+            for (int c = 0; c < N; c++) acc[(size_t)r * N + c] = rot_read<T, N>(&lutT[(size_t)r * N], c, a0);
+        for (int i = 0; i < n; i++) {
+            int a = (int)(modswitch<T>((T)ct[i], C::LOGN) & (2 * N - 1));
+            const cplx *ggsw = &fbsk[(size_t)i * C::GGSW_CPLX];
+            for (int j = 0; j < K1; j++) for (int t = 0; t < TH; t++) for (int p = 0; p < P; p++) F[j][t][p] = cplx{0, 0};
+            static_for<0, L>([&](auto tl) {
+                for (int r = 0; r < K1; r++) {
+                    for (int t = 0; t < TH; t++) C::template digits<decltype(tl)::value>(t, &acc[(size_t)r * N], a, x[t]);
+                    forward();
+                    for (int t = 0; t < TH; t++) {
+                        cplx Ft[K1][P];
+                        for (int j = 0; j < K1; j++) for (int p = 0; p < P; p++) Ft[j][p] = F[j][t][p];
+                        C::mac(t, L - 1 - decltype(tl)::value, r, ggsw, x[t], Ft);
+                        for (int j = 0; j < K1; j++) for (int p = 0; p < P; p++) F[j][t][p] = Ft[j][p];
+                    }
+                }
+            });
+            for (int j = 0; j < K1; j++) {
+                for (int t = 0; t < TH; t++) for (int pp = 0; pp < P; pp++) x[t][pp] = F[j][t][brev(pp, C::LOGP)];
+                for (int t = 0; t < TH; t++) C::invA(t, x[t], S1.data(), &tb);
+                for (int t = 0; t < TH; t++) C::invB_load(t, x[t], S1.data());
+                for (int t = 0; t < TH; t++) C::invB_store(t, x[t], S1.data());
+                for (int t = 0; t < TH; t++) { C::invC(t, x[t], S1.data(), &tb); C::accumulate(t, x[t], &acc[(size_t)j * N]); }
+            }
+        }
+        for (size_t c = 0; c < acc.size(); c++) out[(size_t)b * K1 * N + c] = (uint64_t)acc[c];
+    }
+    return 0;
+}
+
+extern "C" int emul_blind_rotate_big(int n, int k, int N, int base_log, int level, int bits, const uint64_t *bsk_std,
+                                     const uint64_t *lwe, int batch, const uint64_t *lut, uint64_t *out_glwe) {
+    if (bits == 64 && N == 8192 && k == 1 && level == 2 && base_log == 15)
+        return run_big<uint64_t, 1, 2, 15>(bsk_std, n, lwe, batch, lut, out_glwe);
+    return 1;
+}

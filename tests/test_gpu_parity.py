@@ -30,7 +30,7 @@ def _sdiff(a, b, bits):
     return d.astype(np.int64)
 
 
-@pytest.mark.parametrize("name", ["TOY_U64", "TOY_U32", "TOY_2_2", "TOY_1_1", "MESSAGE_2_CARRY_2", "BOOLEAN_DEFAULT"])
+@pytest.mark.parametrize("name", ["TOY_U64", "TOY_U32", "TOY_2_2", "TOY_1_1", "TOY_3_3", "MESSAGE_2_CARRY_2", "BOOLEAN_DEFAULT"])
 def test_keyswitch_bit_exact(ctx, name):
     import tfhe_rs_odd_b200 as t
     o = get_oracle(name)
@@ -92,7 +92,8 @@ def _pbs_case(ctx, name, B, seed=11):
     return o, p, bsk, ksk, msgs, pts, luts, idx, expect
 
 
-@pytest.mark.parametrize("name,B", [("TOY_U64", 9), ("TOY_U32", 10), ("TOY_2_2", 7), ("TOY_1_1", 5),
+@pytest.mark.parametrize("name,B", [("TOY_U64", 9), ("TOY_U32", 10), ("TOY_2_2", 7), ("TOY_1_1", 5), ("TOY_3_3", 5),
+                                    ("MESSAGE_3_CARRY_3", 6),
                                     ("MESSAGE_2_CARRY_2", 48), ("MESSAGE_1_CARRY_1", 16), ("BOOLEAN_DEFAULT", 33)])
 def test_pbs_decrypts_like_oracle(ctx, name, B):
     import tfhe_rs_odd_b200 as t
@@ -114,7 +115,7 @@ def test_pbs_decrypts_like_oracle(ctx, name, B):
     assert d.max() < phase_bound(o), (d.max(), phase_bound(o))
 
 
-@pytest.mark.parametrize("name,B", [("TOY_U64", 6), ("TOY_2_2", 5), ("MESSAGE_2_CARRY_2", 40)])
+@pytest.mark.parametrize("name,B", [("TOY_U64", 6), ("TOY_2_2", 5), ("TOY_3_3", 4), ("MESSAGE_2_CARRY_2", 40)])
 def test_ks_pbs_like_oracle(ctx, name, B):
     import tfhe_rs_odd_b200 as t
     o, p, bsk, ksk, msgs, pts, luts, idx, expect = _pbs_case(ctx, name, B, seed=5)

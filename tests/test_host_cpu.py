@@ -150,3 +150,24 @@ def test_single_level_digit_closed_form(emul):
                 xs.append(np.uint64(((top << (64 - b)) | lo) & (2 ** 64 - 1)))
     xs = np.array(xs, dtype=np.uint64)
     assert emul.emul_check_single_level_digit(_p(xs), xs.size) == 0
+
+
+def test_big_kernel_stages_on_cpu_match_oracle(emul):
+    # N = 8192 (PARAM_MESSAGE_3_CARRY_3 shape, tiny n): the 256-thread stage sequence of blind_rotate_big.cu on the CPU
+    o = get_oracle("TOY_3_3")
+    msgs = np.array([1, 17, 40])
+    cts = o.encrypt(o.encode(msgs), "small")
+    lut = o.lut(lambda x: (x + 5) % o.pmod)
+    ref = o.pbs(cts, lut, sample_extract=False)
+    out = np.zeros((3, o.glwe_len), np.uint64)
+    assert emul.emul_blind_rotate_big(o.n, o.k, o.N, o.b, o.l, o.bits, _p(o.bsk), _p(cts), 3, _p(lut), _p(out)) == 0
+    ph = np.array([o.glwe_phase(g)[0] for g in out]); ph_ref = np.array([o.glwe_phase(g)[0] for g in ref])
+    assert np.array_equal(o.decode(ph) % o.pmod, (msgs + 5) % o.pmod)
+    assert np.array_equal(o.decode(ph), o.decode(ph_ref))
+    assert np.abs((ph - ph_ref).astype(np.int64)).max() / 2.0 ** 64 < phase_bound(o)
+    ct = np.zeros((1, o.n + 1), np.uint64)
+    ct[0, 2] = np.uint64(0x1234567890ABCDEF); ct[0, o.n] = np.uint64(0x0234567890ABCDEF)
+    ref = o.pbs(ct, lut, sample_extract=False)
+    out = np.zeros((1, o.glwe_len), np.uint64)
+    emul.emul_blind_rotate_big(o.n, o.k, o.N, o.b, o.l, o.bits, _p(o.bsk), _p(ct), 1, _p(lut), _p(out))
+    assert np.abs((out - ref).astype(np.int64)).max() < 2 ** 36       # one CMUX: f64 FFT precision only

@@ -46,6 +46,7 @@ struct b200tfhe_context {
     std::mutex mu;
     std::string err;
     void *tw16 = nullptr, *tw32 = nullptr;  // TwTables<R> on the device
+    void *twbig = nullptr;                  // BigTables (N = 8192)
     Workspace ws;
     uint64_t launches = 0;
 };
@@ -94,9 +95,11 @@ static size_t small_len(const Params &p) { return (size_t)p.n + 1; }
 static size_t glwe_len(const Params &p) { return (size_t)(p.k + 1) * p.N; }
 
 static const void *tw_fwd(const b200tfhe_context *ctx, int R) {
+    if (R == 256) return ctx->twbig;
     return R == 32 ? (const void *)((TwTables<32> *)ctx->tw32)->fwd : (const void *)((TwTables<16> *)ctx->tw16)->fwd;
 }
 static const void *tw_inv(const b200tfhe_context *ctx, int R) {
+    if (R == 256) return ctx->twbig;
     return R == 32 ? (const void *)((TwTables<32> *)ctx->tw32)->inv : (const void *)((TwTables<16> *)ctx->tw16)->inv;
 }
 
@@ -126,9 +129,12 @@ int b200tfhe_context_create(int device, b200tfhe_context **out) {
     {
         static TwTables<16> t16;
         static TwTables<32> t32;
+        static BigTables tbig;
         static std::once_flag once;
-        std::call_once(once, [] { fill_tw_tables(t16); fill_tw_tables(t32); });
+        std::call_once(once, [] { fill_tw_tables(t16); fill_tw_tables(t32); fill_big_tables(tbig); });
         if ((e = cudaMalloc(&ctx->tw16, sizeof(t16))) != cudaSuccess || (e = cudaMalloc(&ctx->tw32, sizeof(t32))) != cudaSuccess ||
+            (e = cudaMalloc(&ctx->twbig, sizeof(tbig))) != cudaSuccess ||
+            (e = cudaMemcpy(ctx->twbig, &tbig, sizeof(tbig), cudaMemcpyHostToDevice)) != cudaSuccess ||
             (e = cudaMemcpy(ctx->tw16, &t16, sizeof(t16), cudaMemcpyHostToDevice)) != cudaSuccess ||
             (e = cudaMemcpy(ctx->tw32, &t32, sizeof(t32), cudaMemcpyHostToDevice)) != cudaSuccess) {
             delete ctx;
@@ -146,6 +152,7 @@ int b200tfhe_context_destroy(b200tfhe_context *ctx) {
     ctx->ws.release();
     cudaFree(ctx->tw16);
     cudaFree(ctx->tw32);
+    cudaFree(ctx->twbig);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
     return 0;

@@ -199,7 +199,7 @@ int br_supported(const Params &p) {
     if (p.bits == (int)sizeof(T) * 8 && p.N == 2 * R * R && p.k == K && p.pbs_level == L && p.pbs_base_log == BL) return R;
     BR_INSTANCES(X)
 #undef X
-    return 0;
+    return br_big_supported(p);
 }
 
 int br_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
@@ -209,12 +209,13 @@ int br_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
         return launch_br<T, R, K, L, BL, CTS>(a, st);
     BR_INSTANCES(X)
 #undef X
-    return -1;
+    return br_big_launch(p, a, st);
 }
 
 int bsk_convert_launch(const Params &p, const void *std_bsk, void *out, const void *tw_fwd, cudaStream_t st) {
     size_t npoly = (size_t)p.n * p.pbs_level * (p.k + 1) * (p.k + 1);
     int R = br_supported(p);
+    if (R == 256) return bsk_convert_big_launch(p, std_bsk, out, tw_fwd, st);
     int grid = 148 * 4;
     if (R == 32 && p.bits == 64) bsk_convert_kernel<uint64_t, 32><<<grid, 64, 0, st>>>((const uint64_t *)std_bsk, (cplx *)out, npoly, (const cplx *)tw_fwd);
     else if (R == 16 && p.bits == 64) bsk_convert_kernel<uint64_t, 16><<<grid, 128, 0, st>>>((const uint64_t *)std_bsk, (cplx *)out, npoly, (const cplx *)tw_fwd);

@@ -1,0 +1,151 @@
+// br_big.cuh -- CMUX stages for N = 8192 (PARAM_MESSAGE_3_CARRY_3: k = 1, l = 2): one CTA of 256 threads per ciphertext.
+//
+// Same reference semantics as br_core.cuh (fft64/crypto/ggsw.rs:477-598, bootstrap.rs:243-344); different shape because
+// the accumulator (128 KB) and a Fourier polynomial (64 KB) no longer fit a warp-sized team:
+//   * FFT of size M = 4096 = 16 x 256: every thread holds 16 points; pass A is a radix-16 DIT over the stride-256
+//     index in registers, then a CTA-wide transpose through one 64 KB shared buffer hands each 16-thread team one
+//     256-point DFT, done as 16 x 16 exactly like the small-N team FFT (in-place XOR-swizzled 16x16 transpose).
+//   * After the forward transform thread `tid` holds positions p*256 + tid (p < 16) of EVERY polynomial, so the Fourier
+//     multiply-accumulate is register-to-register: F[j][p] += G[..][j][p][tid] * D[p]; no Fourier buffer in shared memory.
+//   * Shared memory: acc 128 KB + exchange 64 KB + mod-switched mask.
+#pragma once
+#include "fft_reg.cuh"
+#include "br_core.cuh"
+
+namespace b200tfhe {
+
+struct BigTables {
+    cplx t1f[16][256];  // u_t * w_4096^{t k1}       u_t = e^{i pi t/N}, w_4096 = e^{-2 pi i/4096}
+    cplx t1i[16][256];  // conj(t1f) / M
+    cplx pf[8][16];     // plain 256-point team DFT: [b<4][lane] = w_256^{lane b}, [4+a][lane] = w_256^{lane 4a}
+    cplx pi[8][16];     // conjugates
+};
+
+template <typename T, int K, int L, int BASE_LOG> struct BigCore {
+    static constexpr int P = 16, TH = 256, M = 4096, N = 8192, K1 = K + 1, LOGP = 4, LOGN = 13;
+    static constexpr int TWQ = 2;  // e^{i pi 256 m / N} = e^{2 pi i (2m)/128}
+    static constexpr int GGSW_CPLX = L * K1 * K1 * M;
+    static constexpr size_t ACC_BYTES = (size_t)K1 * N * sizeof(T), XCH_BYTES = (size_t)M * sizeof(cplx);
+
+    HD static int swz(int row, int col) { return row * 16 + (col ^ row); }
+
+    // digits of level index t (t = 0 <-> level L, the first digit the recurrence emits) of acc_r*X^a - acc_r
+    template <int TL> HD static void digits(int tid, const T *acc_r, int a, cplx (&x)[P]) {
+        static_for<0, P>([&](auto p) {
+            constexpr int m = brev(decltype(p)::value, LOGP);
+            const int c = tid + TH * m;
+            T d0 = rot_read<T, N>(acc_r, c, a) - acc_r[c];
+            T d1 = rot_read<T, N>(acc_r, c + M, a) - acc_r[c + M];
+            T s0 = decomp_init_state<T>(d0, BASE_LOG, L), s1 = decomp_init_state<T>(d1, BASE_LOG, L);
+            int32_t g0 = 0, g1 = 0;
+            static_for<0, TL + 1>([&](auto) {
+                g0 = (int32_t)decomp_next_digit<T>(s0, BASE_LOG);
+                g1 = (int32_t)decomp_next_digit<T>(s1, BASE_LOG);
+            });
+            x[decltype(p)::value] = cplx{int_to_double(g0), int_to_double(g1)};
+        });
+    }
+    HD static void key_input(int tid, const T *poly, cplx (&x)[P]) {
+        static_for<0, P>([&](auto p) {
+            constexpr int m = brev(decltype(p)::value, LOGP);
+            const int c = tid + TH * m;
+            x[decltype(p)::value] = cplx{torus_to_double<T>(poly[c]), torus_to_double<T>(poly[c + M])};
+        });
+    }
+
+    // ---- forward: fwdA | CTA sync | fwdB_load | team sync | fwdB_pass1 | team sync | fwdB_pass2 | (CTA sync before next fwdA)
+    HD static void fwdA(int tid, cplx (&x)[P], cplx *S1, const BigTables *tb) {
+        static_for<0, P>([&](auto p) {
+            constexpr int m = brev(decltype(p)::value, LOGP);
+            x[decltype(p)::value] = cmul_root<m * TWQ>(x[decltype(p)::value]);
+        });
+        fft_dit<P, -1>(x);
+        static_for<0, P>([&](auto k1) {
+            S1[decltype(k1)::value * TH + tid] = cmul(x[decltype(k1)::value], tb->t1f[decltype(k1)::value][tid]);
+        });
+    }
+    HD static void fwdB_load(int tid, cplx (&x)[P], const cplx *S1) {
+        const int team = tid >> 4, lane = tid & 15;
+        static_for<0, P>([&](auto p) { x[decltype(p)::value] = S1[team * TH + lane + 16 * brev(decltype(p)::value, LOGP)]; });
+    }
+    template <int DIR> HD static void team_twiddle(int lane, cplx (&x)[P], const cplx (*tw)[16]) {
+        cplx r[4];
+        for (int b = 1; b < 4; b++) r[b] = tw[b][lane];
+        static_for<0, 4>([&](auto a) {
+            if constexpr (decltype(a)::value == 0) {
+                static_for<1, 4>([&](auto b) { x[decltype(b)::value] = cmul(x[decltype(b)::value], r[decltype(b)::value]); });
+            } else {
+                cplx q = tw[4 + decltype(a)::value][lane];
+                x[decltype(a)::value * 4] = cmul(x[decltype(a)::value * 4], q);
+                static_for<1, 4>([&](auto b) {
+                    constexpr int e = decltype(a)::value * 4 + decltype(b)::value;
+                    x[e] = cmul(x[e], cmul(r[decltype(b)::value], q));
+                });
+            }
+        });
+    }
+    HD static void fwdB_pass1(int tid, cplx (&x)[P], cplx *S1, const BigTables *tb) {
+        const int team = tid >> 4, lane = tid & 15;
+        fft_dit<P, -1>(x);
+        team_twiddle<-1>(lane, x, tb->pf);
+        static_for<0, P>([&](auto e) { S1[team * TH + swz(decltype(e)::value, lane)] = x[decltype(e)::value]; });
+    }
+    // after this x[p] = Fourier position p*256 + tid
+    HD static void fwdB_pass2(int tid, cplx (&x)[P], const cplx *S1) {
+        const int team = tid >> 4, lane = tid & 15;
+        static_for<0, P>([&](auto p) { x[decltype(p)::value] = S1[team * TH + swz(lane, brev(decltype(p)::value, LOGP))]; });
+        fft_dit<P, -1>(x);
+    }
+
+    // F[j][p] += G[lvl][r][j][p*256 + tid] * x[p]
+    HD static void mac(int tid, int lvl, int r, const cplx *ggsw, const cplx (&x)[P], cplx (&F)[K1][P]) {
+        static_for<0, K1>([&](auto j) {
+            const cplx *g = ggsw + ((size_t)(lvl * K1 + r) * K1 + decltype(j)::value) * M + tid;
+            cplx gv[P];
+            static_for<0, P>([&](auto p) { gv[decltype(p)::value] = ldg_stream(g + decltype(p)::value * TH); });
+            static_for<0, P>([&](auto p) {
+                cplx &f = F[decltype(j)::value][decltype(p)::value];
+                const cplx a = gv[decltype(p)::value], d = x[decltype(p)::value];
+                f.re = fma_(a.re, d.re, f.re);
+                f.re = fma_(-a.im, d.im, f.re);
+                f.im = fma_(a.re, d.im, f.im);
+                f.im = fma_(a.im, d.re, f.im);
+            });
+        });
+    }
+
+    // ---- inverse: (x[pp] = F[brev(pp)]) invA | team sync | invB_load | team sync | invB_store | CTA sync | invC
+    HD static void invA(int tid, cplx (&x)[P], cplx *S1, const BigTables *tb) {
+        const int team = tid >> 4, lane = tid & 15;
+        fft_dit<P, +1>(x);
+        team_twiddle<+1>(lane, x, tb->pi);
+        static_for<0, P>([&](auto l) { S1[team * TH + swz(decltype(l)::value, lane)] = x[decltype(l)::value]; });
+    }
+    HD static void invB_load(int tid, cplx (&x)[P], const cplx *S1) {
+        const int team = tid >> 4, lane = tid & 15;
+        static_for<0, P>([&](auto p) { x[decltype(p)::value] = S1[team * TH + swz(lane, brev(decltype(p)::value, LOGP))]; });
+    }
+    HD static void invB_store(int tid, cplx (&x)[P], cplx *S1) {
+        const int team = tid >> 4, lane = tid & 15;
+        fft_dit<P, +1>(x);
+        static_for<0, P>([&](auto m2) { S1[team * TH + lane + 16 * decltype(m2)::value] = x[decltype(m2)::value]; });
+    }
+    // result: x[m].re -> coefficient tid + 256 m, x[m].im -> that + M, already scaled by 1/M and un-twisted
+    HD static void invC(int tid, cplx (&x)[P], const cplx *S1, const BigTables *tb) {
+        static_for<0, P>([&](auto pp) {
+            constexpr int k1 = brev(decltype(pp)::value, LOGP);
+            x[decltype(pp)::value] = cmul(S1[k1 * TH + tid], tb->t1i[k1][tid]);
+        });
+        fft_dit<P, +1>(x);
+        static_for<0, P>([&](auto m) { x[decltype(m)::value] = cmul_root<-decltype(m)::value * TWQ>(x[decltype(m)::value]); });
+    }
+    HD static void accumulate(int tid, const cplx (&x)[P], T *acc_j) {
+        static_for<0, P>([&](auto m) {
+            const int c = tid + TH * decltype(m)::value;
+            acc_j[c] += torus_from_double<T>(x[decltype(m)::value].re);
+            acc_j[c + M] += torus_from_double<T>(x[decltype(m)::value].im);
+        });
+    }
+};
+
+}  // namespace b200tfhe

@@ -24,6 +24,11 @@ int br_supported(const Params &p);  // returns team radix R (16/32) or 0
 int br_launch(const Params &p, const BRLaunch &a, cudaStream_t st);
 int bsk_convert_launch(const Params &p, const void *std_bsk, void *out, const void *tw_fwd, cudaStream_t st);
 
+// blind_rotate_big.cu (N = 8192)
+int br_big_supported(const Params &p);
+int br_big_launch(const Params &p, const BRLaunch &a, cudaStream_t st);
+int bsk_convert_big_launch(const Params &p, const void *std_bsk, void *out, const void *tables, cudaStream_t st);
+
 // keyswitch.cu
 struct KSLaunch {
     const void *in;   size_t in_stride;    // [batch][in_stride], n_in+1 used

@@ -1,6 +1,7 @@
 // twiddles.hpp -- host-side generation of the per-lane twiddle tables (long double, reduced angles).
 #pragma once
 #include "fft_reg.cuh"
+#include "br_big.cuh"
 #include <cmath>
 
 namespace b200tfhe {
@@ -24,6 +25,24 @@ template <int R> void fill_tw_tables(TwTables<R> &t) {
         for (int a = 0; a < R / 4; a++) {
             t.fwd[4 + a][lane] = root_2N(-(long long)lane * 16 * a, N);          // w_l^{4a} = e^{-2 pi i l 4a/M}
             t.inv[4 + a][lane] = root_2N((long long)4 * a * (4 * lane - 1), N);  // z_l^{4a}
+        }
+    }
+}
+
+inline void fill_big_tables(BigTables &t) {
+    const int N = 8192, M = 4096;
+    for (int k1 = 0; k1 < 16; k1++)
+        for (int th = 0; th < 256; th++) {
+            cplx z = root_2N((long long)th * (1 - 4 * k1), N);      // u_t * w_4096^{t k1}
+            t.t1f[k1][th] = z;
+            t.t1i[k1][th] = cplx{z.re / M, -z.im / M};
+        }
+    for (int lane = 0; lane < 16; lane++) {
+        for (int b = 0; b < 4; b++) {
+            cplx z = root_2N(-(long long)lane * b * 64, N);          // w_256^{lane b}
+            t.pf[b][lane] = z; t.pi[b][lane] = cplx{z.re, -z.im};
+            cplx q = root_2N(-(long long)lane * b * 256, N);         // w_256^{lane 4b}
+            t.pf[4 + b][lane] = q; t.pi[4 + b][lane] = cplx{q.re, -q.im};
         }
     }
 }
