@@ -255,6 +255,18 @@ def main():
     br_steps = max(2, min(args.steps, 3))
     ms_br = timed(step_br, br_steps, 1) / br_steps
     ms_ks = timed(step_ks, br_steps, 1) / br_steps
+    # single-PBS latency (the metric's second half): batch of ONE ciphertext through the same KS+PBS entry point
+    lat = []
+    for it in range(60):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        ctx.check(lib.b200tfhe_ks_pbs_batch_dev(ctx._h, ksk._h, bsk._h, VP(d_in.data_ptr()), VP(d_out.data_ptr()),
+                                                VP(d_lut.data_ptr()), None, 1))
+        e1.record(stream)
+        torch.cuda.synchronize()
+        if it >= 10:
+            lat.append(e0.elapsed_time(e1))
+    lat.sort()
     tf = C.c_double()
     ctx.check(lib.b200tfhe_probe_fp64_tflops(ctx._h, C.c_double(300.0), C.byref(tf)))
 
@@ -286,6 +298,9 @@ def main():
         "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": B * big * 8 + glwe * 8, "d2h_bytes_per_step": B * big * 8,
                 "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": int(launches),
+        "latency": {"what": "single KS+PBS (batch 1), device-resident, CUDA events", "p50_ms": lat[len(lat) // 2],
+                    "p99_ms": lat[min(len(lat) - 1, int(len(lat) * 0.99))], "samples": len(lat),
+                    "reference_published_ms": 16.6},
         "roofline": {"bound": "fp64", "kernel": "blind_rotate_kernel", "achieved": achieved, "peak": tf.value, "unit": "TFLOP/s",
                      "frac": achieved / tf.value if tf.value else None, "traffic": None,
                      "peak_source": "live b200tfhe_probe_fp64_tflops (MEASURED_PEAKS.json has no FP64 figure)",

@@ -169,3 +169,53 @@ def test_blind_rotate_glwe_and_errors(ctx):
     bad = t.core_crypto.make_params(o.n, o.k, 1024, o.b, o.l, o.b_ks, o.l_ks, 64)
     with pytest.raises(t.B200TfheError):
         t.FourierLweBootstrapKey.alloc(ctx, bad)                                                 # unsupported set
+
+
+def test_shortint_apply_lookup_table_mixed_trivial_and_encrypted(ctx):
+    """shortint/server_key/tests/shortint.rs:366-430 (keyswitch_bootstrap / programmable_bootstrap) + :216 (trivial_pbs):
+    a list mixing encrypted and trivial ciphertexts, two tables selected per ciphertext, metadata updates."""
+    from tfhe_rs_odd_b200 import shortint
+    o = get_oracle("MESSAGE_2_CARRY_2")
+    p, bsk, ksk = _keys(ctx, o)
+    sk = shortint.ServerKey(ksk, bsk, 4, 4, "ks_pbs")
+    B = 24
+    rng = np.random.default_rng(21)
+    msgs = rng.integers(0, 16, B)
+    data = o.encrypt(o.encode(msgs), "big")
+    noise = np.full(B, shortint.NOISE_NOMINAL)
+    triv = np.arange(B) % 3 == 0
+    data[triv, :-1] = 0
+    data[triv, -1] = o.encode(msgs[triv])
+    noise[triv] = shortint.NOISE_ZERO
+    cts = shortint.CiphertextList(data, degree=15, noise_level=noise)
+    lut_a = sk.generate_lookup_table(lambda x: (x * x) % 16)
+    lut_b = sk.generate_lookup_table(lambda x: x // 4)          # carry extract, degree 3
+    idx = (np.arange(B) % 2).astype(np.uint32)
+    out = sk.apply_lookup_table(cts, [lut_a, lut_b], idx)
+    want = np.where(idx == 0, (msgs * msgs) % 16, msgs // 4)
+    assert np.array_equal(o.decode(o.phase(out.data, "big")) % 16, want)
+    assert np.array_equal(out.degree, np.where(idx == 0, lut_a.degree, lut_b.degree))
+    assert (out.noise_level[triv] == shortint.NOISE_ZERO).all() and (out.noise_level[~triv] == shortint.NOISE_NOMINAL).all()
+    assert not out.data[triv, :-1].any()                          # trivial stays trivial, never touched the GPU
+    # encrypted part equals the raw C-ABI result on the same inputs, bit for bit (host layer adds no arithmetic)
+    import tfhe_rs_odd_b200 as t
+    raw = t.keyswitch_programmable_bootstrap(ksk, bsk, data[~triv], np.stack([lut_a.acc, lut_b.acc]), lut_idx=idx[~triv])
+    assert np.array_equal(raw, out.data[~triv])
+
+
+def test_boolean_server_key_trivial_arms_and_not(ctx):
+    """boolean/server_key/tests.rs trivial/encrypted mixes: Trivial operands never bootstrap (engine/mod.rs:614-622,980-993)."""
+    from tfhe_rs_odd_b200 import boolean
+    o = get_oracle("TOY_U32")
+    p, bsk, ksk = _keys(ctx, o)
+    sk = boolean.ServerKey(ksk, bsk, pbs_first=True)
+    a = np.array([0, 0, 1, 1], bool); b = np.array([0, 1, 0, 1], bool)
+    T, F = 1 << 29, 7 << 29
+    ca = o.encrypt(np.where(a, T, F).astype(np.uint64), "small", seed=3).astype(np.uint32)
+    dec = lambda c: o.decode_bool(o.phase(np.asarray(c).astype(np.uint64), "small"))
+    assert np.array_equal(dec(sk.not_(ca)), ~a)
+    assert np.array_equal(sk.and_(a, b), a & b)                                   # trivial, trivial
+    for name, fn, want in [("and", sk.and_, a & b), ("nand", sk.nand, ~(a & b)), ("or", sk.or_, a | b),
+                           ("nor", sk.nor, ~(a | b)), ("xor", sk.xor, a ^ b), ("xnor", sk.xnor, ~(a ^ b))]:
+        assert np.array_equal(dec(fn(ca, b)), want), name                          # encrypted, trivial
+        assert np.array_equal(dec(fn(a, o.encrypt(np.where(b, T, F).astype(np.uint64), "small", seed=8).astype(np.uint32))), want), name

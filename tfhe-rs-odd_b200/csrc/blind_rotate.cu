@@ -202,8 +202,20 @@ int br_supported(const Params &p) {
     return br_big_supported(p);
 }
 
+// small batches (fewer ciphertexts than 3 per SM): one ciphertext per CTA spreads them over more SMs and avoids ghost
+// ciphertexts inside a CTA -- this is also the single-PBS latency configuration
+#define BR_SMALL_BATCH_INSTANCES(X)  \
+    X(uint64_t, 32, 1, 1, 23, 1)
+
 int br_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
     if (a.batch <= 0) return 0;
+    if (a.batch < 3 * 148) {
+#define X(T, R, K, L, BL, CTS) \
+    if (p.bits == (int)sizeof(T) * 8 && p.N == 2 * R * R && p.k == K && p.pbs_level == L && p.pbs_base_log == BL) \
+        return launch_br<T, R, K, L, BL, CTS>(a, st);
+        BR_SMALL_BATCH_INSTANCES(X)
+#undef X
+    }
 #define X(T, R, K, L, BL, CTS) \
     if (p.bits == (int)sizeof(T) * 8 && p.N == 2 * R * R && p.k == K && p.pbs_level == L && p.pbs_base_log == BL) \
         return launch_br<T, R, K, L, BL, CTS>(a, st);
