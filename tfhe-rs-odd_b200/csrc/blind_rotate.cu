@@ -12,6 +12,7 @@
 // par_convert_standard_lwe_bootstrap_key_to_fourier (algorithms/lwe_bootstrap_key_conversion.rs:99-152).
 #include "br_core.cuh"
 #include "kernels.h"
+#include <cstdlib>
 
 #ifndef B200TFHE_REALIGN
 #define B200TFHE_REALIGN 1
@@ -209,6 +210,9 @@ int br_supported(const Params &p) {
 
 int br_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
     if (a.batch <= 0) return 0;
+    static const bool no_tmem = getenv("B200TFHE_NO_TMEM") != nullptr;   // A/B switch for profiling
+    static const bool force_tmem = getenv("B200TFHE_FORCE_TMEM") != nullptr;   // tests: exercise the TMEM kernel on small batches
+    if (!no_tmem && (force_tmem || a.batch >= 4 * 148) && br_tmem_supported(p)) return br_tmem_launch(p, a, st);
     if (a.batch < 3 * 148) {
 #define X(T, R, K, L, BL, CTS) \
     if (p.bits == (int)sizeof(T) * 8 && p.N == 2 * R * R && p.k == K && p.pbs_level == L && p.pbs_base_log == BL) \

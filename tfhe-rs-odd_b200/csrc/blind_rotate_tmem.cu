@@ -1,0 +1,231 @@
+// blind_rotate_tmem.cu -- blind rotation for (N = 2048, k = 1, l = 1) with the forward transforms exchanged through
+// TENSOR MEMORY: 4 ciphertexts per CTA (8 warps / SM) instead of 3 (6 warps).
+//
+// Why: the shared-memory budget of blind_rotate.cu is 67 KB per ciphertext (accumulator 32 KB + one exchange/Fourier region
+// per polynomial 2 x 17 KB), i.e. 3 ciphertexts = 6 warps per SM, and ncu shows the FP64 pipe starved by latency at that
+// occupancy (profiles/r01_ncu_blind_rotate_summary.json).  Here
+//   * a team's own Fourier polynomial D_r never leaves its registers: its own key row is applied register-to-register;
+//   * D_r reaches the other team through TMEM (tcgen05.st / tcgen05.ld, 32x32b shape: thread l of a warp owns TMEM lane
+//     32*(warp%4)+l).  The two teams of ciphertext q are warps q and q+4, which address the same TMEM lane quadrant, and the
+//     MAC needs exactly "same lane, same Fourier position" of the other polynomial -- no cross-lane movement at all;
+//   * the two teams then share ONE 17 KB exchange region for their FFT transposes (team 0 first, team 1 second, ordered by
+//     named barriers), so a ciphertext needs 49 KB of shared memory and 4 fit next to the twiddle tables.
+// TMEM use per CTA: 4 quadrants x 2 polynomials x 128 columns = 256 columns.  No tensor-core instruction is involved: TMEM
+// is used as a 256 KB per-SM scratchpad that does not consume shared-memory capacity or LDS/STS bandwidth.
+#include "br_core.cuh"
+#include "kernels.h"
+
+namespace b200tfhe {
+
+#if defined(__CUDA_ARCH__)
+DEV void tmem_st32(uint32_t taddr, const uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+        "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]), "r"(v[10]),
+        "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]), "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]),
+        "r"(v[21]), "r"(v[22]), "r"(v[23]), "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]),
+        "r"(v[31])
+        : "memory");
+}
+DEV void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+          "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]),
+          "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
+          "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr)
+        : "memory");
+}
+DEV void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+DEV void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+DEV void tmem_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+DEV void tmem_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+DEV void named_bar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+#endif
+
+constexpr int TM_CTS = 4;        // ciphertexts per CTA
+constexpr int TM_COLS = 256;     // TMEM columns allocated per CTA
+
+template <typename T, int BL>
+__global__ void __launch_bounds__(TM_CTS * 64, 1)
+blind_rotate_tmem_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const T *__restrict__ luts,
+                         const uint32_t *__restrict__ lut_idx, const cplx *__restrict__ bsk, T *__restrict__ out,
+                         size_t out_stride, int n, int batch, int mode, const cplx *__restrict__ tw_fwd_,
+                         const cplx *__restrict__ tw_inv_) {
+#if defined(__CUDA_ARCH__)
+    constexpr int R = 32, K = 1, L = 1, K1 = 2;
+    typedef BRCore<T, R, K, L, BL> C;
+    typedef TeamFFT<R> FFT;
+    constexpr int N = C::N, REGION = C::REGION, CH = C::CH, THREADS = TM_CTS * 64;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ uint32_t tmem_base_smem;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q = warp & 3, r = warp >> 2;        // ciphertext slot = TMEM lane quadrant; team (polynomial) index
+    int ct = blockIdx.x * TM_CTS + q;
+    const bool live = ct < batch;
+    if (!live) ct = batch - 1;
+
+    const size_t ahat_bytes = (((size_t)(n + 1) * sizeof(uint16_t)) + 15) & ~(size_t)15;
+    constexpr size_t XCH_BYTES = (size_t)REGION * sizeof(cplx), ACC_BYTES = (size_t)K1 * N * sizeof(T);
+    cplx *region = reinterpret_cast<cplx *>(smem_raw + (size_t)q * XCH_BYTES);                     // shared by the 2 teams
+    T *acc_ct = reinterpret_cast<T *>(smem_raw + TM_CTS * XCH_BYTES + (size_t)q * ACC_BYTES);
+    T *acc_r = acc_ct + (size_t)r * N;
+    uint16_t *ahat = reinterpret_cast<uint16_t *>(smem_raw + TM_CTS * (XCH_BYTES + ACC_BYTES) + q * ahat_bytes);
+    cplx *tw_s = reinterpret_cast<cplx *>(smem_raw + TM_CTS * (XCH_BYTES + ACC_BYTES + ahat_bytes));
+    constexpr int TW_HALF = TwTables<R>::ENTRIES * R;
+    for (int e = threadIdx.x; e < TW_HALF; e += THREADS) {
+        tw_s[e] = tw_fwd_[e];
+        tw_s[TW_HALF + e] = tw_inv_[e];
+    }
+    const cplx(*twf)[R] = reinterpret_cast<const cplx(*)[R]>(tw_s);
+    const cplx(*twi)[R] = reinterpret_cast<const cplx(*)[R]>(tw_s + TW_HALF);
+
+    // ---- tensor-memory allocation (one warp), address broadcast through shared memory -------------------------------
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(&tmem_base_smem)), "n"(TM_COLS));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    // ---- prologue ----------------------------------------------------------------------------------------------------
+    const T *lwe = lwe_in + (size_t)ct * lwe_stride;
+    for (int i = r * R + lane; i <= n; i += K1 * R) ahat[i] = (uint16_t)(modswitch<T>(lwe[i], C::LOGN) & (2 * N - 1));
+    tmem_fence_before();
+    __syncthreads();
+    tmem_fence_after();
+    const uint32_t tmem_base = tmem_base_smem;
+    // lane field (bits 31..16) = first lane of this warp's quadrant; column field = my / the other team's polynomial
+    const uint32_t t_mine = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(r * 128);
+    const uint32_t t_other = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((1 - r) * 128);
+    {
+        const T *lut = luts + (size_t)(lut_idx ? lut_idx[ct] : 0) * K1 * N + (size_t)r * N;
+        const int a0 = (2 * N - (int)ahat[n]) & (2 * N - 1);
+        for (int c = lane; c < N; c += R) acc_r[c] = rot_read<T, N>(lut, c, a0);
+    }
+    __syncwarp();
+    const int bar_ct = 1 + 2 * q, bar_x = 2 + 2 * q;      // named barriers of this ciphertext (64 threads each)
+
+    for (int i = 0; i < n; i++) {
+        __syncthreads();   // re-align the CTA (instruction-cache sharing); also orders team 1's last use of `region` before team 0's next
+        const int a = ahat[i];
+        const cplx *ggsw_i = bsk + (size_t)i * C::GGSW_CPLX;
+        cplx x[R];
+        {
+            int32_t dre[1][R], dim[1][R];
+            C::digits(lane, acc_r, a, dre, dim);
+            C::template digits_to_cplx<0>(dre, dim, x);
+        }
+        FFT::fwd_pass1_compute(lane, x, twf);
+        // forward transpose through the shared region: team 0, then team 1
+        if (r == 1) named_bar_sync(bar_x, 64);
+        FFT::pass1_store(lane, x, region);
+        __syncwarp();
+        FFT::fwd_pass2_load(lane, x, region);
+        __syncwarp();
+        if (r == 0) named_bar_sync(bar_x, 64);
+        cplx g[CH];
+        C::template own_chunk_load<0>(lane, r, ggsw_i, g);      // key loads in flight during the second radix-32 pass
+        FFT::fwd_pass2_compute(x);                              // x[p] = D_r at Fourier position p
+        // D_r -> tensor memory, in register order pp (position brev(pp)) so that the reader's chunks are contiguous columns
+        cplx F[R];
+        static_for<0, R>([&](auto pp) { F[decltype(pp)::value] = x[brev(decltype(pp)::value, FFT::LOGR)]; });
+        static_for<0, 4>([&](auto part) {
+            uint32_t v[32];
+            static_for<0, 8>([&](auto e) {
+                constexpr int pp = decltype(part)::value * 8 + decltype(e)::value;
+                v[4 * decltype(e)::value + 0] = (uint32_t)__double2loint(F[pp].re);
+                v[4 * decltype(e)::value + 1] = (uint32_t)__double2hiint(F[pp].re);
+                v[4 * decltype(e)::value + 2] = (uint32_t)__double2loint(F[pp].im);
+                v[4 * decltype(e)::value + 3] = (uint32_t)__double2hiint(F[pp].im);
+            });
+            tmem_st32(t_mine + decltype(part)::value * 32, v);
+        });
+        // own key row, register to register (F currently holds D_r in register order)
+        {
+            cplx xb[R];
+            static_for<0, R>([&](auto pp) { xb[decltype(pp)::value] = F[decltype(pp)::value]; });
+            C::template own_chunk_apply<0>(xb, g, F);
+            C::template own_chunk_load<1>(lane, r, ggsw_i, g);
+            C::template own_chunk_apply<1>(xb, g, F);
+        }
+        cplx h[CH];
+        C::template other_chunk_load<0>(lane, 1 - r, r, ggsw_i, h);   // in flight across the barrier
+        tmem_wait_st();
+        tmem_fence_before();
+        named_bar_sync(bar_ct, 64);
+        tmem_fence_after();
+        static_for<0, 4>([&](auto part) {
+            if constexpr (decltype(part)::value == 2) C::template other_chunk_load<1>(lane, 1 - r, r, ggsw_i, h);
+            uint32_t v[32];
+            tmem_ld32(t_other + decltype(part)::value * 32, v);
+            tmem_wait_ld();
+            static_for<0, 8>([&](auto e) {
+                constexpr int pp = decltype(part)::value * 8 + decltype(e)::value;
+                cplx d{__hiloint2double((int)v[4 * decltype(e)::value + 1], (int)v[4 * decltype(e)::value + 0]),
+                       __hiloint2double((int)v[4 * decltype(e)::value + 3], (int)v[4 * decltype(e)::value + 2])};
+                C::mac_one(F[pp], h[pp % CH], d);
+            });
+        });
+        tmem_fence_before();
+        named_bar_sync(bar_ct, 64);      // the other team has read my D: next iteration may overwrite it; also orders
+        tmem_fence_after();              // team 1's forward use of `region` before team 0's inverse use
+        FFT::inv_pass1_compute(lane, F, twi);
+        if (r == 1) named_bar_sync(bar_x, 64);
+        FFT::pass1_store(lane, F, region);
+        __syncwarp();
+        cplx y[R];
+        static_for<0, R>([&](auto p) { y[decltype(p)::value] = region[lane * FFT::ROW + brev(decltype(p)::value, FFT::LOGR)]; });
+        __syncwarp();
+        if (r == 0) named_bar_sync(bar_x, 64);
+        fft_dit<R, +1>(y);
+        static_for<0, R>([&](auto m) {
+            cplx t = cmul_root<-decltype(m)::value * FFT::TWQ>(y[decltype(m)::value]);
+            const int c = lane + R * decltype(m)::value;
+            acc_r[c] += torus_from_double<T>(t.re);
+            acc_r[c + C::M] += torus_from_double<T>(t.im);
+        });
+        __syncwarp();
+    }
+
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TM_COLS));
+    if (!live) return;
+    T *o = out + (size_t)ct * out_stride;
+    if (mode == BR_MODE_GLWE) {
+        for (int c = lane; c < N; c += R) o[(size_t)r * N + c] = acc_r[c];
+    } else {
+        if (r < K) {
+            for (int t = lane; t < N; t += R) o[(size_t)r * N + t] = (t == 0) ? acc_r[0] : (T)(0 - acc_r[N - t]);
+        } else if (lane == 0) {
+            o[(size_t)K * N] = acc_r[0];
+        }
+    }
+#endif
+}
+
+int br_tmem_supported(const Params &p) {
+    return p.bits == 64 && p.N == 2048 && p.k == 1 && p.pbs_level == 1 && p.pbs_base_log == 23;
+}
+
+int br_tmem_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
+    if (!br_tmem_supported(p)) return -1;
+    typedef BRCore<uint64_t, 32, 1, 1, 23> C;
+    auto kern = blind_rotate_tmem_kernel<uint64_t, 23>;
+    size_t ahat = (((size_t)(a.n + 1) * sizeof(uint16_t)) + 15) & ~(size_t)15;
+    size_t smem = TM_CTS * ((size_t)C::REGION * sizeof(cplx) + (size_t)2 * C::N * sizeof(uint64_t) + ahat) + sizeof(TwTables<32>);
+    static size_t configured = 0;
+    if (smem > configured) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return (int)e;
+        configured = smem;
+    }
+    int grid = (a.batch + TM_CTS - 1) / TM_CTS;
+    kern<<<grid, TM_CTS * 64, smem, st>>>((const uint64_t *)a.lwe_in, a.lwe_stride, (const uint64_t *)a.luts, a.lut_idx,
+                                         (const cplx *)a.bsk, (uint64_t *)a.out, a.out_stride, a.n, a.batch, a.mode,
+                                         (const cplx *)a.tw_fwd, (const cplx *)a.tw_inv);
+    return (int)cudaGetLastError();
+}
+
+}  // namespace b200tfhe

@@ -50,6 +50,14 @@ template <typename T, int R, int K, int L, int BASE_LOG> struct BRCore {
     // transposed partial results in fbuf_r[t] (t = 0 is level L, the first one the recurrence emits).
     HD static void digits_fwd_pass1(int lane, const T *acc_r, int a, cplx *fbuf_r, const cplx (*twf)[R]) {
         int32_t dre[L][R], dim[L][R];
+        digits(lane, acc_r, a, dre, dim);
+        static_for<0, L>([&](auto t) {
+            cplx x[R];
+            digits_to_cplx<decltype(t)::value>(dre, dim, x);
+            FFT::fwd_pass1(lane, x, fbuf_r + decltype(t)::value * REGION, twf);
+        });
+    }
+    HD static void digits(int lane, const T *acc_r, int a, int32_t (&dre)[L][R], int32_t (&dim)[L][R]) {
         static_for<0, R>([&](auto p) {
             constexpr int m = brev(decltype(p)::value, FFT::LOGR);
             const int c = lane + R * m;
@@ -66,13 +74,10 @@ template <typename T, int R, int K, int L, int BASE_LOG> struct BRCore {
                 });
             }
         });
-        static_for<0, L>([&](auto t) {
-            cplx x[R];
-            static_for<0, R>([&](auto p) {
-                x[decltype(p)::value] = cplx{int_to_double(dre[decltype(t)::value][decltype(p)::value]),
-                                             int_to_double(dim[decltype(t)::value][decltype(p)::value])};
-            });
-            FFT::fwd_pass1(lane, x, fbuf_r + decltype(t)::value * REGION, twf);
+    }
+    template <int TL> HD static void digits_to_cplx(const int32_t (&dre)[L][R], const int32_t (&dim)[L][R], cplx (&x)[R]) {
+        static_for<0, R>([&](auto p) {
+            x[decltype(p)::value] = cplx{int_to_double(dre[TL][decltype(p)::value]), int_to_double(dim[TL][decltype(p)::value])};
         });
     }
 
@@ -146,6 +151,31 @@ template <typename T, int R, int K, int L, int BASE_LOG> struct BRCore {
         f.re = fma_(-gv.im, dv.im, f.re);
         f.im = fma_(gv.re, dv.im, f.im);
         f.im = fma_(gv.im, dv.re, f.im);
+    }
+
+    // ---- pieces used by the TMEM variant of the kernel (blind_rotate.cu, single level): the team's own forward
+    // transform is still in registers after pass 2, so its own key row is applied register-to-register; the other
+    // team's transform arrives through tensor memory.  Register pp <-> Fourier position brev(pp) throughout.
+    template <int HALF> HD static void own_chunk_load(int lane, int j, const cplx *ggsw, cplx (&g)[CH]) {
+        const cplx *row = ggsw + ((size_t)j * K1 + j) * M;          // level 1, row r = j, column j
+        static_for<0, CH>([&](auto i) {
+            constexpr int pp = HALF * CH + decltype(i)::value;
+            g[decltype(i)::value] = ldg_stream(row + brev(pp, FFT::LOGR) * R + lane);
+        });
+    }
+    // F[pp] = D_own[pp] * g   (xb holds D_own already permuted to register order pp)
+    template <int HALF> HD static void own_chunk_apply(const cplx (&xb)[R], const cplx (&g)[CH], cplx (&F)[R]) {
+        static_for<0, CH>([&](auto i) {
+            constexpr int pp = HALF * CH + decltype(i)::value;
+            F[pp] = cmul(xb[pp], g[decltype(i)::value]);
+        });
+    }
+    template <int HALF> HD static void other_chunk_load(int lane, int r, int j, const cplx *ggsw, cplx (&h)[CH]) {
+        const cplx *row = ggsw + ((size_t)r * K1 + j) * M;
+        static_for<0, CH>([&](auto i) {
+            constexpr int pp = HALF * CH + decltype(i)::value;
+            h[decltype(i)::value] = ldg_stream(row + brev(pp, FFT::LOGR) * R + lane);
+        });
     }
 
     // Stage B2 (after a ciphertext-wide sync: every team finished reading D): inverse pass 1 into own region

@@ -149,12 +149,23 @@ template <int R> struct TeamFFT {
     // x[p] must hold the folded input point m = brev(p) of this lane (coefficient lane + R*m as real part,
     // + M as imaginary part), NOT yet twisted.  After the call x[k1] = u_l w_l^{k1} sum_m x_m v_m w_R^{m k1},
     // and it has been written to S[k1][lane].
-    HD static void fwd_pass1(int lane, cplx (&x)[R], cplx *region, const cplx (*tw)[R]) {
+    HD static void fwd_pass1_compute(int lane, cplx (&x)[R], const cplx (*tw)[R]) {
         static_for<0, R>([&](auto p) {
             constexpr int m = brev(decltype(p)::value, LOGR);
             x[decltype(p)::value] = cmul_root<m * TWQ>(x[decltype(p)::value]);
         });
         fft_dit<R, -1>(x);
+        mid_twiddle(lane, x, tw);
+    }
+    HD static void pass1_store(int lane, const cplx (&x)[R], cplx *region) {
+        static_for<0, R>([&](auto k1) { region[decltype(k1)::value * ROW + lane] = x[decltype(k1)::value]; });
+    }
+    HD static void fwd_pass1(int lane, cplx (&x)[R], cplx *region, const cplx (*tw)[R]) {
+        fwd_pass1_compute(lane, x, tw);
+        pass1_store(lane, x, region);
+    }
+    // x[e] *= r[e & 3] * q[e >> 2]  (per-lane tables, see TwTables)
+    HD static void mid_twiddle(int lane, cplx (&x)[R], const cplx (*tw)[R]) {
         cplx r[4];
         for (int b = 0; b < 4; b++) r[b] = tw[b][lane];
         static_for<0, R / 4>([&](auto a) {
@@ -168,7 +179,6 @@ template <int R> struct TeamFFT {
                 });
             }
         });
-        static_for<0, R>([&](auto k1) { region[decltype(k1)::value * ROW + lane] = x[decltype(k1)::value]; });
     }
     // team sync, then: x[p] <- S[lane][brev(p)]
     HD static void fwd_pass2_load(int lane, cplx (&x)[R], const cplx *region) {
@@ -179,22 +189,13 @@ template <int R> struct TeamFFT {
 
     // ---- inverse ----------------------------------------------------------------------------------
     // x[p] must hold Fourier position brev(p)*R + lane.  Writes S'[l][lane] = conj-twiddled partial result.
-    HD static void inv_pass1(int lane, cplx (&x)[R], cplx *region, const cplx (*tw)[R]) {
+    HD static void inv_pass1_compute(int lane, cplx (&x)[R], const cplx (*tw)[R]) {
         fft_dit<R, +1>(x);
-        cplx r[4];
-        for (int b = 0; b < 4; b++) r[b] = tw[b][lane];
-        static_for<0, R / 4>([&](auto a) {
-            if constexpr (decltype(a)::value == 0) {
-                static_for<0, 4>([&](auto b) { x[decltype(b)::value] = cmul(x[decltype(b)::value], r[decltype(b)::value]); });
-            } else {
-                cplx q = tw[4 + decltype(a)::value][lane];
-                static_for<0, 4>([&](auto b) {
-                    constexpr int e = decltype(a)::value * 4 + decltype(b)::value;
-                    x[e] = cmul(x[e], cmul(r[decltype(b)::value], q));
-                });
-            }
-        });
-        static_for<0, R>([&](auto l) { region[decltype(l)::value * ROW + lane] = x[decltype(l)::value]; });
+        mid_twiddle(lane, x, tw);
+    }
+    HD static void inv_pass1(int lane, cplx (&x)[R], cplx *region, const cplx (*tw)[R]) {
+        inv_pass1_compute(lane, x, tw);
+        pass1_store(lane, x, region);
     }
     // team sync, then: x[p] <- S'[lane][brev(p)], DIT, un-twist by the compile-time root.
     // Result: x[m] = (1/M) * conj(twist) * inverse DFT, i.e. re -> coefficient lane + R*m, im -> that + M.

@@ -29,6 +29,10 @@ int br_big_supported(const Params &p);
 int br_big_launch(const Params &p, const BRLaunch &a, cudaStream_t st);
 int bsk_convert_big_launch(const Params &p, const void *std_bsk, void *out, const void *tables, cudaStream_t st);
 
+// blind_rotate_tmem.cu (N = 2048, k = 1, l = 1: Fourier polynomials exchanged through tensor memory, 4 ct per CTA)
+int br_tmem_supported(const Params &p);
+int br_tmem_launch(const Params &p, const BRLaunch &a, cudaStream_t st);
+
 // keyswitch.cu
 struct KSLaunch {
     const void *in;   size_t in_stride;    // [batch][in_stride], n_in+1 used
