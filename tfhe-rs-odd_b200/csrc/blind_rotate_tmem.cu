@@ -8,10 +8,13 @@
 //   * D_r reaches the other team through TMEM (tcgen05.st / tcgen05.ld, 32x32b shape: thread l of a warp owns TMEM lane
 //     32*(warp%4)+l).  The two teams of ciphertext q are warps q and q+4, which address the same TMEM lane quadrant, and the
 //     MAC needs exactly "same lane, same Fourier position" of the other polynomial -- no cross-lane movement at all;
-//   * the two teams then share ONE 17 KB exchange region for their FFT transposes (team 0 first, team 1 second, ordered by
-//     named barriers), so a ciphertext needs 49 KB of shared memory and 4 fit next to the twiddle tables.
-// TMEM use per CTA: 4 quadrants x 2 polynomials x 128 columns = 256 columns.  No tensor-core instruction is involved: TMEM
-// is used as a 256 KB per-SM scratchpad that does not consume shared-memory capacity or LDS/STS bandwidth.
+//   * every team owns a HALF-size (8.5 KB) transpose region and does each 32x32 transpose in two column halves (16 source
+//     lanes at a time, 16 values parked in registers in between), so a ciphertext needs 32 + 17 = 49 KB of shared memory,
+//     4 fit next to the twiddle tables, and the teams never wait for each other's transposes;
+//   * the TMEM slots are double-buffered by iteration parity, so ONE 64-thread named barrier per iteration and ciphertext
+//     is the only inter-warp synchronisation of the data path.
+// TMEM use per CTA: 4 quadrants x 2 buffers x 2 polynomials x 128 columns = all 512 columns (1 CTA per SM).  No
+// tensor-core instruction is involved: TMEM is a 256 KB per-SM scratchpad that costs no shared-memory capacity or bandwidth.
 #include "br_core.cuh"
 #include "kernels.h"
 
@@ -44,10 +47,41 @@ DEV void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "mem
 DEV void tmem_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 DEV void tmem_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 DEV void named_bar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+DEV void named_bar_arrive(int id, int count) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+
+// 32x32 transpose of one warp's register tile through a half-size region (R rows of R/2 + 1 cplx):
+// in: x[k1] of lane s = S[k1][s];  out: x[p] of lane l = S[l][brev(p)].
+template <int R> DEV void transpose_split(int lane, cplx (&x)[R], cplx *hreg) {
+    constexpr int H = R / 2, ROWH = H + 1, LOGR = clog2(R);
+    cplx t[H];
+    if (lane < H) static_for<0, R>([&](auto k1) { hreg[decltype(k1)::value * ROWH + lane] = x[decltype(k1)::value]; });
+    __syncwarp();
+    static_for<0, H>([&](auto c) { t[decltype(c)::value] = hreg[lane * ROWH + decltype(c)::value]; });
+    __syncwarp();
+    if (lane >= H) static_for<0, R>([&](auto k1) { hreg[decltype(k1)::value * ROWH + lane - H] = x[decltype(k1)::value]; });
+    __syncwarp();
+    static_for<0, R>([&](auto p) {
+        constexpr int c = brev(decltype(p)::value, LOGR);
+        if constexpr (c < H) x[decltype(p)::value] = t[c];
+        else x[decltype(p)::value] = hreg[lane * ROWH + c - H];
+    });
+    __syncwarp();
+}
+#endif
+
+// Iteration alignment of the 4 ciphertexts of a CTA:
+//   0  none (warps drift apart: 4 instruction streams, instruction-cache misses)
+//   -1 lockstep (__syncthreads per iteration: one instruction stream, but every ciphertext hits the shared-memory pipe in
+//      the same cycles and the FP64 pipes in the same cycles -- measured: time = T_lsu + T_fp64)
+//   k>0 STAGGERED ring: ciphertext q starts iteration i when ciphertext q-1 has decomposed k of its 32 points of iteration
+//      i (and 0 waits for 3 of iteration i-1).  The streams stay a few hundred instructions apart (inside the 32 KB L1.5
+//      instruction cache) while the load/store bursts of one ciphertext overlap the FP64 phases of the others.
+#ifndef B200TFHE_TMEM_STAGGER
+#define B200TFHE_TMEM_STAGGER 8
 #endif
 
 constexpr int TM_CTS = 4;        // ciphertexts per CTA
-constexpr int TM_COLS = 256;     // TMEM columns allocated per CTA
+constexpr int TM_COLS = 512;     // TMEM columns allocated per CTA (2 buffers x 2 polynomials x 128)
 
 template <typename T, int BL>
 __global__ void __launch_bounds__(TM_CTS * 64, 1)
@@ -59,7 +93,7 @@ blind_rotate_tmem_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const 
     constexpr int R = 32, K = 1, L = 1, K1 = 2;
     typedef BRCore<T, R, K, L, BL> C;
     typedef TeamFFT<R> FFT;
-    constexpr int N = C::N, REGION = C::REGION, CH = C::CH, THREADS = TM_CTS * 64;
+    constexpr int N = C::N, CH = C::CH, THREADS = TM_CTS * 64;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ uint32_t tmem_base_smem;
 
@@ -70,12 +104,12 @@ blind_rotate_tmem_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const 
     if (!live) ct = batch - 1;
 
     const size_t ahat_bytes = (((size_t)(n + 1) * sizeof(uint16_t)) + 15) & ~(size_t)15;
-    constexpr size_t XCH_BYTES = (size_t)REGION * sizeof(cplx), ACC_BYTES = (size_t)K1 * N * sizeof(T);
-    cplx *region = reinterpret_cast<cplx *>(smem_raw + (size_t)q * XCH_BYTES);                     // shared by the 2 teams
-    T *acc_ct = reinterpret_cast<T *>(smem_raw + TM_CTS * XCH_BYTES + (size_t)q * ACC_BYTES);
-    T *acc_r = acc_ct + (size_t)r * N;
-    uint16_t *ahat = reinterpret_cast<uint16_t *>(smem_raw + TM_CTS * (XCH_BYTES + ACC_BYTES) + q * ahat_bytes);
-    cplx *tw_s = reinterpret_cast<cplx *>(smem_raw + TM_CTS * (XCH_BYTES + ACC_BYTES + ahat_bytes));
+    constexpr int HREGION = R * (R / 2 + 1);      // cplx per private half-size transpose region
+    constexpr size_t XCH_BYTES = (size_t)HREGION * sizeof(cplx), ACC_BYTES = (size_t)N * sizeof(T);
+    cplx *hreg = reinterpret_cast<cplx *>(smem_raw + (size_t)warp * XCH_BYTES);
+    T *acc_r = reinterpret_cast<T *>(smem_raw + 2 * TM_CTS * XCH_BYTES + (size_t)(q * K1 + r) * ACC_BYTES);
+    uint16_t *ahat = reinterpret_cast<uint16_t *>(smem_raw + 2 * TM_CTS * (XCH_BYTES + ACC_BYTES) + q * ahat_bytes);
+    cplx *tw_s = reinterpret_cast<cplx *>(smem_raw + 2 * TM_CTS * (XCH_BYTES + ACC_BYTES) + TM_CTS * ahat_bytes);
     constexpr int TW_HALF = TwTables<R>::ENTRIES * R;
     for (int e = threadIdx.x; e < TW_HALF; e += THREADS) {
         tw_s[e] = tw_fwd_[e];
@@ -95,60 +129,68 @@ blind_rotate_tmem_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const 
     tmem_fence_before();
     __syncthreads();
     tmem_fence_after();
-    const uint32_t tmem_base = tmem_base_smem;
-    // lane field (bits 31..16) = first lane of this warp's quadrant; column field = my / the other team's polynomial
-    const uint32_t t_mine = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(r * 128);
-    const uint32_t t_other = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((1 - r) * 128);
+    // lane field (bits 31..16) = first lane of this warp's quadrant; columns: [buffer][polynomial][128]
+    const uint32_t t_quad = tmem_base_smem + ((uint32_t)(q * 32) << 16);
     {
         const T *lut = luts + (size_t)(lut_idx ? lut_idx[ct] : 0) * K1 * N + (size_t)r * N;
         const int a0 = (2 * N - (int)ahat[n]) & (2 * N - 1);
         for (int c = lane; c < N; c += R) acc_r[c] = rot_read<T, N>(lut, c, a0);
     }
     __syncwarp();
-    const int bar_ct = 1 + 2 * q, bar_x = 2 + 2 * q;      // named barriers of this ciphertext (64 threads each)
+    const int bar_ct = 1 + q;      // named barrier of this ciphertext (64 threads)
+#if B200TFHE_TMEM_STAGGER > 0
+    const int bar_top = 1 + TM_CTS + q, bar_next = 1 + TM_CTS + ((q + 1) & (TM_CTS - 1));   // 128 threads: 64 sync + 64 arrive
+    if (q == TM_CTS - 1) named_bar_arrive(bar_next, 128);     // lets ciphertext 0 into iteration 0
+#endif
 
     for (int i = 0; i < n; i++) {
-        __syncthreads();   // re-align the CTA (instruction-cache sharing); also orders team 1's last use of `region` before team 0's next
+#if B200TFHE_TMEM_STAGGER < 0
+        __syncthreads();
+#elif B200TFHE_TMEM_STAGGER > 0
+        named_bar_sync(bar_top, 128);
+#define RELEASE_POINT(k) if constexpr ((k) == B200TFHE_TMEM_STAGGER) { if (q != TM_CTS - 1 || i != n - 1) named_bar_arrive(bar_next, 128); }
+#endif
+#ifndef RELEASE_POINT
+#define RELEASE_POINT(k)
+#endif
         const int a = ahat[i];
         const cplx *ggsw_i = bsk + (size_t)i * C::GGSW_CPLX;
-        cplx x[R];
+        const uint32_t t_mine = t_quad + (uint32_t)((i & 1) * 256 + r * 128);
+        const uint32_t t_other = t_quad + (uint32_t)((i & 1) * 256 + (1 - r) * 128);
+        cplx F[R];
         {
             int32_t dre[1][R], dim[1][R];
-            C::digits(lane, acc_r, a, dre, dim);
-            C::template digits_to_cplx<0>(dre, dim, x);
+            constexpr int REL = B200TFHE_TMEM_STAGGER > 0 ? B200TFHE_TMEM_STAGGER : 0;   // points done before the release
+            C::template digits_range<0, REL>(lane, acc_r, a, dre, dim);
+            RELEASE_POINT(B200TFHE_TMEM_STAGGER)
+            C::template digits_range<REL, R>(lane, acc_r, a, dre, dim);
+            C::template digits_to_cplx<0>(dre, dim, F);
         }
-        FFT::fwd_pass1_compute(lane, x, twf);
-        // forward transpose through the shared region: team 0, then team 1
-        if (r == 1) named_bar_sync(bar_x, 64);
-        FFT::pass1_store(lane, x, region);
-        __syncwarp();
-        FFT::fwd_pass2_load(lane, x, region);
-        __syncwarp();
-        if (r == 0) named_bar_sync(bar_x, 64);
+        FFT::fwd_pass1_compute(lane, F, twf);
+        transpose_split<R>(lane, F, hreg);
         cplx g[CH];
         C::template own_chunk_load<0>(lane, r, ggsw_i, g);      // key loads in flight during the second radix-32 pass
-        FFT::fwd_pass2_compute(x);                              // x[p] = D_r at Fourier position p
-        // D_r -> tensor memory, in register order pp (position brev(pp)) so that the reader's chunks are contiguous columns
-        cplx F[R];
-        static_for<0, R>([&](auto pp) { F[decltype(pp)::value] = x[brev(decltype(pp)::value, FFT::LOGR)]; });
+        FFT::fwd_pass2_compute(F);                              // F[p] = D_r at Fourier position p*R + lane
+        // D_r -> tensor memory in register order pp (position brev(pp)), so that the reader's chunks are contiguous columns
         static_for<0, 4>([&](auto part) {
             uint32_t v[32];
             static_for<0, 8>([&](auto e) {
-                constexpr int pp = decltype(part)::value * 8 + decltype(e)::value;
-                v[4 * decltype(e)::value + 0] = (uint32_t)__double2loint(F[pp].re);
-                v[4 * decltype(e)::value + 1] = (uint32_t)__double2hiint(F[pp].re);
-                v[4 * decltype(e)::value + 2] = (uint32_t)__double2loint(F[pp].im);
-                v[4 * decltype(e)::value + 3] = (uint32_t)__double2hiint(F[pp].im);
+                constexpr int pos = brev(decltype(part)::value * 8 + decltype(e)::value, FFT::LOGR);
+                v[4 * decltype(e)::value + 0] = (uint32_t)__double2loint(F[pos].re);
+                v[4 * decltype(e)::value + 1] = (uint32_t)__double2hiint(F[pos].re);
+                v[4 * decltype(e)::value + 2] = (uint32_t)__double2loint(F[pos].im);
+                v[4 * decltype(e)::value + 3] = (uint32_t)__double2hiint(F[pos].im);
             });
             tmem_st32(t_mine + decltype(part)::value * 32, v);
         });
-        // own key row, register to register (F currently holds D_r in register order)
+        // own key row, register to register and in place: Y[pp] = G[r][r][brev(pp)] * D_r[brev(pp)]
+        cplx Y[R];
         {
             cplx xb[R];
-            static_for<0, R>([&](auto pp) { xb[decltype(pp)::value] = F[decltype(pp)::value]; });
-            C::template own_chunk_apply<0>(xb, g, F);
+            static_for<0, R>([&](auto pp) { xb[decltype(pp)::value] = F[brev(decltype(pp)::value, FFT::LOGR)]; });
+            C::template own_chunk_apply<0>(xb, g, Y);
             C::template own_chunk_load<1>(lane, r, ggsw_i, g);
-            C::template own_chunk_apply<1>(xb, g, F);
+            C::template own_chunk_apply<1>(xb, g, Y);
         }
         cplx h[CH];
         C::template other_chunk_load<0>(lane, 1 - r, r, ggsw_i, h);   // in flight across the barrier
@@ -165,23 +207,16 @@ blind_rotate_tmem_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const 
                 constexpr int pp = decltype(part)::value * 8 + decltype(e)::value;
                 cplx d{__hiloint2double((int)v[4 * decltype(e)::value + 1], (int)v[4 * decltype(e)::value + 0]),
                        __hiloint2double((int)v[4 * decltype(e)::value + 3], (int)v[4 * decltype(e)::value + 2])};
-                C::mac_one(F[pp], h[pp % CH], d);
+                C::mac_one(Y[pp], h[pp % CH], d);
             });
         });
-        tmem_fence_before();
-        named_bar_sync(bar_ct, 64);      // the other team has read my D: next iteration may overwrite it; also orders
-        tmem_fence_after();              // team 1's forward use of `region` before team 0's inverse use
-        FFT::inv_pass1_compute(lane, F, twi);
-        if (r == 1) named_bar_sync(bar_x, 64);
-        FFT::pass1_store(lane, F, region);
-        __syncwarp();
-        cplx y[R];
-        static_for<0, R>([&](auto p) { y[decltype(p)::value] = region[lane * FFT::ROW + brev(decltype(p)::value, FFT::LOGR)]; });
-        __syncwarp();
-        if (r == 0) named_bar_sync(bar_x, 64);
-        fft_dit<R, +1>(y);
+        // no second barrier: the slots are double-buffered, and the next write of THIS buffer (iteration i+2) comes after
+        // the barrier of iteration i+1, which the other team reaches only after these reads
+        FFT::inv_pass1_compute(lane, Y, twi);
+        transpose_split<R>(lane, Y, hreg);
+        fft_dit<R, +1>(Y);
         static_for<0, R>([&](auto m) {
-            cplx t = cmul_root<-decltype(m)::value * FFT::TWQ>(y[decltype(m)::value]);
+            cplx t = cmul_root<-decltype(m)::value * FFT::TWQ>(Y[decltype(m)::value]);
             const int c = lane + R * decltype(m)::value;
             acc_r[c] += torus_from_double<T>(t.re);
             acc_r[c + C::M] += torus_from_double<T>(t.im);
@@ -189,8 +224,9 @@ blind_rotate_tmem_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const 
         __syncwarp();
     }
 
+    tmem_fence_before();
     __syncthreads();
-    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TM_COLS));
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base_smem), "n"(TM_COLS));
     if (!live) return;
     T *o = out + (size_t)ct * out_stride;
     if (mode == BR_MODE_GLWE) {
@@ -214,7 +250,7 @@ int br_tmem_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
     typedef BRCore<uint64_t, 32, 1, 1, 23> C;
     auto kern = blind_rotate_tmem_kernel<uint64_t, 23>;
     size_t ahat = (((size_t)(a.n + 1) * sizeof(uint16_t)) + 15) & ~(size_t)15;
-    size_t smem = TM_CTS * ((size_t)C::REGION * sizeof(cplx) + (size_t)2 * C::N * sizeof(uint64_t) + ahat) + sizeof(TwTables<32>);
+    size_t smem = TM_CTS * ((size_t)2 * 32 * 17 * sizeof(cplx) + (size_t)2 * C::N * sizeof(uint64_t) + ahat) + sizeof(TwTables<32>);
     static size_t configured = 0;
     if (smem > configured) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

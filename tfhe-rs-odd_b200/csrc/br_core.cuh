@@ -58,7 +58,11 @@ template <typename T, int R, int K, int L, int BASE_LOG> struct BRCore {
         });
     }
     HD static void digits(int lane, const T *acc_r, int a, int32_t (&dre)[L][R], int32_t (&dim)[L][R]) {
-        static_for<0, R>([&](auto p) {
+        digits_range<0, R>(lane, acc_r, a, dre, dim);
+    }
+    template <int P0, int P1>
+    HD static void digits_range(int lane, const T *acc_r, int a, int32_t (&dre)[L][R], int32_t (&dim)[L][R]) {
+        static_for<P0, P1>([&](auto p) {
             constexpr int m = brev(decltype(p)::value, FFT::LOGR);
             const int c = lane + R * m;
             T d0 = rot_read<T, N>(acc_r, c, a) - acc_r[c];
