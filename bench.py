@@ -301,7 +301,9 @@ def main():
         "latency": {"what": "single KS+PBS (batch 1), device-resident, CUDA events", "p50_ms": lat[len(lat) // 2],
                     "p99_ms": lat[min(len(lat) - 1, int(len(lat) * 0.99))], "samples": len(lat),
                     "reference_published_ms": 16.6},
-        "roofline": {"bound": "fp64", "kernel": "blind_rotate_kernel", "achieved": achieved, "peak": tf.value, "unit": "TFLOP/s",
+        "roofline": {"bound": "fp64",
+                     "kernel": ("blind_rotate_tmem_kernel" if args.batch >= 4 * 148 and not os.environ.get("B200TFHE_NO_TMEM")
+                                else "blind_rotate_kernel"), "achieved": achieved, "peak": tf.value, "unit": "TFLOP/s",
                      "frac": achieved / tf.value if tf.value else None, "traffic": None,
                      "peak_source": "live b200tfhe_probe_fp64_tflops (MEASURED_PEAKS.json has no FP64 figure)",
                      "flop_per_pbs": fl, "ms_per_launch": ms_br, "pbs_per_s_kernel_only": B / (ms_br * 1e-3),

@@ -17,6 +17,8 @@
 // tensor-core instruction is involved: TMEM is a 256 KB per-SM scratchpad that costs no shared-memory capacity or bandwidth.
 #include "br_core.cuh"
 #include "kernels.h"
+#include <cstdio>
+#include <cstdlib>
 
 namespace b200tfhe {
 
@@ -67,6 +69,20 @@ template <int R> DEV void transpose_split(int lane, cplx (&x)[R], cplx *hreg) {
     });
     __syncwarp();
 }
+
+// (P * X^a)[c] - own for a 64-bit torus and ONE decomposition level, returned as the double value of the balanced digit.
+// s8 = 8 * (c - a): bits 3..13 address the coefficient, bit 14 is the sign (X^N = -1).  Closed form of
+// BRCore::single_level_digit (exhaustively identical over all 2^32 upper words; the lower word only matters through the
+// borrow of the subtraction):  w = (2^31 + 2^sh - 1 - d_hi) >> (sh + 1),  digit = B/2 - w,  sh = 32 - BASE_LOG - 1.
+template <int BASE_LOG> DEV double rot_digit_f64(const unsigned char *acc_bytes, uint32_t s8, uint64_t own) {
+    constexpr int SH = 32 - BASE_LOG - 1;
+    const uint64_t v = *reinterpret_cast<const uint64_t *>(acc_bytes + (s8 & 0x3FF8u));
+    const uint32_t neg = (s8 >> 14) & 1u;
+    const uint32_t m = 0u - neg;
+    const uint64_t d = (v ^ (((uint64_t)m << 32) | m)) + (uint64_t)neg - own;
+    const uint32_t w = (0x80000000u + (1u << SH) - 1u - (uint32_t)(d >> 32)) >> (SH + 1);
+    return (4503599627370496.0 + (double)(1u << (BASE_LOG - 1))) - __hiloint2double(0x43300000, (int)w);
+}
 #endif
 
 // Iteration alignment of the 4 ciphertexts of a CTA:
@@ -76,8 +92,23 @@ template <int R> DEV void transpose_split(int lane, cplx (&x)[R], cplx *hreg) {
 //   k>0 STAGGERED ring: ciphertext q starts iteration i when ciphertext q-1 has decomposed k of its 32 points of iteration
 //      i (and 0 waits for 3 of iteration i-1).  The streams stay a few hundred instructions apart (inside the 32 KB L1.5
 //      instruction cache) while the load/store bursts of one ciphertext overlap the FP64 phases of the others.
+#ifndef B200TFHE_TMEM_PREFETCH
+#define B200TFHE_TMEM_PREFETCH 2
+#endif
 #ifndef B200TFHE_TMEM_STAGGER
 #define B200TFHE_TMEM_STAGGER 8
+#endif
+
+// Debug build only (-DB200TFHE_TMEM_TRACE): CTA 0 records %clock64 at the phase boundaries of a few iterations; the
+// launcher dumps them to the file named by B200TFHE_TRACE_FILE (see tools/tmem_trace.py).
+#ifdef B200TFHE_TMEM_TRACE
+constexpr int TR_IT = 6, TR_I0 = 300, TR_ST = 12;
+__device__ unsigned long long g_tmem_trace[8][TR_IT][TR_ST];
+#define STAMP(k) \
+    if (blockIdx.x == 0 && lane == 0 && i >= TR_I0 && i < TR_I0 + TR_IT) { \
+        unsigned long long t_; asm volatile("mov.u64 %0, %%clock64;" : "=l"(t_)::"memory"); g_tmem_trace[warp][i - TR_I0][k] = t_; }
+#else
+#define STAMP(k)
 #endif
 
 constexpr int TM_CTS = 4;        // ciphertexts per CTA
@@ -143,33 +174,55 @@ blind_rotate_tmem_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const 
     if (q == TM_CTS - 1) named_bar_arrive(bar_next, 128);     // lets ciphertext 0 into iteration 0
 #endif
 
+    // The thread's own 64 updated coefficients stay in registers from the accumulate step to the decomposition that follows
+    // it (they are re-read from shared memory one iteration later; the other lanes read them rotated).
+    T own_re[R], own_im[R];
+    static_for<0, R>([&](auto m) {
+        own_re[decltype(m)::value] = acc_r[lane + R * decltype(m)::value];
+        own_im[decltype(m)::value] = acc_r[lane + R * decltype(m)::value + C::M];
+    });
+    const unsigned char *acc_bytes = reinterpret_cast<const unsigned char *>(acc_r);
     for (int i = 0; i < n; i++) {
+        // decomposition of acc*X^a_i - acc at this lane's 32 folded points -> F (doubles), with the ring alignment inside
+        cplx F[R];
+        STAMP(0)
 #if B200TFHE_TMEM_STAGGER < 0
         __syncthreads();
 #elif B200TFHE_TMEM_STAGGER > 0
         named_bar_sync(bar_top, 128);
-#define RELEASE_POINT(k) if constexpr ((k) == B200TFHE_TMEM_STAGGER) { if (q != TM_CTS - 1 || i != n - 1) named_bar_arrive(bar_next, 128); }
 #endif
-#ifndef RELEASE_POINT
-#define RELEASE_POINT(k)
+        STAMP(1)
+        const uint32_t base8 = (uint32_t)(lane - (int)ahat[i]) << 3;      // byte offset of coefficient (lane - a); bit 14 = sign
+        static_for<0, R>([&](auto p) {
+            constexpr int m = brev(decltype(p)::value, FFT::LOGR);
+#if B200TFHE_TMEM_STAGGER > 0
+            if constexpr (decltype(p)::value == B200TFHE_TMEM_STAGGER) {
+                if (q != TM_CTS - 1 || i != n - 1) named_bar_arrive(bar_next, 128);
+            }
 #endif
-        const int a = ahat[i];
+            if constexpr (decltype(p)::value % 4 == 0) asm volatile("" ::: "memory");   // bounds the loads in flight (registers)
+            F[decltype(p)::value] = cplx{rot_digit_f64<BL>(acc_bytes, base8 + 8u * R * m, own_re[m]),
+                                         rot_digit_f64<BL>(acc_bytes, base8 + 8u * R * m + 8u * C::M, own_im[m])};
+        });
         const cplx *ggsw_i = bsk + (size_t)i * C::GGSW_CPLX;
         const uint32_t t_mine = t_quad + (uint32_t)((i & 1) * 256 + r * 128);
         const uint32_t t_other = t_quad + (uint32_t)((i & 1) * 256 + (1 - r) * 128);
-        cplx F[R];
-        {
-            int32_t dre[1][R], dim[1][R];
-            constexpr int REL = B200TFHE_TMEM_STAGGER > 0 ? B200TFHE_TMEM_STAGGER : 0;   // points done before the release
-            C::template digits_range<0, REL>(lane, acc_r, a, dre, dim);
-            RELEASE_POINT(B200TFHE_TMEM_STAGGER)
-            C::template digits_range<REL, R>(lane, acc_r, a, dre, dim);
-            C::template digits_to_cplx<0>(dre, dim, F);
-        }
+        STAMP(2)
         FFT::fwd_pass1_compute(lane, F, twf);
+        asm volatile("" : "+d"(F[0].re), "+d"(F[31].im));
+        STAMP(3)
         transpose_split<R>(lane, F, hreg);
+        STAMP(4)
         cplx g[CH];
         C::template own_chunk_load<0>(lane, r, ggsw_i, g);      // key loads in flight during the second radix-32 pass
+#if B200TFHE_TMEM_PREFETCH == 5
+        if (q == 0) { C::template chunk_prefetch<1>(lane, r, r, ggsw_i); C::template chunk_prefetch<0>(lane, 1 - r, r, ggsw_i); }
+#elif B200TFHE_TMEM_PREFETCH >= 1
+        C::template chunk_prefetch<1>(lane, r, r, ggsw_i);
+#endif
+#if B200TFHE_TMEM_PREFETCH >= 2 && B200TFHE_TMEM_PREFETCH != 5
+        C::template chunk_prefetch<0>(lane, 1 - r, r, ggsw_i);
+#endif
         FFT::fwd_pass2_compute(F);                              // F[p] = D_r at Fourier position p*R + lane
         // D_r -> tensor memory in register order pp (position brev(pp)), so that the reader's chunks are contiguous columns
         static_for<0, 4>([&](auto part) {
@@ -194,10 +247,18 @@ blind_rotate_tmem_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const 
         }
         cplx h[CH];
         C::template other_chunk_load<0>(lane, 1 - r, r, ggsw_i, h);   // in flight across the barrier
+#if B200TFHE_TMEM_PREFETCH == 3
+        C::template chunk_prefetch<1>(lane, 1 - r, r, ggsw_i);
+#endif
         tmem_wait_st();
         tmem_fence_before();
+        STAMP(5)
         named_bar_sync(bar_ct, 64);
         tmem_fence_after();
+#if B200TFHE_TMEM_PREFETCH == 4
+        C::template chunk_prefetch<1>(lane, 1 - r, r, ggsw_i);
+#endif
+        STAMP(6)
         static_for<0, 4>([&](auto part) {
             if constexpr (decltype(part)::value == 2) C::template other_chunk_load<1>(lane, 1 - r, r, ggsw_i, h);
             uint32_t v[32];
@@ -208,20 +269,31 @@ blind_rotate_tmem_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const 
                 cplx d{__hiloint2double((int)v[4 * decltype(e)::value + 1], (int)v[4 * decltype(e)::value + 0]),
                        __hiloint2double((int)v[4 * decltype(e)::value + 3], (int)v[4 * decltype(e)::value + 2])};
                 C::mac_one(Y[pp], h[pp % CH], d);
+                asm volatile("" : "+d"(Y[pp].re), "+d"(Y[pp].im));   // consume this part before the next tcgen05.ld (registers)
             });
         });
         // no second barrier: the slots are double-buffered, and the next write of THIS buffer (iteration i+2) comes after
         // the barrier of iteration i+1, which the other team reaches only after these reads
+        STAMP(7)
         FFT::inv_pass1_compute(lane, Y, twi);
+        asm volatile("" : "+d"(Y[0].re), "+d"(Y[31].im));
+        STAMP(8)
         transpose_split<R>(lane, Y, hreg);
+        STAMP(9)
         fft_dit<R, +1>(Y);
+        asm volatile("" : "+d"(Y[0].re), "+d"(Y[31].im));
+        STAMP(10)
         static_for<0, R>([&](auto m) {
             cplx t = cmul_root<-decltype(m)::value * FFT::TWQ>(Y[decltype(m)::value]);
             const int c = lane + R * decltype(m)::value;
-            acc_r[c] += torus_from_double<T>(t.re);
-            acc_r[c + C::M] += torus_from_double<T>(t.im);
+            if constexpr (decltype(m)::value % 4 == 0) asm volatile("" ::: "memory");
+            own_re[decltype(m)::value] = acc_r[c] + torus_from_double<T>(t.re);
+            own_im[decltype(m)::value] = acc_r[c + C::M] + torus_from_double<T>(t.im);
+            acc_r[c] = own_re[decltype(m)::value];
+            acc_r[c + C::M] = own_im[decltype(m)::value];
         });
         __syncwarp();
+        STAMP(11)
     }
 
     tmem_fence_before();
@@ -261,6 +333,22 @@ int br_tmem_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
     kern<<<grid, TM_CTS * 64, smem, st>>>((const uint64_t *)a.lwe_in, a.lwe_stride, (const uint64_t *)a.luts, a.lut_idx,
                                          (const cplx *)a.bsk, (uint64_t *)a.out, a.out_stride, a.n, a.batch, a.mode,
                                          (const cplx *)a.tw_fwd, (const cplx *)a.tw_inv);
+#ifdef B200TFHE_TMEM_TRACE
+    if (const char *f = getenv("B200TFHE_TRACE_FILE")) {
+        static unsigned long long host[8][TR_IT][TR_ST];
+        cudaStreamSynchronize(st);
+        cudaMemcpyFromSymbol(host, g_tmem_trace, sizeof(host));
+        if (FILE *fp = fopen(f, "w")) {
+            for (int w = 0; w < 8; w++)
+                for (int it = 0; it < TR_IT; it++) {
+                    fprintf(fp, "%d %d", w, it);
+                    for (int k = 0; k < TR_ST; k++) fprintf(fp, " %llu", host[w][it][k]);
+                    fprintf(fp, "\n");
+                }
+            fclose(fp);
+        }
+    }
+#endif
     return (int)cudaGetLastError();
 }
 

@@ -174,6 +174,17 @@ template <typename T, int R, int K, int L, int BASE_LOG> struct BRCore {
             F[pp] = cmul(xb[pp], g[decltype(i)::value]);
         });
     }
+#if defined(__CUDA_ARCH__)
+    // L1 prefetch of the 8 KB chunk HALF of key row (r, j): 64 lines, two per lane
+    template <int HALF> DEV static void chunk_prefetch(int lane, int r, int j, const cplx *ggsw) {
+        const cplx *row = ggsw + ((size_t)r * K1 + j) * M;
+        static_for<0, CH / 8>([&](auto h) {
+            const int pp = HALF * CH + decltype(h)::value * 8 + (lane >> 2);
+            const int pos = (int)(__brev((unsigned)pp) >> (32 - FFT::LOGR));
+            prefetch_l1(reinterpret_cast<const char *>(row + pos * R) + (lane & 3) * 128);
+        });
+    }
+#endif
     template <int HALF> HD static void other_chunk_load(int lane, int r, int j, const cplx *ggsw, cplx (&h)[CH]) {
         const cplx *row = ggsw + ((size_t)r * K1 + j) * M;
         static_for<0, CH>([&](auto i) {
