@@ -49,6 +49,28 @@ def test_keyswitch_bit_exact(ctx, name):
     assert t.keyswitch_lwe_ciphertext(ksk, np.zeros((0, o.big + 1), _dt(o))).shape == (0, o.n + 1)
 
 
+@pytest.mark.parametrize("name", ["TOY_U64", "TOY_U32", "TOY_1_1", "TOY_3_3", "MESSAGE_2_CARRY_2", "BOOLEAN_DEFAULT"])
+def test_keyswitch_tensor_core_path_bit_exact(ctx, name):
+    """Batches of >= 64 ciphertexts take the tcgen05 kind::i8 kernel (digits x byte planes of the key): same bits as the
+    oracle, ragged against the 128-row tile, with all-zero / all-one / sign-boundary rows."""
+    import tfhe_rs_odd_b200 as t
+    o = get_oracle(name)
+    p, bsk, ksk = _keys(ctx, o)
+    rng = np.random.default_rng(11)
+    B = 150 if o.big <= 2048 else 70
+    cts = rng.integers(0, 2 ** o.bits, size=(B, o.big + 1), dtype=np.uint64)
+    cts[0, :] = 0
+    cts[1, :] = (1 << o.bits) - 1
+    cts[2, :] = 1 << (o.bits - 1)
+    cts[3, :] = (1 << (o.bits - 1)) - 1
+    ref = o.keyswitch(cts)
+    got = t.keyswitch_lwe_ciphertext(ksk, cts.astype(_dt(o)))
+    assert np.array_equal(got.astype(np.uint64), ref)
+    # the small-batch kernel and the tensor-core kernel agree with each other bit for bit
+    small = t.keyswitch_lwe_ciphertext(ksk, cts[:40].astype(_dt(o)))
+    assert np.array_equal(small, got[:40])
+
+
 @pytest.mark.parametrize("bits,N", [(64, 2048), (64, 512), (32, 512), (64, 8192)])
 def test_modswitch_and_sample_extract_bit_exact(ctx, bits, N):
     import tfhe_rs_odd_b200 as t

@@ -8,6 +8,7 @@
 #include <string>
 #include <vector>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 using namespace b200tfhe;
@@ -15,7 +16,7 @@ using namespace b200tfhe;
 static thread_local std::string g_global_err = "";
 
 struct Workspace {
-    enum { IN = 0, OUT, MID, LUTS, IDX, A, B, NSLOTS };
+    enum { IN = 0, OUT, MID, LUTS, IDX, A, B, DIG, NSLOTS };
     void *ptr[NSLOTS] = {};
     size_t cap[NSLOTS] = {};
     cudaError_t get(int slot, size_t bytes, void **out) {
@@ -62,6 +63,7 @@ struct b200tfhe_ksk {
     void *d_ksk, *d_colsum;
     size_t bytes;
     bool finalized;
+    KSTensorKey tk;      // byte-plane copy of the key for the tensor-core path (d_planes == nullptr: not available)
 };
 
 static int fail(b200tfhe_context *ctx, const std::string &msg) {
@@ -256,7 +258,7 @@ int b200tfhe_ksk_alloc(b200tfhe_context *ctx, const b200tfhe_params *pp, b200tfh
     std::lock_guard<std::mutex> g(ctx->mu);
     CK(cudaSetDevice(ctx->device));
     size_t bytes = (size_t)p.k * p.N * p.ks_level * small_len(p) * sz(p);
-    b200tfhe_ksk *k = new b200tfhe_ksk{ctx, p, nullptr, nullptr, bytes, false};
+    b200tfhe_ksk *k = new b200tfhe_ksk{ctx, p, nullptr, nullptr, bytes, false, {}};
     cudaError_t e = cudaMalloc(&k->d_ksk, bytes);
     if (e == cudaSuccess) e = cudaMalloc(&k->d_colsum, small_len(p) * sz(p));
     if (e != cudaSuccess) { cudaFree(k->d_ksk); delete k; return fail_cuda(ctx, "cudaMalloc(ksk)", e); }
@@ -270,6 +272,15 @@ int b200tfhe_ksk_finalize(b200tfhe_context *ctx, b200tfhe_ksk *k) {
     int rc = ks_colsum_launch(k->d_ksk, k->d_colsum, k->p.k * k->p.N, k->p.n, k->p.ks_level, k->p.ks_base_log, k->p.bits, ctx->stream);
     ctx->launches++;
     if (rc) return fail(ctx, "ks_colsum launch failed: " + std::to_string(rc));
+    const int n_in = k->p.k * k->p.N;
+    if (!getenv("B200TFHE_NO_KS_TC") && ks_tc_supported(k->p.bits, n_in, k->p.n, k->p.ks_level, k->p.ks_base_log)) {
+        if (k->tk.d_planes) { cudaFree(k->tk.d_planes); k->tk.d_planes = nullptr; }
+        void *planes = nullptr;
+        CK(cudaMalloc(&planes, ks_tc_key_bytes(k->p.bits, n_in, k->p.n, k->p.ks_level)));
+        rc = ks_tc_prepare_key(&k->tk, k->d_ksk, planes, k->p.bits, n_in, k->p.n, k->p.ks_level, ctx->stream);
+        ctx->launches++;
+        if (rc) { cudaFree(planes); k->tk.d_planes = nullptr; return fail(ctx, "ks_tc_prepare_key failed: " + std::to_string(rc)); }
+    }
     CK(cudaStreamSynchronize(ctx->stream));
     k->finalized = true;
     return 0;
@@ -297,6 +308,7 @@ int b200tfhe_ksk_destroy(b200tfhe_ksk *ksk) {
     cudaSetDevice(ksk->ctx->device);
     cudaFree(ksk->d_ksk);
     cudaFree(ksk->d_colsum);
+    if (ksk->tk.d_planes) cudaFree(ksk->tk.d_planes);
     delete ksk;
     return 0;
 }
@@ -308,8 +320,17 @@ static int ks_dev_locked(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const v
     REQUIRE(ksk->finalized, "keyswitch: key not finalized (call b200tfhe_ksk_finalize after filling the device buffer)");
     const Params &p = ksk->p;
     KSLaunch a{d_in, big_len(p), d_out, small_len(p), ksk->d_ksk, ksk->d_colsum, p.k * p.N, p.n, p.ks_level, p.ks_base_log, p.bits, (int)batch};
-    int rc = ks_launch(a, ctx->stream);
-    ctx->launches++;
+    static const int tc_min = getenv("B200TFHE_KS_TC_MIN") ? atoi(getenv("B200TFHE_KS_TC_MIN")) : 64;
+    int rc;
+    if (ksk->tk.d_planes && (int)batch >= tc_min) {
+        void *digits = nullptr;
+        CK(ctx->ws.get(Workspace::DIG, (size_t)batch * ksk->tk.kp, &digits));
+        rc = ks_tc_launch(a, ksk->tk, digits, ctx->stream);
+        ctx->launches += 2;
+    } else {
+        rc = ks_launch(a, ctx->stream);
+        ctx->launches++;
+    }
     if (rc) return fail(ctx, "keyswitch launch failed: " + std::to_string(rc));
     return 0;
 }

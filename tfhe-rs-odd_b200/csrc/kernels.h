@@ -44,6 +44,18 @@ struct KSLaunch {
 int ks_launch(const KSLaunch &a, cudaStream_t st);
 int ks_colsum_launch(const void *ksk, void *colsum, int n_in, int n_out, int level, int base_log, int bits, cudaStream_t st);
 
+// keyswitch_tc.cu (tcgen05 kind::i8 path: digits x byte-planes of the key)
+struct KSTensorKey {
+    void *d_planes = nullptr;              // [(n_out+1) * W/8][kp] bytes, kp = padded n_in * level
+    size_t kp = 0;
+    alignas(64) unsigned char map_b[128];  // CUtensorMap of d_planes (opaque here: kernels.h does not include cuda.h)
+};
+int ks_tc_supported(int bits, int n_in, int n_out, int level, int base_log);
+size_t ks_tc_padded_k(int n_in, int level);
+size_t ks_tc_key_bytes(int bits, int n_in, int n_out, int level);
+int ks_tc_prepare_key(KSTensorKey *tk, const void *ksk, void *planes, int bits, int n_in, int n_out, int level, cudaStream_t st);
+int ks_tc_launch(const KSLaunch &a, const KSTensorKey &tk, void *digits, cudaStream_t st);   // digits: batch * kp bytes of scratch
+
 // misc_kernels.cu
 int modswitch_launch(const void *in, uint32_t *out, size_t count, int log2N, int bits, cudaStream_t st);
 int sample_extract_launch(const void *glwe, void *lwe, int k, int N, int batch, int bits, cudaStream_t st);
