@@ -250,7 +250,7 @@ def main():
     sampler.start()
     ms_total = timed(step_dev, args.steps, args.warmup)
     clocks = sampler.stop()
-    launches = ctx.launch_count - l0 - 2 * args.warmup
+    launches = (ctx.launch_count - l0) // (args.steps + args.warmup) * args.steps   # kernels of the timed steps only
     ms_e2e = timed(step_e2e, args.steps, args.warmup)
     br_steps = max(2, min(args.steps, 3))
     ms_br = timed(step_br, br_steps, 1) / br_steps

@@ -51,8 +51,8 @@ def test_keyswitch_bit_exact(ctx, name):
 
 @pytest.mark.parametrize("name", ["TOY_U64", "TOY_U32", "TOY_1_1", "TOY_3_3", "MESSAGE_2_CARRY_2", "BOOLEAN_DEFAULT"])
 def test_keyswitch_tensor_core_path_bit_exact(ctx, name):
-    """Batches of >= 64 ciphertexts take the tcgen05 kind::i8 kernel (digits x byte planes of the key): same bits as the
-    oracle, ragged against the 128-row tile, with all-zero / all-one / sign-boundary rows."""
+    """The tcgen05 kind::i8 keyswitch (digits x byte planes of the key): same bits as the oracle on a batch that is ragged
+    against the 128-row tile, with all-zero / all-one / sign-boundary rows."""
     import tfhe_rs_odd_b200 as t
     o = get_oracle(name)
     p, bsk, ksk = _keys(ctx, o)
@@ -66,9 +66,19 @@ def test_keyswitch_tensor_core_path_bit_exact(ctx, name):
     ref = o.keyswitch(cts)
     got = t.keyswitch_lwe_ciphertext(ksk, cts.astype(_dt(o)))
     assert np.array_equal(got.astype(np.uint64), ref)
-    # the small-batch kernel and the tensor-core kernel agree with each other bit for bit
     small = t.keyswitch_lwe_ciphertext(ksk, cts[:40].astype(_dt(o)))
     assert np.array_equal(small, got[:40])
+
+
+def test_keyswitch_cuda_core_kernel_bit_exact():
+    """The integer-pipe keyswitch kernel (kept for parameter sets the tensor-core path does not cover) stays bit-exact:
+    run the keyswitch test in a child process with the tensor-core path disabled."""
+    import subprocess, sys, os
+    env = dict(os.environ, B200TFHE_NO_KS_TC="1")
+    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-m", "gpu", __file__, "-k",
+                        "test_keyswitch_bit_exact and (TOY_U64 or TOY_U32 or MESSAGE_2_CARRY_2)"],
+                       env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
 
 
 @pytest.mark.parametrize("bits,N", [(64, 2048), (64, 512), (32, 512), (64, 8192)])

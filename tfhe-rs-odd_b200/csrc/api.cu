@@ -320,7 +320,7 @@ static int ks_dev_locked(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const v
     REQUIRE(ksk->finalized, "keyswitch: key not finalized (call b200tfhe_ksk_finalize after filling the device buffer)");
     const Params &p = ksk->p;
     KSLaunch a{d_in, big_len(p), d_out, small_len(p), ksk->d_ksk, ksk->d_colsum, p.k * p.N, p.n, p.ks_level, p.ks_base_log, p.bits, (int)batch};
-    static const int tc_min = getenv("B200TFHE_KS_TC_MIN") ? atoi(getenv("B200TFHE_KS_TC_MIN")) : 64;
+    static const int tc_min = getenv("B200TFHE_KS_TC_MIN") ? atoi(getenv("B200TFHE_KS_TC_MIN")) : 1;
     int rc;
     if (ksk->tk.d_planes && (int)batch >= tc_min) {
         void *digits = nullptr;
