@@ -32,6 +32,10 @@ PARAMS = {
     "TOY_2_2": (12, 1, 2048, 23, 1, 3, 5, 64, 1e-9, 0.00000000000000029403601535432533, 16, "ks_pbs"),
     "TOY_3_3": (6, 1, 8192, 15, 2, 3, 6, 64, 1e-9, 0.0000000000000000002168404344971009, 64, "ks_pbs"),
     "TOY_1_1": (12, 3, 512, 18, 1, 4, 3, 64, 1e-9, 0.0000000000034525330484572114, 4, "ks_pbs"),
+    # the sets of the committed golden fixtures (tests/golden/): n = 4 keeps the stored keys small
+    "GOLD_U64": (4, 1, 512, 12, 2, 4, 4, 64, 1e-9, 1e-15, 4, "ks_pbs"),
+    "GOLD_U32": (4, 2, 512, 6, 3, 3, 4, 32, 1e-7, 1e-8, 0, "pbs_ks"),
+    "GOLD_2_2": (4, 1, 2048, 23, 1, 3, 5, 64, 1e-9, 0.00000000000000029403601535432533, 16, "ks_pbs"),
 }
 
 
@@ -106,6 +110,13 @@ class Oracle:
         if fourier:
             self.fbsk = np.zeros(self.bsk.size, np.float64)
             L.orc_bsk_to_fourier(C.byref(self.p), _p(self.bsk), _p(self.fbsk), self.nthreads)
+        return self
+
+    def load_keys(self, small_key, glwe_key, ksk, bsk):
+        """Install externally stored keys (golden fixtures) instead of generating them."""
+        self.small_key, self.glwe_key, self.ksk, self.bsk = u64(small_key), u64(glwe_key), u64(ksk), u64(bsk)
+        self.fbsk = np.zeros(self.bsk.size, np.float64)
+        lib().orc_bsk_to_fourier(C.byref(self.p), _p(self.bsk), _p(self.fbsk), self.nthreads)
         return self
 
     # ---- ciphertexts ------------------------------------------------------------------------

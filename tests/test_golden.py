@@ -1,0 +1,103 @@
+"""Committed golden vectors (tests/golden/ks_pbs_golden.npz, written by tests/golden/make_golden.py).
+
+CPU half (`-m "not gpu"`): the oracle, loaded with the STORED keys, still reproduces every stored output -- integer stages
+bit for bit, PBS outputs by decrypted message and by phase within the analytic bound (the f64 FFT of a rebuilt oracle may
+round differently on another host).  GPU half (`-m gpu`): the CUDA path through the C ABI on the same stored bytes.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import params_of, phase_bound
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ks_pbs_golden.npz")
+SHORTINT_SETS = ["GOLD_2_2", "GOLD_U64"]
+
+
+@pytest.fixture(scope="module")
+def z():
+    return np.load(GOLD)
+
+
+def _oracle(z, name):
+    from oracle.oracle import Oracle
+    return Oracle(name).load_keys(z[f"{name}.small_key"], z[f"{name}.glwe_key"], z[f"{name}.ksk"], z[f"{name}.bsk"])
+
+
+def _phase_close(o, got_phase, ref_phase, bits):
+    d = (got_phase.astype(np.uint64) - ref_phase.astype(np.uint64))
+    if bits == 32:
+        d = (d & np.uint64(0xFFFFFFFF)).astype(np.uint32).astype(np.int32).astype(np.float64)
+    else:
+        d = d.astype(np.int64).astype(np.float64)
+    return np.abs(d).max() / 2.0 ** bits < phase_bound(o)
+
+
+# ---- CPU: oracle vs stored vectors ---------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", SHORTINT_SETS)
+def test_oracle_reproduces_golden_shortint(z, name):
+    from oracle.oracle import lib
+    o = _oracle(z, name)
+    cts = z[f"{name}.cts"]
+    ks = o.keyswitch(cts)
+    assert np.array_equal(ks, z[f"{name}.ks_out"])
+    ms = np.array([[lib().orc_modswitch(int(v), int(np.log2(o.N)), o.bits) for v in row] for row in ks], np.uint32)
+    assert np.array_equal(ms, z[f"{name}.modswitch"])
+    assert np.array_equal(np.stack([o.lut(lambda x: x), o.lut(lambda x: (3 * x + 1) % o.pmod)]), z[f"{name}.luts"])
+    out = o.ks_pbs(cts, z[f"{name}.luts"], z[f"{name}.lut_idx"])
+    ph = o.phase(out, "big")
+    assert np.array_equal(o.decode(ph) % o.pmod, z[f"{name}.ks_pbs_msgs"])
+    assert _phase_close(o, ph, z[f"{name}.ks_pbs_phase"], o.bits)
+    # rows 2.. are honest encryptions: the stored messages are LUT(msg)
+    msgs, idx = z[f"{name}.msgs"], z[f"{name}.lut_idx"]
+    exp = np.where(idx == 0, msgs, (3 * msgs + 1) % o.pmod)
+    assert np.array_equal(z[f"{name}.ks_pbs_msgs"][2:], exp[2:])
+
+
+def test_oracle_reproduces_golden_boolean(z):
+    name = "GOLD_U32"
+    o = _oracle(z, name)
+    a, b = z[f"{name}.a"].astype(np.uint64), z[f"{name}.b"].astype(np.uint64)
+    pro = o.gate_prologue(1, a, b)
+    assert np.array_equal(pro.astype(np.uint32), z[f"{name}.nand_prologue"])
+    out = o.pbs_ks(pro, o.boolean_lut())
+    bits = o.decode_bool(o.phase(out, "small"))
+    assert np.array_equal(bits, z[f"{name}.nand_bits"])
+    assert np.array_equal(bits, (1 - (z[f"{name}.a_bits"] & z[f"{name}.b_bits"])).astype(bool))
+
+
+# ---- GPU: CUDA path vs stored vectors ------------------------------------------------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", SHORTINT_SETS)
+def test_cuda_path_matches_golden_shortint(ctx, z, name):
+    import tfhe_rs_odd_b200 as t
+    o = _oracle(z, name)
+    p = params_of(o)
+    bsk = t.convert_standard_lwe_bootstrap_key_to_fourier(ctx, p, z[f"{name}.bsk"])
+    ksk = t.LweKeyswitchKey.upload(ctx, p, z[f"{name}.ksk"])
+    cts = z[f"{name}.cts"]
+    ks = t.keyswitch_lwe_ciphertext(ksk, cts)
+    assert np.array_equal(ks, z[f"{name}.ks_out"])                                     # bit-exact
+    ms = t.fast_pbs_modulus_switch(ctx, ks, o.N, 64)
+    assert np.array_equal(np.asarray(ms).reshape(ks.shape).astype(np.uint32), z[f"{name}.modswitch"])   # bit-exact
+    out = t.keyswitch_programmable_bootstrap(ksk, bsk, cts, z[f"{name}.luts"], lut_idx=z[f"{name}.lut_idx"])
+    ph = o.phase(out, "big")
+    assert np.array_equal(o.decode(ph) % o.pmod, z[f"{name}.ks_pbs_msgs"])            # decrypted values equal
+    assert _phase_close(o, ph, z[f"{name}.ks_pbs_phase"], o.bits)
+
+
+@pytest.mark.gpu
+def test_cuda_path_matches_golden_boolean(ctx, z):
+    import tfhe_rs_odd_b200 as t
+    from tfhe_rs_odd_b200 import boolean
+    name = "GOLD_U32"
+    o = _oracle(z, name)
+    p = params_of(o)
+    bsk = t.convert_standard_lwe_bootstrap_key_to_fourier(ctx, p, z[f"{name}.bsk"])
+    ksk = t.LweKeyswitchKey.upload(ctx, p, z[f"{name}.ksk"])
+    out = boolean.gate_batch(ksk, bsk, 1, z[f"{name}.a"], z[f"{name}.b"], pbs_first=True)
+    bits = o.decode_bool(o.phase(out.astype(np.uint64), "small"))
+    assert np.array_equal(bits, z[f"{name}.nand_bits"])
+    ref_ph = o.phase(z[f"{name}.nand_out"].astype(np.uint64), "small")
+    assert _phase_close(o, o.phase(out.astype(np.uint64), "small"), ref_ph, 32)

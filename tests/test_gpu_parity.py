@@ -251,3 +251,32 @@ def test_boolean_server_key_trivial_arms_and_not(ctx):
                            ("nor", sk.nor, ~(a | b)), ("xor", sk.xor, a ^ b), ("xnor", sk.xnor, ~(a ^ b))]:
         assert np.array_equal(dec(fn(ca, b)), want), name                          # encrypted, trivial
         assert np.array_equal(dec(fn(a, o.encrypt(np.where(b, T, F).astype(np.uint64), "small", seed=8).astype(np.uint32))), want), name
+
+
+def test_full_size_batch_properties(ctx):
+    """BASELINE configs[1] at full size (16384 ciphertexts, PARAM_MESSAGE_2_CARRY_2, 4 LUTs indexed per ciphertext): the
+    size at which the TMEM blind-rotation kernel and the tensor-core keyswitch run 28 waves deep.  Size-independent
+    properties: every output decrypts to LUT(msg); the keyswitch is bit-exact on a sampled subset; the result does not
+    depend on the position of a ciphertext in the batch (permutation equivariance, bit for bit); two runs are identical."""
+    import tfhe_rs_odd_b200 as t
+    o = get_oracle("MESSAGE_2_CARRY_2")
+    p, bsk, ksk = _keys(ctx, o)
+    B = 16384
+    rng = np.random.default_rng(2024)
+    msgs = rng.integers(0, o.pmod, B)
+    fs = [lambda x: x, lambda x: (x * x) % o.pmod, lambda x: (5 * x + 3) % o.pmod, lambda x: o.pmod - 1 - x]
+    luts = np.stack([o.lut(f) for f in fs])
+    idx = rng.integers(0, 4, B).astype(np.uint32)
+    cts = o.encrypt(o.encode(msgs), "big", seed=0xF00D0000)
+    out = t.keyswitch_programmable_bootstrap(ksk, bsk, cts, luts, lut_idx=idx)
+    expect = np.array([fs[i](int(m)) for i, m in zip(idx, msgs)])
+    assert np.array_equal(o.decode(o.phase(out, "big")) % o.pmod, expect)
+    # keyswitch alone, full size, bit-exact on a sampled subset (the oracle needs ~10 ms per ciphertext)
+    ks = t.keyswitch_lwe_ciphertext(ksk, cts)
+    rows = np.concatenate([[0, 1, 127, 128, B - 1], rng.integers(0, B, 43)])
+    assert np.array_equal(ks[rows], o.keyswitch(cts[rows]))
+    # position independence and run-to-run determinism
+    perm = rng.permutation(B)
+    out_p = t.keyswitch_programmable_bootstrap(ksk, bsk, cts[perm], luts, lut_idx=idx[perm])
+    assert np.array_equal(out_p, out[perm])
+    assert np.array_equal(t.keyswitch_programmable_bootstrap(ksk, bsk, cts, luts, lut_idx=idx), out)
