@@ -257,7 +257,7 @@ def main():
     ms_ks = timed(step_ks, br_steps, 1) / br_steps
     # single-PBS latency (the metric's second half): batch of ONE ciphertext through the same KS+PBS entry point
     lat = []
-    for it in range(60):
+    for it in range(210):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
         ctx.check(lib.b200tfhe_ks_pbs_batch_dev(ctx._h, ksk._h, bsk._h, VP(d_in.data_ptr()), VP(d_out.data_ptr()),
@@ -287,6 +287,15 @@ def main():
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     bsk_bytes, ksk_bytes = bbytes, kbytes
     hbm_alg = (B * (small + big) * 8 + bsk_bytes) / (ms_br * 1e-3) / 1e9   # minimum HBM traffic of one blind-rotation launch
+    br_kernel = ("blind_rotate_tmem_kernel" if args.batch >= 4 * 148 and not os.environ.get("B200TFHE_NO_TMEM")
+                 else "blind_rotate_kernel")
+    traffic = None   # DRAM bytes of one launch of that kernel, from the committed ncu capture (same kernel, same batch)
+    try:
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json"))).get(br_kernel)
+        if tr and tr["batch"] == B:
+            traffic = tr["dram_bytes_per_launch"]
+    except (OSError, ValueError, KeyError):
+        pass
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
@@ -302,9 +311,8 @@ def main():
                     "p99_ms": lat[min(len(lat) - 1, int(len(lat) * 0.99))], "samples": len(lat),
                     "reference_published_ms": 16.6},
         "roofline": {"bound": "fp64",
-                     "kernel": ("blind_rotate_tmem_kernel" if args.batch >= 4 * 148 and not os.environ.get("B200TFHE_NO_TMEM")
-                                else "blind_rotate_kernel"), "achieved": achieved, "peak": tf.value, "unit": "TFLOP/s",
-                     "frac": achieved / tf.value if tf.value else None, "traffic": None,
+                     "kernel": br_kernel, "achieved": achieved, "peak": tf.value, "unit": "TFLOP/s",
+                     "frac": achieved / tf.value if tf.value else None, "traffic": traffic,
                      "peak_source": "live b200tfhe_probe_fp64_tflops (MEASURED_PEAKS.json has no FP64 figure)",
                      "flop_per_pbs": fl, "ms_per_launch": ms_br, "pbs_per_s_kernel_only": B / (ms_br * 1e-3),
                      "hbm": {"achieved": hbm_alg, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_alg / hbm_peak,
