@@ -266,6 +266,7 @@ def main():
         torch.cuda.synchronize()
         if it >= 10:
             lat.append(e0.elapsed_time(e1))
+    lat_order = list(lat)
     lat.sort()
     tf = C.c_double()
     ctx.check(lib.b200tfhe_probe_fp64_tflops(ctx._h, C.c_double(300.0), C.byref(tf)))
@@ -308,7 +309,8 @@ def main():
                 "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": int(launches),
         "latency": {"what": "single KS+PBS (batch 1), device-resident, CUDA events", "p50_ms": lat[len(lat) // 2],
-                    "p99_ms": lat[min(len(lat) - 1, int(len(lat) * 0.99))], "samples": len(lat),
+                    "p99_ms": lat[min(len(lat) - 1, int(len(lat) * 0.99))], "min_ms": lat[0], "samples": len(lat),
+                    "first20_median_ms": sorted(lat_order[:20])[10], "last20_median_ms": sorted(lat_order[-20:])[10],
                     "reference_published_ms": 16.6},
         "roofline": {"bound": "fp64",
                      "kernel": br_kernel, "achieved": achieved, "peak": tf.value, "unit": "TFLOP/s",

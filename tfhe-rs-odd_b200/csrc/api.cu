@@ -50,6 +50,10 @@ struct b200tfhe_context {
     void *twbig = nullptr;                  // BigTables (N = 8192)
     Workspace ws;
     uint64_t launches = 0;
+    // host-pointer calls on large batches are cut into chunks: H2D of chunk i+1 and D2H of chunk i-1 overlap the kernels of chunk i
+    enum { MAX_CHUNKS = 8 };
+    cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
+    cudaEvent_t ev_in[MAX_CHUNKS] = {}, ev_done[MAX_CHUNKS] = {}, ev_start = nullptr;
 };
 struct b200tfhe_bsk {
     b200tfhe_context *ctx;
@@ -156,6 +160,13 @@ int b200tfhe_context_destroy(b200tfhe_context *ctx) {
     cudaFree(ctx->tw32);
     cudaFree(ctx->twbig);
     cudaStreamDestroy(ctx->stream);
+    if (ctx->s_h2d) cudaStreamDestroy(ctx->s_h2d);
+    if (ctx->s_d2h) cudaStreamDestroy(ctx->s_d2h);
+    for (int i = 0; i < b200tfhe_context::MAX_CHUNKS; i++) {
+        if (ctx->ev_in[i]) cudaEventDestroy(ctx->ev_in[i]);
+        if (ctx->ev_done[i]) cudaEventDestroy(ctx->ev_done[i]);
+    }
+    if (ctx->ev_start) cudaEventDestroy(ctx->ev_start);
     delete ctx;
     return 0;
 }
@@ -432,7 +443,6 @@ static int host_op(b200tfhe_context *ctx, Op op, const b200tfhe_ksk *ksk, const 
     void *d_in, *d_out, *d_mid = nullptr, *d_luts = nullptr, *d_idx = nullptr;
     CK(ctx->ws.get(Workspace::IN, batch * in_len * s, &d_in));
     CK(ctx->ws.get(Workspace::OUT, batch * out_len * s, &d_out));
-    CK(cudaMemcpyAsync(d_in, in, batch * in_len * s, cudaMemcpyHostToDevice, ctx->stream));
     if (need_bsk) {
         CK(ctx->ws.get(Workspace::LUTS, (size_t)n_luts * glwe_len(p) * s, &d_luts));
         CK(cudaMemcpyAsync(d_luts, luts, (size_t)n_luts * glwe_len(p) * s, cudaMemcpyHostToDevice, ctx->stream));
@@ -441,24 +451,81 @@ static int host_op(b200tfhe_context *ctx, Op op, const b200tfhe_ksk *ksk, const 
             CK(cudaMemcpyAsync(d_idx, lut_idx, (size_t)batch * 4, cudaMemcpyHostToDevice, ctx->stream));
         }
     }
-    int rc = 0;
-    switch (op) {
-        case OP_KS: rc = ks_dev_locked(ctx, ksk, d_in, d_out, batch); break;
-        case OP_PBS: rc = br_dev_locked(ctx, bsk, d_in, d_out, d_luts, (const uint32_t *)d_idx, batch, BR_MODE_LWE); break;
-        case OP_BR: rc = br_dev_locked(ctx, bsk, d_in, d_out, d_luts, (const uint32_t *)d_idx, batch, BR_MODE_GLWE); break;
-        case OP_KS_PBS:
-            CK(ctx->ws.get(Workspace::MID, batch * small_len(p) * s, &d_mid));
-            rc = ks_dev_locked(ctx, ksk, d_in, d_mid, batch);
-            if (!rc) rc = br_dev_locked(ctx, bsk, d_mid, d_out, d_luts, (const uint32_t *)d_idx, batch, BR_MODE_LWE);
-            break;
-        case OP_PBS_KS:
-            CK(ctx->ws.get(Workspace::MID, batch * big_len(p) * s, &d_mid));
-            rc = br_dev_locked(ctx, bsk, d_in, d_mid, d_luts, (const uint32_t *)d_idx, batch, BR_MODE_LWE);
-            if (!rc) rc = ks_dev_locked(ctx, ksk, d_mid, d_out, batch);
-            break;
+    // one chunk of the batch through the kernels (device pointers already offset)
+    auto run = [&](const char *ci, char *co, const uint32_t *cidx, uint32_t cb, size_t first) -> int {
+        int rc = 0;
+        switch (op) {
+            case OP_KS: rc = ks_dev_locked(ctx, ksk, ci, co, cb); break;
+            case OP_PBS: rc = br_dev_locked(ctx, bsk, ci, co, d_luts, cidx, cb, BR_MODE_LWE); break;
+            case OP_BR: rc = br_dev_locked(ctx, bsk, ci, co, d_luts, cidx, cb, BR_MODE_GLWE); break;
+            case OP_KS_PBS: {
+                char *mid = (char *)d_mid + first * small_len(p) * s;
+                rc = ks_dev_locked(ctx, ksk, ci, mid, cb);
+                if (!rc) rc = br_dev_locked(ctx, bsk, mid, co, d_luts, cidx, cb, BR_MODE_LWE);
+                break;
+            }
+            case OP_PBS_KS: {
+                char *mid = (char *)d_mid + first * big_len(p) * s;
+                rc = br_dev_locked(ctx, bsk, ci, mid, d_luts, cidx, cb, BR_MODE_LWE);
+                if (!rc) rc = ks_dev_locked(ctx, ksk, mid, co, cb);
+                break;
+            }
+        }
+        return rc;
+    };
+    if (op == OP_KS_PBS) CK(ctx->ws.get(Workspace::MID, batch * small_len(p) * s, &d_mid));
+    if (op == OP_PBS_KS) CK(ctx->ws.get(Workspace::MID, batch * big_len(p) * s, &d_mid));
+
+    // chunking: only when every chunk still fills the GPU for several waves (unit = 4 ciphertexts x 148 SMs)
+    static const uint32_t min_chunk = getenv("B200TFHE_CHUNK_MIN") ? (uint32_t)atoi(getenv("B200TFHE_CHUNK_MIN")) : 6 * 592;
+    uint32_t n_chunks = 1, chunk = batch;
+    if (batch >= 2 * min_chunk && min_chunk > 0) {
+        n_chunks = batch / min_chunk;
+        if (n_chunks > 4) n_chunks = 4;
+        chunk = (batch + n_chunks - 1) / n_chunks;
+        chunk = (chunk + 591) / 592 * 592;
+        n_chunks = (batch + chunk - 1) / chunk;
     }
-    if (rc) return 1;
-    CK(cudaMemcpyAsync(out, d_out, batch * out_len * s, cudaMemcpyDeviceToHost, ctx->stream));
+    if (n_chunks == 1) {
+        CK(cudaMemcpyAsync(d_in, in, batch * in_len * s, cudaMemcpyHostToDevice, ctx->stream));
+        if (run((const char *)d_in, (char *)d_out, (const uint32_t *)d_idx, batch, 0)) return 1;
+        CK(cudaMemcpyAsync(out, d_out, batch * out_len * s, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        return 0;
+    }
+    if (!ctx->s_h2d) {
+        CK(cudaStreamCreateWithFlags(&ctx->s_h2d, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&ctx->s_d2h, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&ctx->ev_start, cudaEventDisableTiming));
+        for (int i = 0; i < b200tfhe_context::MAX_CHUNKS; i++) {
+            CK(cudaEventCreateWithFlags(&ctx->ev_in[i], cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&ctx->ev_done[i], cudaEventDisableTiming));
+        }
+    }
+    // the copy streams start after whatever is already queued on the main stream (LUT / index uploads, earlier calls)
+    CK(cudaEventRecord(ctx->ev_start, ctx->stream));
+    CK(cudaStreamWaitEvent(ctx->s_h2d, ctx->ev_start, 0));
+    CK(cudaStreamWaitEvent(ctx->s_d2h, ctx->ev_start, 0));
+    for (uint32_t c = 0; c < n_chunks; c++) {
+        const size_t first = (size_t)c * chunk;
+        const uint32_t cb = (uint32_t)((first + chunk <= batch) ? chunk : batch - first);
+        CK(cudaMemcpyAsync((char *)d_in + first * in_len * s, (const char *)in + first * in_len * s, (size_t)cb * in_len * s,
+                           cudaMemcpyHostToDevice, ctx->s_h2d));
+        CK(cudaEventRecord(ctx->ev_in[c], ctx->s_h2d));
+    }
+    for (uint32_t c = 0; c < n_chunks; c++) {
+        const size_t first = (size_t)c * chunk;
+        const uint32_t cb = (uint32_t)((first + chunk <= batch) ? chunk : batch - first);
+        CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_in[c], 0));
+        if (run((const char *)d_in + first * in_len * s, (char *)d_out + first * out_len * s,
+                d_idx ? (const uint32_t *)d_idx + first : nullptr, cb, first))
+            return 1;
+        CK(cudaEventRecord(ctx->ev_done[c], ctx->stream));
+        CK(cudaStreamWaitEvent(ctx->s_d2h, ctx->ev_done[c], 0));
+        CK(cudaMemcpyAsync((char *)out + first * out_len * s, (const char *)d_out + first * out_len * s, (size_t)cb * out_len * s,
+                           cudaMemcpyDeviceToHost, ctx->s_d2h));
+    }
+    CK(cudaStreamSynchronize(ctx->s_d2h));
     CK(cudaStreamSynchronize(ctx->stream));
     return 0;
 }
