@@ -147,7 +147,8 @@ def test_pbs_decrypts_like_oracle(ctx, name, B):
     assert d.max() < phase_bound(o), (d.max(), phase_bound(o))
 
 
-@pytest.mark.parametrize("name,B", [("TOY_U64", 6), ("TOY_2_2", 5), ("TOY_3_3", 4), ("MESSAGE_2_CARRY_2", 40)])
+@pytest.mark.parametrize("name,B", [("TOY_U64", 6), ("TOY_2_2", 5), ("TOY_3_3", 4), ("MESSAGE_2_CARRY_2", 40),
+                                    ("MESSAGE_1_CARRY_1", 16), ("MESSAGE_3_CARRY_3", 6)])
 def test_ks_pbs_like_oracle(ctx, name, B):
     import tfhe_rs_odd_b200 as t
     o, p, bsk, ksk, msgs, pts, luts, idx, expect = _pbs_case(ctx, name, B, seed=5)
@@ -280,3 +281,22 @@ def test_full_size_batch_properties(ctx):
     out_p = t.keyswitch_programmable_bootstrap(ksk, bsk, cts[perm], luts, lut_idx=idx[perm])
     assert np.array_equal(out_p, out[perm])
     assert np.array_equal(t.keyswitch_programmable_bootstrap(ksk, bsk, cts, luts, lut_idx=idx), out)
+
+
+def test_full_size_boolean_nand_batch(ctx):
+    """BASELINE configs[0]: 8192 NAND gate bootstraps at boolean DEFAULT_PARAMETERS (PBS then keyswitch, u32): every output
+    decrypts to the truth table; position independence bit for bit."""
+    from tfhe_rs_odd_b200 import boolean
+    o = get_oracle("BOOLEAN_DEFAULT")
+    p, bsk, ksk = _keys(ctx, o)
+    B = 8192
+    rng = np.random.default_rng(77)
+    a, b = rng.integers(0, 2, B).astype(bool), rng.integers(0, 2, B).astype(bool)
+    T, F = 1 << 29, 7 << 29
+    ca = o.encrypt(np.where(a, T, F).astype(np.uint64), "small", seed=0xA0000000).astype(np.uint32)
+    cb = o.encrypt(np.where(b, T, F).astype(np.uint64), "small", seed=0xB0000000).astype(np.uint32)
+    out = boolean.gate_batch(ksk, bsk, 1, ca, cb, pbs_first=True)
+    assert np.array_equal(o.decode_bool(o.phase(out.astype(np.uint64), "small")), ~(a & b))
+    perm = rng.permutation(B)
+    out_p = boolean.gate_batch(ksk, bsk, 1, ca[perm], cb[perm], pbs_first=True)
+    assert np.array_equal(out_p, out[perm])
