@@ -300,3 +300,13 @@ def test_full_size_boolean_nand_batch(ctx):
     perm = rng.permutation(B)
     out_p = boolean.gate_batch(ksk, bsk, 1, ca[perm], cb[perm], pbs_first=True)
     assert np.array_equal(out_p, out[perm])
+
+
+def test_warp_specialised_blind_rotation_variant():
+    """blind_rotate_ws.cu (experimental, B200TFHE_WS=1: Fourier warp + torus warp per ciphertext) stays parity-green."""
+    import subprocess, sys, os
+    env = dict(os.environ, B200TFHE_WS="1", B200TFHE_FORCE_TMEM="1")
+    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-m", "gpu", __file__, "-k",
+                        "(test_pbs_decrypts_like_oracle or test_ks_pbs_like_oracle) and (TOY_2_2 or MESSAGE_2_CARRY_2)"],
+                       env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]

@@ -212,6 +212,8 @@ int br_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
     if (a.batch <= 0) return 0;
     static const bool no_tmem = getenv("B200TFHE_NO_TMEM") != nullptr;   // A/B switch for profiling
     static const bool force_tmem = getenv("B200TFHE_FORCE_TMEM") != nullptr;   // tests: exercise the TMEM kernel on small batches
+    static const bool use_ws = getenv("B200TFHE_WS") != nullptr;               // warp-specialised variant (experimental)
+    if (use_ws && (force_tmem || a.batch >= 4 * 148) && br_ws_supported(p)) return br_ws_launch(p, a, st);
     if (!no_tmem && (force_tmem || a.batch >= 4 * 148) && br_tmem_supported(p)) return br_tmem_launch(p, a, st);
     if (a.batch < 3 * 148) {
 #define X(T, R, K, L, BL, CTS) \

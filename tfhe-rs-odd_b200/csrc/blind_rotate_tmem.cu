@@ -15,75 +15,12 @@
 //     is the only inter-warp synchronisation of the data path.
 // TMEM use per CTA: 4 quadrants x 2 buffers x 2 polynomials x 128 columns = all 512 columns (1 CTA per SM).  No
 // tensor-core instruction is involved: TMEM is a 256 KB per-SM scratchpad that costs no shared-memory capacity or bandwidth.
-#include "br_core.cuh"
+#include "tmem_util.cuh"
 #include "kernels.h"
 #include <cstdio>
 #include <cstdlib>
 
 namespace b200tfhe {
-
-#if defined(__CUDA_ARCH__)
-DEV void tmem_st32(uint32_t taddr, const uint32_t (&v)[32]) {
-    asm volatile(
-        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
-        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
-        "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]), "r"(v[10]),
-        "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]), "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]),
-        "r"(v[21]), "r"(v[22]), "r"(v[23]), "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]),
-        "r"(v[31])
-        : "memory");
-}
-DEV void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
-        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
-          "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]),
-          "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
-          "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-        : "r"(taddr)
-        : "memory");
-}
-DEV void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
-DEV void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-DEV void tmem_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-DEV void tmem_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-DEV void named_bar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
-DEV void named_bar_arrive(int id, int count) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory"); }
-
-// 32x32 transpose of one warp's register tile through a half-size region (R rows of R/2 + 1 cplx):
-// in: x[k1] of lane s = S[k1][s];  out: x[p] of lane l = S[l][brev(p)].
-template <int R> DEV void transpose_split(int lane, cplx (&x)[R], cplx *hreg) {
-    constexpr int H = R / 2, ROWH = H + 1, LOGR = clog2(R);
-    cplx t[H];
-    if (lane < H) static_for<0, R>([&](auto k1) { hreg[decltype(k1)::value * ROWH + lane] = x[decltype(k1)::value]; });
-    __syncwarp();
-    static_for<0, H>([&](auto c) { t[decltype(c)::value] = hreg[lane * ROWH + decltype(c)::value]; });
-    __syncwarp();
-    if (lane >= H) static_for<0, R>([&](auto k1) { hreg[decltype(k1)::value * ROWH + lane - H] = x[decltype(k1)::value]; });
-    __syncwarp();
-    static_for<0, R>([&](auto p) {
-        constexpr int c = brev(decltype(p)::value, LOGR);
-        if constexpr (c < H) x[decltype(p)::value] = t[c];
-        else x[decltype(p)::value] = hreg[lane * ROWH + c - H];
-    });
-    __syncwarp();
-}
-
-// (P * X^a)[c] - own for a 64-bit torus and ONE decomposition level, returned as the double value of the balanced digit.
-// s8 = 8 * (c - a): bits 3..13 address the coefficient, bit 14 is the sign (X^N = -1).  Closed form of
-// BRCore::single_level_digit (exhaustively identical over all 2^32 upper words; the lower word only matters through the
-// borrow of the subtraction):  w = (2^31 + 2^sh - 1 - d_hi) >> (sh + 1),  digit = B/2 - w,  sh = 32 - BASE_LOG - 1.
-template <int BASE_LOG> DEV double rot_digit_f64(const unsigned char *acc_bytes, uint32_t s8, uint64_t own) {
-    constexpr int SH = 32 - BASE_LOG - 1;
-    const uint64_t v = *reinterpret_cast<const uint64_t *>(acc_bytes + (s8 & 0x3FF8u));
-    const uint32_t neg = (s8 >> 14) & 1u;
-    const uint32_t m = 0u - neg;
-    const uint64_t d = (v ^ (((uint64_t)m << 32) | m)) + (uint64_t)neg - own;
-    const uint32_t w = (0x80000000u + (1u << SH) - 1u - (uint32_t)(d >> 32)) >> (SH + 1);
-    return (4503599627370496.0 + (double)(1u << (BASE_LOG - 1))) - __hiloint2double(0x43300000, (int)w);
-}
-#endif
 
 // Iteration alignment of the 4 ciphertexts of a CTA:
 //   0  none (warps drift apart: 4 instruction streams, instruction-cache misses)
@@ -92,6 +29,9 @@ template <int BASE_LOG> DEV double rot_digit_f64(const unsigned char *acc_bytes,
 //   k>0 STAGGERED ring: ciphertext q starts iteration i when ciphertext q-1 has decomposed k of its 32 points of iteration
 //      i (and 0 waits for 3 of iteration i-1).  The streams stay a few hundred instructions apart (inside the 32 KB L1.5
 //      instruction cache) while the load/store bursts of one ciphertext overlap the FP64 phases of the others.
+#ifndef B200TFHE_TMEM_FENCE
+#define B200TFHE_TMEM_FENCE 4
+#endif
 #ifndef B200TFHE_TMEM_PREFETCH
 #define B200TFHE_TMEM_PREFETCH 2
 #endif
@@ -200,7 +140,7 @@ blind_rotate_tmem_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const 
                 if (q != TM_CTS - 1 || i != n - 1) named_bar_arrive(bar_next, 128);
             }
 #endif
-            if constexpr (decltype(p)::value % 4 == 0) asm volatile("" ::: "memory");   // bounds the loads in flight (registers)
+            if constexpr (decltype(p)::value % B200TFHE_TMEM_FENCE == 0) asm volatile("" ::: "memory");   // bounds the loads in flight (registers)
             F[decltype(p)::value] = cplx{rot_digit_f64<BL>(acc_bytes, base8 + 8u * R * m, own_re[m]),
                                          rot_digit_f64<BL>(acc_bytes, base8 + 8u * R * m + 8u * C::M, own_im[m])};
         });
@@ -286,7 +226,7 @@ blind_rotate_tmem_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const 
         static_for<0, R>([&](auto m) {
             cplx t = cmul_root<-decltype(m)::value * FFT::TWQ>(Y[decltype(m)::value]);
             const int c = lane + R * decltype(m)::value;
-            if constexpr (decltype(m)::value % 4 == 0) asm volatile("" ::: "memory");
+            if constexpr (decltype(m)::value % B200TFHE_TMEM_FENCE == 0) asm volatile("" ::: "memory");
             own_re[decltype(m)::value] = acc_r[c] + torus_from_double<T>(t.re);
             own_im[decltype(m)::value] = acc_r[c + C::M] + torus_from_double<T>(t.im);
             acc_r[c] = own_re[decltype(m)::value];

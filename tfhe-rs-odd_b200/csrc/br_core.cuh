@@ -174,7 +174,22 @@ template <typename T, int R, int K, int L, int BASE_LOG> struct BRCore {
             F[pp] = cmul(xb[pp], g[decltype(i)::value]);
         });
     }
+    // quarter QT (8 positions, register order pp = QT*8 + e <-> Fourier position brev(pp)) of key row (r, j), level 1
+    template <int QT> HD static void quarter_load(int lane, int r, int j, const cplx *ggsw, cplx (&h)[8]) {
+        const cplx *row = ggsw + ((size_t)r * K1 + j) * M;
+        static_for<0, 8>([&](auto e) {
+            constexpr int pp = QT * 8 + decltype(e)::value;
+            h[decltype(e)::value] = ldg_stream(row + brev(pp, FFT::LOGR) * R + lane);
+        });
+    }
 #if defined(__CUDA_ARCH__)
+    // L1 prefetch of that quarter: 8 position rows x 512 B = 32 lines, one per lane
+    template <int QT> DEV static void quarter_prefetch(int lane, int r, int j, const cplx *ggsw) {
+        const cplx *row = ggsw + ((size_t)r * K1 + j) * M;
+        const int pp = QT * 8 + (lane >> 2);
+        const int pos = (int)(__brev((unsigned)pp) >> (32 - FFT::LOGR));
+        prefetch_l1(reinterpret_cast<const char *>(row + pos * R) + (lane & 3) * 128);
+    }
     // L1 prefetch of the 8 KB chunk HALF of key row (r, j): 64 lines, two per lane
     template <int HALF> DEV static void chunk_prefetch(int lane, int r, int j, const cplx *ggsw) {
         const cplx *row = ggsw + ((size_t)r * K1 + j) * M;

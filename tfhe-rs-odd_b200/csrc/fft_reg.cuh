@@ -155,10 +155,17 @@ template <int R> struct TeamFFT {
     // + M as imaginary part), NOT yet twisted.  After the call x[k1] = u_l w_l^{k1} sum_m x_m v_m w_R^{m k1},
     // and it has been written to S[k1][lane].
     HD static void fwd_pass1_compute(int lane, cplx (&x)[R], const cplx (*tw)[R]) {
+        twist(x);
+        fwd_pass1_compute_twisted(lane, x, tw);
+    }
+    // the two halves of fwd_pass1_compute, for kernels that twist in another warp (blind_rotate_ws.cu)
+    HD static void twist(cplx (&x)[R]) {
         static_for<0, R>([&](auto p) {
             constexpr int m = brev(decltype(p)::value, LOGR);
             x[decltype(p)::value] = cmul_root<m * TWQ>(x[decltype(p)::value]);
         });
+    }
+    HD static void fwd_pass1_compute_twisted(int lane, cplx (&x)[R], const cplx (*tw)[R]) {
         fft_dit<R, -1>(x);
         mid_twiddle(lane, x, tw);
     }

@@ -33,6 +33,10 @@ int bsk_convert_big_launch(const Params &p, const void *std_bsk, void *out, cons
 int br_tmem_supported(const Params &p);
 int br_tmem_launch(const Params &p, const BRLaunch &a, cudaStream_t st);
 
+// blind_rotate_ws.cu (same parameter set; warp-specialised: Fourier warp + torus warp per ciphertext)
+int br_ws_supported(const Params &p);
+int br_ws_launch(const Params &p, const BRLaunch &a, cudaStream_t st);
+
 // keyswitch.cu
 struct KSLaunch {
     const void *in;   size_t in_stride;    // [batch][in_stride], n_in+1 used
