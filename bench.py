@@ -257,6 +257,8 @@ def main():
     ms_ks = timed(step_ks, br_steps, 1) / br_steps
     # single-PBS latency (the metric's second half): batch of ONE ciphertext through the same KS+PBS entry point
     lat = []
+    lat_sampler = ClockSampler(local)
+    lat_sampler.start()
     for it in range(210):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
@@ -266,6 +268,7 @@ def main():
         torch.cuda.synchronize()
         if it >= 10:
             lat.append(e0.elapsed_time(e1))
+    lat_clocks = lat_sampler.stop()
     lat_order = list(lat)
     lat.sort()
     tf = C.c_double()
@@ -311,6 +314,7 @@ def main():
         "latency": {"what": "single KS+PBS (batch 1), device-resident, CUDA events", "p50_ms": lat[len(lat) // 2],
                     "p99_ms": lat[min(len(lat) - 1, int(len(lat) * 0.99))], "min_ms": lat[0], "samples": len(lat),
                     "first20_median_ms": sorted(lat_order[:20])[10], "last20_median_ms": sorted(lat_order[-20:])[10],
+                    "sm_mhz_during": lat_clocks.get("sm_mhz"),
                     "reference_published_ms": 16.6},
         "roofline": {"bound": "fp64",
                      "kernel": br_kernel, "achieved": achieved, "peak": tf.value, "unit": "TFLOP/s",
