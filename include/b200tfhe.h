@@ -156,6 +156,37 @@ int b200tfhe_ks_pbs_batch_dev(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, co
 int b200tfhe_pbs_ks_batch_dev(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, const void *d_in,
                               void *d_out, const void *d_luts, const uint32_t *d_lut_idx, uint32_t batch);
 
+/* ---- device-resident waves over a ciphertext pool ---------------------------------------------
+ * The reference evaluates a shortint / integer / Trivium circuit as rayon-parallel layers of
+ *   leveled prologue (unchecked_add, unchecked_scalar_mul: core_crypto/algorithms/lwe_linear_algebra.rs:191-215,556-572;
+ *   bivariate packing lhs*factor + rhs: shortint/server_key/bivariate_pbs.rs:167-182)  +  apply_lookup_table
+ * (integer/server_key/radix_parallel/mul.rs:329-424, apps/trivium/src/trivium/trivium_shortint.rs:81-168).  A pool keeps
+ * the ciphertexts of such a circuit in HBM; b200tfhe_wave_run executes one layer:
+ *     pool[dst] <- LUT_lut( sum_k scale[k] * pool[src[k]] + (0,...,0,plaintext) )      for every op, lut < 0: no bootstrap
+ * Every op of a wave reads the pool as it was before the wave.  The first n_pbs ops are the bootstrapped ones (lut >= 0),
+ * the rest are purely linear (lut < 0).  Asynchronous on the context's stream. */
+typedef struct b200tfhe_pool b200tfhe_pool;
+typedef struct {
+    uint32_t dst;          /* pool slot written */
+    uint32_t src[4];       /* pool slots read (ignored where scale == 0) */
+    uint32_t reserved;
+    int64_t scale[4];      /* cleartext multipliers, wrapping */
+    uint64_t plaintext;    /* added to the body (already encoded, e.g. value * delta) */
+    int32_t lut;           /* accumulator index into the pool's LUT table, or < 0 */
+    uint32_t reserved2;
+} b200tfhe_wave_op;
+/* big != 0: slots hold kN+1 scalars and a bootstrap is keyswitch -> PBS (shortint *_KS_PBS sets); big == 0: n+1 scalars,
+ * PBS -> keyswitch (boolean DEFAULT_PARAMETERS) */
+int b200tfhe_pool_create(b200tfhe_context *ctx, const b200tfhe_params *p, int big, uint32_t capacity, b200tfhe_pool **out);
+int b200tfhe_pool_destroy(b200tfhe_pool *pool);
+int b200tfhe_pool_write(b200tfhe_context *ctx, b200tfhe_pool *pool, uint32_t first, uint32_t count, const void *host_cts);
+int b200tfhe_pool_read(b200tfhe_context *ctx, const b200tfhe_pool *pool, uint32_t first, uint32_t count, void *host_cts);
+int b200tfhe_pool_device_buffer(const b200tfhe_pool *pool, void **d_ptr, size_t *bytes);
+/* accumulators (GLWE, (k+1)N scalars each) used by the pool's waves; copied to the device */
+int b200tfhe_pool_set_luts(b200tfhe_context *ctx, b200tfhe_pool *pool, const void *host_luts, uint32_t n_luts);
+int b200tfhe_wave_run(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, b200tfhe_pool *pool,
+                      const b200tfhe_wave_op *ops, uint32_t n_ops, uint32_t n_pbs);
+
 /* sustained FP64 FMA rate of the device in TFLOP/s (register-only probe kernel, best of repeated runs over
  * about duration_ms): the measured denominator of the blind rotation's FP64 roofline */
 int b200tfhe_probe_fp64_tflops(b200tfhe_context *ctx, double duration_ms, double *tflops);

@@ -49,6 +49,13 @@ _PROTOS = {
     "b200tfhe_pbs_ks_batch_dev": [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _U32],
     "b200tfhe_launch_count": [_VP],
     "b200tfhe_probe_fp64_tflops": [_VP, C.c_double, C.POINTER(C.c_double)],
+    "b200tfhe_pool_create": [_VP, C.POINTER(Params), _I, _U32, _PP],
+    "b200tfhe_pool_destroy": [_VP],
+    "b200tfhe_pool_write": [_VP, _VP, _U32, _U32, _VP],
+    "b200tfhe_pool_read": [_VP, _VP, _U32, _U32, _VP],
+    "b200tfhe_pool_device_buffer": [_VP, _PP, C.POINTER(_SZ)],
+    "b200tfhe_pool_set_luts": [_VP, _VP, _VP, _U32],
+    "b200tfhe_wave_run": [_VP, _VP, _VP, _VP, _VP, _U32, _U32],
 }
 for _s in ("u64", "u32"):
     _PROTOS[f"b200tfhe_keyswitch_batch_{_s}"] = [_VP, _VP, _VP, _VP, _U32]

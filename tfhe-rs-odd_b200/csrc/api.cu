@@ -643,6 +643,144 @@ int b200tfhe_sample_extract_batch_u64(b200tfhe_context *ctx, const uint64_t *g, 
 int b200tfhe_sample_extract_batch_u32(b200tfhe_context *ctx, const uint32_t *g, uint32_t *l, uint32_t k, uint32_t N, uint32_t b) { return sample_extract_host(ctx, g, l, k, N, b, 32); }
 
 
+
+// ---- device-resident waves over a ciphertext pool -------------------------------------------------------------------
+static_assert(sizeof(b200tfhe_wave_op) == sizeof(WaveOp) && sizeof(WaveOp) == 72, "wave op layout");
+struct b200tfhe_pool {
+    b200tfhe_context *ctx;
+    Params p;
+    bool big;
+    uint32_t capacity;
+    size_t len;                       // scalars per slot
+    void *d_slots = nullptr, *d_luts = nullptr, *d_ops = nullptr, *d_staging = nullptr, *d_mid = nullptr, *d_out = nullptr;
+    uint32_t *d_idx = nullptr;
+    uint32_t n_luts = 0, ops_cap = 0;
+};
+
+int b200tfhe_pool_create(b200tfhe_context *ctx, const b200tfhe_params *pp, int big, uint32_t capacity, b200tfhe_pool **out) {
+    REQUIRE(ctx && pp && out, "pool_create: null argument");
+    *out = nullptr;
+    REQUIRE(capacity > 0, "pool_create: empty pool");
+    Params p = to_params(pp);
+    if (check_pbs_params(ctx, p) || check_ks_params(ctx, p)) return 1;
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    b200tfhe_pool *pl = new b200tfhe_pool{ctx, p, big != 0, capacity, big ? big_len(p) : small_len(p)};
+    cudaError_t e = cudaMalloc(&pl->d_slots, (size_t)capacity * pl->len * sz(p));
+    if (e != cudaSuccess) { delete pl; return fail_cuda(ctx, "cudaMalloc(pool)", e); }
+    cudaMemsetAsync(pl->d_slots, 0, (size_t)capacity * pl->len * sz(p), ctx->stream);
+    *out = pl;
+    return 0;
+}
+int b200tfhe_pool_destroy(b200tfhe_pool *pl) {
+    if (!pl) return 0;
+    cudaSetDevice(pl->ctx->device);
+    cudaStreamSynchronize(pl->ctx->stream);
+    for (void *q : {pl->d_slots, pl->d_luts, pl->d_ops, pl->d_staging, pl->d_mid, pl->d_out, (void *)pl->d_idx})
+        if (q) cudaFree(q);
+    delete pl;
+    return 0;
+}
+int b200tfhe_pool_write(b200tfhe_context *ctx, b200tfhe_pool *pl, uint32_t first, uint32_t count, const void *host) {
+    REQUIRE(ctx && pl && pl->ctx == ctx, "pool_write: bad handle");
+    REQUIRE((uint64_t)first + count <= pl->capacity, "pool_write: slot range out of bounds");
+    if (count == 0) return 0;
+    REQUIRE(host, "pool_write: null buffer");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    const size_t bytes = pl->len * sz(pl->p);
+    CK(cudaMemcpyAsync((char *)pl->d_slots + first * bytes, host, count * bytes, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+int b200tfhe_pool_read(b200tfhe_context *ctx, const b200tfhe_pool *pl, uint32_t first, uint32_t count, void *host) {
+    REQUIRE(ctx && pl && pl->ctx == ctx, "pool_read: bad handle");
+    REQUIRE((uint64_t)first + count <= pl->capacity, "pool_read: slot range out of bounds");
+    if (count == 0) return 0;
+    REQUIRE(host, "pool_read: null buffer");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    const size_t bytes = pl->len * sz(pl->p);
+    CK(cudaMemcpyAsync(host, (const char *)pl->d_slots + first * bytes, count * bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+int b200tfhe_pool_device_buffer(const b200tfhe_pool *pl, void **d_ptr, size_t *bytes) {
+    if (!pl || !d_ptr || !bytes) return 1;
+    *d_ptr = pl->d_slots;
+    *bytes = (size_t)pl->capacity * pl->len * sz(pl->p);
+    return 0;
+}
+int b200tfhe_pool_set_luts(b200tfhe_context *ctx, b200tfhe_pool *pl, const void *host_luts, uint32_t n_luts) {
+    REQUIRE(ctx && pl && pl->ctx == ctx, "pool_set_luts: bad handle");
+    REQUIRE(host_luts && n_luts > 0, "pool_set_luts: null / empty accumulator list");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (pl->d_luts) { cudaFree(pl->d_luts); pl->d_luts = nullptr; }
+    const size_t bytes = (size_t)n_luts * glwe_len(pl->p) * sz(pl->p);
+    CK(cudaMalloc(&pl->d_luts, bytes));
+    CK(cudaMemcpy(pl->d_luts, host_luts, bytes, cudaMemcpyHostToDevice));
+    pl->n_luts = n_luts;
+    return 0;
+}
+int b200tfhe_wave_run(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, b200tfhe_pool *pl,
+                      const b200tfhe_wave_op *ops, uint32_t n_ops, uint32_t n_pbs) {
+    REQUIRE(ctx && pl && pl->ctx == ctx, "wave_run: bad handle");
+    if (n_ops == 0) return 0;
+    REQUIRE(ops && n_pbs <= n_ops, "wave_run: bad operation list");
+    if (n_pbs) {
+        if (check_pair(ctx, ksk, bsk)) return 1;
+        REQUIRE(pl->n_luts > 0, "wave_run: the pool has no accumulators (b200tfhe_pool_set_luts)");
+    }
+    const Params &p = pl->p;
+    if (n_pbs) {
+        const Params &kp = bsk->p;
+        REQUIRE(kp.n == p.n && kp.k == p.k && kp.N == p.N && kp.bits == p.bits, "wave_run: keys and pool have different parameters");
+    }
+    for (uint32_t i = 0; i < n_ops; i++) {
+        const b200tfhe_wave_op &o = ops[i];
+        REQUIRE(o.dst < pl->capacity, "wave_run: destination slot out of range");
+        for (int k = 0; k < 4; k++) REQUIRE(o.scale[k] == 0 || o.src[k] < pl->capacity, "wave_run: source slot out of range");
+        if (i < n_pbs) REQUIRE(o.lut >= 0 && (uint32_t)o.lut < pl->n_luts, "wave_run: accumulator index out of range");
+        else REQUIRE(o.lut < 0, "wave_run: bootstrapped operations must come first");
+    }
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    const size_t s = sz(p), len = pl->len, mid_len = pl->big ? small_len(p) : big_len(p);
+    if (pl->ops_cap < n_ops) {
+        CK(cudaStreamSynchronize(ctx->stream));
+        for (void *q : {pl->d_ops, pl->d_staging, pl->d_mid, pl->d_out, (void *)pl->d_idx})
+            if (q) cudaFree(q);
+        pl->d_ops = pl->d_staging = pl->d_mid = pl->d_out = nullptr; pl->d_idx = nullptr; pl->ops_cap = 0;
+        uint32_t cap = n_ops < 256 ? 256 : n_ops;
+        CK(cudaMalloc(&pl->d_ops, (size_t)cap * sizeof(WaveOp)));
+        CK(cudaMalloc(&pl->d_staging, (size_t)cap * len * s));
+        CK(cudaMalloc(&pl->d_out, (size_t)cap * len * s));
+        CK(cudaMalloc(&pl->d_mid, (size_t)cap * mid_len * s));
+        CK(cudaMalloc((void **)&pl->d_idx, (size_t)cap * 4));
+        pl->ops_cap = cap;
+    }
+    // pageable source: cudaMemcpyAsync returns once the operations are staged, so the caller's array can be reused
+    CK(cudaMemcpyAsync(pl->d_ops, ops, (size_t)n_ops * sizeof(WaveOp), cudaMemcpyHostToDevice, ctx->stream));
+    int rc = wave_gather_launch(pl->d_slots, len, (const WaveOp *)pl->d_ops, (int)n_ops, pl->d_staging, pl->d_idx, (int)n_pbs, p.bits, ctx->stream);
+    ctx->launches++;
+    if (rc) return fail(ctx, "wave gather launch failed: " + std::to_string(rc));
+    if (n_pbs) {
+        if (pl->big) {
+            if (ks_dev_locked(ctx, ksk, pl->d_staging, pl->d_mid, n_pbs)) return 1;
+            if (br_dev_locked(ctx, bsk, pl->d_mid, pl->d_out, pl->d_luts, pl->d_idx, n_pbs, BR_MODE_LWE)) return 1;
+        } else {
+            if (br_dev_locked(ctx, bsk, pl->d_staging, pl->d_mid, pl->d_luts, pl->d_idx, n_pbs, BR_MODE_LWE)) return 1;
+            if (ks_dev_locked(ctx, ksk, pl->d_mid, pl->d_out, n_pbs)) return 1;
+        }
+    }
+    rc = wave_scatter_launch(pl->d_slots, len, (const WaveOp *)pl->d_ops, (int)n_ops, (int)n_pbs, pl->d_out, pl->d_staging, p.bits, ctx->stream);
+    ctx->launches++;
+    if (rc) return fail(ctx, "wave scatter launch failed: " + std::to_string(rc));
+    return 0;
+}
+
 // Measures the sustained FP64 FMA rate of the device (TFLOP/s, 2 flop per FMA) with a register-only kernel:
 // the denominator of the blind rotation's FP64 roofline.  duration_ms: how long to run (>= 20).
 int b200tfhe_probe_fp64_tflops(b200tfhe_context *ctx, double duration_ms, double *tflops) {

@@ -60,6 +60,21 @@ size_t ks_tc_key_bytes(int bits, int n_in, int n_out, int level);
 int ks_tc_prepare_key(KSTensorKey *tk, const void *ksk, void *planes, int bits, int n_in, int n_out, int level, cudaStream_t st);
 int ks_tc_launch(const KSLaunch &a, const KSTensorKey &tk, void *digits, cudaStream_t st);   // digits: batch * kp bytes of scratch
 
+// wave_kernels.cu (device-resident waves over a ciphertext pool); WaveOp is layout-identical to b200tfhe_wave_op
+struct WaveOp {
+    uint32_t dst;
+    uint32_t src[4];
+    uint32_t reserved;
+    int64_t scale[4];
+    uint64_t plaintext;
+    int32_t lut;
+    uint32_t reserved2;
+};
+int wave_gather_launch(const void *pool, size_t len, const WaveOp *d_ops, int n_ops, void *staging, uint32_t *d_lut_idx, int n_pbs,
+                       int bits, cudaStream_t st);
+int wave_scatter_launch(void *pool, size_t len, const WaveOp *d_ops, int n_ops, int n_pbs, const void *pbs_out, const void *staging,
+                        int bits, cudaStream_t st);
+
 // misc_kernels.cu
 int modswitch_launch(const void *in, uint32_t *out, size_t count, int log2N, int bits, cudaStream_t st);
 int sample_extract_launch(const void *glwe, void *lwe, int k, int N, int batch, int bits, cudaStream_t st);
