@@ -113,3 +113,35 @@ def test_trivium_keystream_on_device(ctx):
         bits = o.decode(o.phase(out[s], "big")) % 2
         assert np.array_equal(bits, trivium_reference_bits(keys[s], ivs[s], 64)), s
     tr.pool.close()
+
+
+@pytest.mark.gpu
+def test_radix_multiplication_on_device(ctx):
+    """BASELINE configs[3] in small: 16-bit radix integers (8 blocks at PARAM_MESSAGE_2_CARRY_2), schoolbook product in the
+    structure of unchecked_mul_parallelized (radix_parallel/mul.rs:329-424): one wave of bivariate block products, then
+    column-sum waves; result equals x * y mod 2^16 for every pair."""
+    from tfhe_rs_odd_b200.waves import CiphertextPool, OpGraph
+    from tfhe_rs_odd_b200 import radix
+    o = get_oracle("MESSAGE_2_CARRY_2")
+    p, ksk, bsk, sk = _server_key(ctx, o)
+    M, NB = 6, 8
+    rng = np.random.default_rng(21)
+    x, y = rng.integers(0, 1 << 16, M), rng.integers(0, 1 << 16, M)
+    x[0], y[0] = 0xFFFF, 0xFFFF
+    x[1], y[1] = 0, 0x1234
+    blocks = lambda v: np.stack([(v >> (2 * i)) & 3 for i in range(NB)], axis=1)
+    pool = CiphertextPool(ctx, p, capacity=M * 400, big=True)
+    pool.set_luts(np.stack(radix.radix_luts(sk)))
+    X, Y, OUT = 0, M * NB, 2 * M * NB
+    pool.write(X, o.encrypt(o.encode(blocks(x).reshape(-1)), "big", seed=0x61))
+    pool.write(Y, o.encrypt(o.encode(blocks(y).reshape(-1)), "big", seed=0x62000))
+    g = OpGraph(pool)
+    alloc = radix.SlotAllocator(3 * M * NB, pool.capacity)
+    for m in range(M):
+        radix.mul(g, alloc, X + m * NB, Y + m * NB, OUT + m * NB, NB)
+    waves = g.run(ksk, bsk)
+    assert waves[0] == (M * (36 + 28), M * (36 + 28))        # the block-product wave: nb(nb+1)/2 lsb + nb(nb-1)/2 msb terms
+    got = o.decode(o.phase(pool.read(OUT, M * NB), "big")).reshape(M, NB) % 4
+    total = sum(got[:, i].astype(np.int64) << (2 * i) for i in range(NB))
+    assert np.array_equal(total, (x * y) % (1 << 16))
+    pool.close()
