@@ -174,14 +174,7 @@ static int launch_br(const BRLaunch &a, cudaStream_t st) {
     typedef BRConfig<T, R, K, L, BL, CTS> CFG;
     auto kern = blind_rotate_kernel<T, R, K, L, BL, CTS>;
     size_t smem = CFG::smem_bytes(a.n);
-    static bool configured = false;  // per instantiation
-    static size_t configured_smem = 0;
-    if (!configured || smem > configured_smem) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return (int)e;
-        configured = true;
-        configured_smem = smem;
-    }
+    if (cudaError_t e = ensure_dynamic_smem((const void *)kern, smem)) return (int)e;
     int grid = (a.batch + CTS - 1) / CTS;
     kern<<<grid, CFG::THREADS, smem, st>>>((const T *)a.lwe_in, a.lwe_stride, (const T *)a.luts, a.lut_idx,
                                            (const cplx *)a.bsk, (T *)a.out, a.out_stride, a.n, a.batch, a.mode,

@@ -107,12 +107,7 @@ template <typename T, int K, int L, int BL> static int launch_big(const BRLaunch
     typedef BigCore<T, K, L, BL> C;
     auto kern = blind_rotate_big_kernel<T, K, L, BL>;
     size_t smem = C::ACC_BYTES + C::XCH_BYTES + ((((size_t)a.n + 1) * 2 + 15) & ~(size_t)15);
-    static size_t configured = 0;
-    if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return (int)e;
-        configured = smem;
-    }
+    if (cudaError_t e = ensure_dynamic_smem((const void *)kern, smem)) return (int)e;
     kern<<<a.batch, 256, smem, st>>>((const T *)a.lwe_in, a.lwe_stride, (const T *)a.luts, a.lut_idx, (const cplx *)a.bsk,
                                      (T *)a.out, a.out_stride, a.n, a.batch, a.mode, (const BigTables *)a.tw_fwd);
     return (int)cudaGetLastError();
@@ -139,12 +134,7 @@ int bsk_convert_big_launch(const Params &p, const void *std_bsk, void *out, cons
     if (p.bits != 64) return -1;
     size_t npoly = (size_t)p.n * p.pbs_level * (p.k + 1) * (p.k + 1);
     auto kern = bsk_convert_big_kernel<uint64_t>;
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536);
-        if (e != cudaSuccess) return (int)e;
-        configured = true;
-    }
+    if (cudaError_t e = ensure_dynamic_smem((const void *)kern, 65536)) return (int)e;
     int grid = (int)(npoly < 148 * 3 ? npoly : 148 * 3);
     kern<<<grid, 256, 65536, st>>>((const uint64_t *)std_bsk, (cplx *)out, npoly, (const BigTables *)tables);
     return (int)cudaGetLastError();

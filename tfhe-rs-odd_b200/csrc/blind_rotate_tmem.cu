@@ -263,12 +263,7 @@ int br_tmem_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
     auto kern = blind_rotate_tmem_kernel<uint64_t, 23>;
     size_t ahat = (((size_t)(a.n + 1) * sizeof(uint16_t)) + 15) & ~(size_t)15;
     size_t smem = TM_CTS * ((size_t)2 * 32 * 17 * sizeof(cplx) + (size_t)2 * C::N * sizeof(uint64_t) + ahat) + sizeof(TwTables<32>);
-    static size_t configured = 0;
-    if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return (int)e;
-        configured = smem;
-    }
+    if (cudaError_t e = ensure_dynamic_smem((const void *)kern, smem)) return (int)e;
     int grid = (a.batch + TM_CTS - 1) / TM_CTS;
     kern<<<grid, TM_CTS * 64, smem, st>>>((const uint64_t *)a.lwe_in, a.lwe_stride, (const uint64_t *)a.luts, a.lut_idx,
                                          (const cplx *)a.bsk, (uint64_t *)a.out, a.out_stride, a.n, a.batch, a.mode,

@@ -329,15 +329,8 @@ int br_ws_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
     auto kern = blind_rotate_ws_kernel<uint64_t, 23>;
     size_t ahat = (((size_t)(a.n + 1) * sizeof(uint16_t)) + 15) & ~(size_t)15;
     size_t smem = WS_CTS * ((size_t)(B200TFHE_WS_HALF ? 32 * 17 : C::REGION) * sizeof(cplx) + (size_t)2 * C::N * sizeof(uint64_t) + ahat) + sizeof(TwTables<32>);
-    static size_t configured = 0;
-    if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return (int)e;
-        // leave the rest of the 256 KB array to L1: the key block of a MAC (32 KB) is prefetched one transform ahead
-        int pct = (int)((smem + 2048) * 100 / (228 * 1024)) + 1;
-        cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, pct > 100 ? 100 : pct);
-        configured = smem;
-    }
+    // with the half-size transpose region the CTA stays under 196 KB; the carve-out hint leaves the rest of the array to L1
+    if (cudaError_t e = ensure_dynamic_smem((const void *)kern, smem, (int)((smem + 2048) * 100 / (228 * 1024)) + 1)) return (int)e;
     int grid = (a.batch + WS_CTS - 1) / WS_CTS;
     kern<<<grid, WS_CTS * 64, smem, st>>>((const uint64_t *)a.lwe_in, a.lwe_stride, (const uint64_t *)a.luts, a.lut_idx,
                                          (const cplx *)a.bsk, (uint64_t *)a.out, a.out_stride, a.n, a.batch, a.mode,

@@ -3,7 +3,29 @@
 #include "common.cuh"
 #include <cuda_runtime.h>
 
+#include <map>
+#include <mutex>
+#include <utility>
+
 namespace b200tfhe {
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device, per-kernel setting: remember what was configured for the
+// (kernel, current device) pair so that one process may drive several devices.  carveout_pct >= 0 also sets the preferred
+// shared-memory carve-out.
+inline cudaError_t ensure_dynamic_smem(const void *kern, size_t bytes, int carveout_pct = -1) {
+    static std::mutex mu;
+    static std::map<std::pair<const void *, int>, size_t> done;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    std::lock_guard<std::mutex> g(mu);
+    size_t &have = done[std::make_pair(kern, dev)];
+    if (bytes <= have) return cudaSuccess;
+    if ((e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess) return e;
+    if (carveout_pct >= 0) cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, carveout_pct > 100 ? 100 : carveout_pct);
+    have = bytes;
+    return cudaSuccess;
+}
 
 enum { BR_MODE_LWE = 0, BR_MODE_GLWE = 1 };
 

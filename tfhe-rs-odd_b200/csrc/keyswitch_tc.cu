@@ -279,20 +279,12 @@ int ks_tc_launch(const KSLaunch &a, const KSTensorKey &tk, void *digits, cudaStr
     const CUtensorMap &map_b = *reinterpret_cast<const CUtensorMap *>(tk.map_b);
     cudaError_t e;
     if (a.bits == 64) {
-        static bool configured = false;
-        if (!configured) {
-            if ((e = cudaFuncSetAttribute(ks_tc_kernel<uint64_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM)) != cudaSuccess) return (int)e;
-            configured = true;
-        }
+        if ((e = ensure_dynamic_smem((const void *)ks_tc_kernel<uint64_t>, TC_SMEM)) != cudaSuccess) return (int)e;
         ks_digits_kernel<uint64_t><<<dgrid, 256, 0, st>>>((const uint64_t *)a.in, a.in_stride, (int8_t *)digits, kp, a.n_in, a.level, a.base_log, a.batch);
         ks_tc_kernel<uint64_t><<<grid, TC_THREADS, TC_SMEM, st>>>(map_a, map_b, (const uint64_t *)a.in, a.in_stride, (uint64_t *)a.out,
                                                                  a.out_stride, a.n_in, a.n_out, k_blocks, a.batch);
     } else {
-        static bool configured = false;
-        if (!configured) {
-            if ((e = cudaFuncSetAttribute(ks_tc_kernel<uint32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM)) != cudaSuccess) return (int)e;
-            configured = true;
-        }
+        if ((e = ensure_dynamic_smem((const void *)ks_tc_kernel<uint32_t>, TC_SMEM)) != cudaSuccess) return (int)e;
         ks_digits_kernel<uint32_t><<<dgrid, 256, 0, st>>>((const uint32_t *)a.in, a.in_stride, (int8_t *)digits, kp, a.n_in, a.level, a.base_log, a.batch);
         ks_tc_kernel<uint32_t><<<grid, TC_THREADS, TC_SMEM, st>>>(map_a, map_b, (const uint32_t *)a.in, a.in_stride, (uint32_t *)a.out,
                                                                  a.out_stride, a.n_in, a.n_out, k_blocks, a.batch);
