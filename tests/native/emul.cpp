@@ -194,3 +194,105 @@ extern "C" int emul_blind_rotate_big(int n, int k, int N, int base_log, int leve
         return run_big<uint64_t, 1, 2, 15>(bsk_std, n, lwe, batch, lut, out_glwe);
     return 1;
 }
+
+// ---- latency kernel (blind_rotate_lat.cu): 64 threads per polynomial, three-pass FFT of fft3.cuh --------------------
+#include "fft3.cuh"
+// forward transform of 1024 folded complex inputs (re, im interleaved); out[f] = sum_j x_j e^{i pi j/N} e^{-2 pi i jf/M}
+extern "C" int emul_fft3_forward(const double *in, double *out) {
+    static Fft3::Tables tb; fill_fft3_tables(tb);
+    std::vector<cplx> b1(Fft3::BUF), b2(Fft3::BUF);
+    static cplx x[64][16];
+    for (int t = 0; t < 64; t++) {
+        for (int p = 0; p < 16; p++) { int j = t + 64 * brev(p, 4); x[t][p] = cplx{in[2 * j], in[2 * j + 1]}; }
+        Fft3::pre_twist(x[t]);
+        Fft3::pass_a(t, x[t], &tb.ta_fwd[0][0], 64, t, b1.data());
+    }
+    for (int t = 0; t < 64; t++) Fft3::pass_b(t, &tb.tb[0][0][0], b1.data(), b2.data());
+    for (int t = 0; t < 64; t++) {
+        Fft3::pass_c(t, x[t], b2.data());
+        for (int f1 = 0; f1 < 16; f1++) { out[2 * (64 * f1 + t)] = x[t][f1].re; out[2 * (64 * f1 + t) + 1] = x[t][f1].im; }
+    }
+    return 0;
+}
+// inverse: X[1024] (interleaved) -> 2048 real coefficients (c[j] = re, c[j+M] = im of untwisted inverse DFT / M)
+extern "C" int emul_fft3_inverse(const double *in, double *coef) {
+    static Fft3::Tables tb; fill_fft3_tables(tb);
+    std::vector<cplx> b1(Fft3::BUF), b2(Fft3::BUF);
+    static cplx x[64][16];
+    for (int t = 0; t < 64; t++) {
+        for (int p = 0; p < 16; p++) { int f = t + 64 * brev(p, 4); x[t][p] = cplx{in[2 * f], -in[2 * f + 1]}; }
+        Fft3::pass_a(t, x[t], &tb.ta_inv[0][0], 4, t >> 4, b1.data());
+    }
+    for (int t = 0; t < 64; t++) Fft3::pass_b(t, &tb.tb[1][0][0], b1.data(), b2.data());
+    for (int t = 0; t < 64; t++) {
+        Fft3::pass_c(t, x[t], b2.data());
+        Fft3::post_twist(x[t]);
+        for (int q = 0; q < 16; q++) { coef[t + 64 * q] = x[t][q].re; coef[t + 64 * q + 1024] = -x[t][q].im; }
+    }
+    return 0;
+}
+
+// full blind rotation with the latency kernel's stage sequence; the bootstrap key is converted by the standard routine
+// (convert_bsk<.., 32, ..>), which pins that both FFTs agree on the Fourier-domain order
+extern "C" int emul_blind_rotate_lat(int n, const uint64_t *bsk_std, const uint64_t *lwe, int batch, const uint64_t *lut,
+                                     uint64_t *out_glwe) {
+    typedef uint64_t T;
+    typedef BRCore<T, 32, 1, 1, 23> C;
+    constexpr int N = 2048, M = 1024, K1 = 2;
+    static Fft3::Tables tb; fill_fft3_tables(tb);
+    std::vector<cplx> fbsk;
+    convert_bsk<T, 32, 1, 1, 23>(bsk_std, n, fbsk);
+    std::vector<cplx> b1(K1 * Fft3::BUF), b2(K1 * Fft3::BUF), D(K1 * M);
+    static cplx x[K1][64][16];
+    for (int b = 0; b < batch; b++) {
+        const uint64_t *ct = lwe + (size_t)b * (n + 1);
+        std::vector<T> acc((size_t)K1 * N);
+        int bhat = (int)(modswitch<T>(ct[n], C::LOGN) & (2 * N - 1));
+        int a0 = (2 * N - bhat) & (2 * N - 1);
+        for (int r = 0; r < K1; r++)
+            for (int c = 0; c < N; c++) acc[(size_t)r * N + c] = rot_read<T, N>(&lut[(size_t)r * N], c, a0);
+        for (int i = 0; i < n; i++) {
+            int a = (int)(modswitch<T>(ct[i], C::LOGN) & (2 * N - 1));
+            const cplx *ggsw = &fbsk[(size_t)i * C::GGSW_CPLX];
+            for (int r = 0; r < K1; r++) {
+                const T *acc_r = &acc[(size_t)r * N];
+                for (int t = 0; t < 64; t++) {
+                    for (int p = 0; p < 16; p++) {
+                        int c = t + 64 * brev(p, 4);
+                        T d0 = rot_read<T, N>(acc_r, c, a) - acc_r[c], d1 = rot_read<T, N>(acc_r, c + M, a) - acc_r[c + M];
+                        x[r][t][p] = cplx{(double)C::single_level_digit(d0), (double)C::single_level_digit(d1)};
+                    }
+                    Fft3::pre_twist(x[r][t]);
+                    Fft3::pass_a(t, x[r][t], &tb.ta_fwd[0][0], 64, t, &b1[r * Fft3::BUF]);
+                }
+                for (int t = 0; t < 64; t++) Fft3::pass_b(t, &tb.tb[0][0][0], &b1[r * Fft3::BUF], &b2[r * Fft3::BUF]);
+                for (int t = 0; t < 64; t++) {
+                    Fft3::pass_c(t, x[r][t], &b2[r * Fft3::BUF]);
+                    for (int f1 = 0; f1 < 16; f1++) D[r * M + 64 * f1 + t] = x[r][t][f1];
+                }
+            }
+            for (int j = 0; j < K1; j++) {
+                for (int t = 0; t < 64; t++) {
+                    for (int p = 0; p < 16; p++) {
+                        int f = t + 64 * brev(p, 4);
+                        cplx F = cmul(ggsw[(size_t)(j * K1 + j) * M + f], D[j * M + f]);            // own row first
+                        C::mac_one(F, ggsw[(size_t)((1 - j) * K1 + j) * M + f], D[(1 - j) * M + f]);
+                        x[j][t][p] = cplx{F.re, -F.im};
+                    }
+                    Fft3::pass_a(t, x[j][t], &tb.ta_inv[0][0], 4, t >> 4, &b1[j * Fft3::BUF]);
+                }
+                for (int t = 0; t < 64; t++) Fft3::pass_b(t, &tb.tb[1][0][0], &b1[j * Fft3::BUF], &b2[j * Fft3::BUF]);
+                for (int t = 0; t < 64; t++) {
+                    Fft3::pass_c(t, x[j][t], &b2[j * Fft3::BUF]);
+                    Fft3::post_twist(x[j][t]);
+                    for (int q = 0; q < 16; q++) {
+                        acc[(size_t)j * N + t + 64 * q] += torus_from_double<T>(x[j][t][q].re);
+                        acc[(size_t)j * N + t + 64 * q + M] += torus_from_double<T>(-x[j][t][q].im);
+                    }
+                }
+            }
+        }
+        for (size_t c = 0; c < acc.size(); c++) out_glwe[(size_t)b * K1 * N + c] = acc[c];
+    }
+    return 0;
+}

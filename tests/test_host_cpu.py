@@ -141,6 +141,40 @@ def test_kernel_single_cmux_matches_oracle_to_fft_precision(emul):
     assert np.abs((out - ref).astype(np.int64)).max() < 2 ** 42      # 2^-22 of the torus
 
 
+def test_three_pass_fft_matches_numpy(emul):
+    # fft3.cuh (the latency kernel's 64-thread FFT): forward vs numpy's DFT of the twisted input, and the inverse round trip
+    rng = np.random.default_rng(11)
+    x = rng.standard_normal(1024) + 1j * rng.standard_normal(1024)
+    inp = np.empty(2048); inp[0::2] = x.real; inp[1::2] = x.imag
+    out = np.empty(2048); coef = np.empty(2048)
+    assert emul.emul_fft3_forward(_p(inp), _p(out)) == 0
+    ref = np.fft.fft(x * np.exp(1j * np.pi * np.arange(1024) / 2048))
+    assert np.abs((out[0::2] + 1j * out[1::2]) - ref).max() / np.abs(ref).max() < 2.0 ** -48
+    assert emul.emul_fft3_inverse(_p(out), _p(coef)) == 0
+    assert np.abs((coef[:1024] + 1j * coef[1024:]) - x).max() < 2.0 ** -46
+
+
+def test_latency_kernel_stages_on_cpu_match_oracle(emul):
+    # blind_rotate_lat.cu's stage sequence, with the bootstrap key converted by the standard routine
+    o = get_oracle("TOY_2_2")
+    B = 3
+    msgs = np.arange(B) % o.pmod
+    pts, lut = o.encode(msgs), o.lut(lambda x: (x + 1) % o.pmod)
+    cts = o.encrypt(pts, "small")
+    ref = o.pbs(cts, lut, sample_extract=False)
+    out = np.zeros((B, o.glwe_len), np.uint64)
+    assert emul.emul_blind_rotate_lat(o.n, _p(o.bsk), _p(cts), B, _p(lut), _p(out)) == 0
+    ph_ref = np.array([o.glwe_phase(g)[0] for g in ref]); ph = np.array([o.glwe_phase(g)[0] for g in out])
+    assert np.array_equal(o.decode(ph) % o.pmod, (msgs + 1) % o.pmod)
+    assert np.abs((ph - ph_ref).astype(np.int64).astype(np.float64)).max() / 2.0 ** 64 < phase_bound(o)
+    ct = np.zeros((1, o.n + 1), np.uint64)      # exactly one external product: FFT-precision agreement
+    ct[0, 3] = np.uint64(0x1234567890ABCDEF); ct[0, o.n] = np.uint64(0x0234567890ABCDEF)
+    ref1 = o.pbs(ct, o.lut(lambda x: x), sample_extract=False)
+    out1 = np.zeros((1, o.glwe_len), np.uint64)
+    assert emul.emul_blind_rotate_lat(o.n, _p(o.bsk), _p(ct), 1, _p(o.lut(lambda x: x)), _p(out1)) == 0
+    assert np.abs((out1 - ref1).astype(np.int64)).max() < 2 ** 42
+
+
 def test_single_level_digit_closed_form(emul):
     rng = np.random.default_rng(9)
     xs = list(rng.integers(0, 2 ** 64, 20000, dtype=np.uint64))

@@ -208,6 +208,9 @@ int br_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
     static const bool use_ws = getenv("B200TFHE_WS") != nullptr;               // warp-specialised variant (experimental)
     if (use_ws && (force_tmem || a.batch >= 4 * 148) && br_ws_supported(p)) return br_ws_launch(p, a, st);
     if (!no_tmem && (force_tmem || a.batch >= 4 * 148) && br_tmem_supported(p)) return br_tmem_launch(p, a, st);
+    // few ciphertexts: one per SM, spread over four warps (blind_rotate_lat.cu)
+    static const int lat_max = getenv("B200TFHE_LAT_MAX") ? atoi(getenv("B200TFHE_LAT_MAX")) : 148;
+    if (a.batch <= lat_max && br_lat_supported(p)) return br_lat_launch(p, a, st);
     if (a.batch < 3 * 148) {
 #define X(T, R, K, L, BL, CTS) \
     if (p.bits == (int)sizeof(T) * 8 && p.N == 2 * R * R && p.k == K && p.pbs_level == L && p.pbs_base_log == BL) \

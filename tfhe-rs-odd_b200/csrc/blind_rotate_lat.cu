@@ -1,0 +1,214 @@
+// blind_rotate_lat.cu -- single-ciphertext ("latency") blind rotation for N = 2048, k = 1, l = 1 (PARAM_MESSAGE_2_CARRY_2).
+//
+// The batch kernels give one polynomial to one warp (32 points per thread) and hide every latency behind the other
+// ciphertexts of the SM.  With ONE ciphertext per SM that leaves two warps on two of the four schedulers, and ncu shows
+// the iteration bound by instruction issue: 5000 SASS instructions per warp-iteration, 1.1 "no instruction" stall cycles
+// per issue because the unrolled 80 KB loop body misses the instruction cache with nobody to share the fetch
+// (profiles/r01_ncu_latency.json).  This kernel is built for that regime instead:
+//   * 64 threads per polynomial, 16 points each (fft3.cuh: 1024 = 16 x 4 x 16), 4 warps = one per scheduler;
+//   * the forward and the inverse transform share ONE copy of the FFT code: the inverse is the forward of the conjugate,
+//     the loop over the two directions is not unrolled, direction-dependent work sits in uniform branches around it;
+//   * this iteration's Fourier GGSW (64 KB) is staged into shared memory by the TMA engine (cp.async.bulk + mbarrier)
+//     while the previous inverse transform and the next decomposition run: no key registers, no exposed L2 latency;
+//   * the closed-form rotated digit (tmem_util.cuh) replaces the generic decomposition recurrence.
+// Same mathematics and same bootstrap-key layout as blind_rotate.cu (reference: fft64/crypto/bootstrap.rs:243-412,
+// fft64/crypto/ggsw.rs:477-598); the stage sequence is executed on the CPU by tests/native/emul.cpp.
+#include "fft3.cuh"
+#include "tmem_util.cuh"
+#include "kernels.h"
+#include "twiddles.hpp"
+#include <map>
+#include <mutex>
+
+namespace b200tfhe {
+
+namespace {
+
+constexpr int LAT_THREADS = 128, LAT_N = 2048, LAT_M = 1024, LAT_K1 = 2, LAT_BL = 23;
+constexpr size_t LAT_KEY_BYTES = (size_t)LAT_K1 * LAT_K1 * LAT_M * sizeof(cplx);        // 65536: one Fourier GGSW
+constexpr size_t LAT_ACC_BYTES = (size_t)LAT_K1 * LAT_N * sizeof(uint64_t);             // 32768
+constexpr size_t LAT_BUF_BYTES = (size_t)LAT_K1 * Fft3::BUF * sizeof(cplx);             // 34816 per exchange buffer
+constexpr size_t LAT_OFF_ACC = LAT_KEY_BYTES;
+constexpr size_t LAT_OFF_BUF1 = LAT_OFF_ACC + LAT_ACC_BYTES;
+constexpr size_t LAT_OFF_BUF2 = LAT_OFF_BUF1 + LAT_BUF_BYTES;
+constexpr size_t LAT_OFF_TAB = LAT_OFF_BUF2 + LAT_BUF_BYTES;
+constexpr size_t LAT_OFF_MBAR = LAT_OFF_TAB + sizeof(Fft3::Tables);
+constexpr size_t LAT_OFF_AHAT = LAT_OFF_MBAR + 16;
+static_assert(sizeof(Fft3::Tables) % 16 == 0, "table block keeps 16-byte alignment");
+
+size_t lat_smem_bytes(int n) { return LAT_OFF_AHAT + ((((size_t)(n + 1) * sizeof(uint16_t)) + 15) & ~(size_t)15); }
+
+#if defined(__CUDA_ARCH__)
+DEV void bulk_load(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
+                 "r"(bytes), "r"(bar)
+                 : "memory");
+}
+DEV void mbarrier_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+#endif
+
+__global__ void __launch_bounds__(LAT_THREADS, 1)
+blind_rotate_lat_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride, const uint64_t *__restrict__ luts,
+                        const uint32_t *__restrict__ lut_idx, const cplx *__restrict__ bsk, uint64_t *__restrict__ out,
+                        size_t out_stride, int n, int mode, const Fft3::Tables *__restrict__ tables_g) {
+#if defined(__CUDA_ARCH__)
+    typedef uint64_t T;
+    constexpr int N = LAT_N, M = LAT_M, K1 = LAT_K1;
+    extern __shared__ __align__(128) unsigned char smem[];
+    cplx *key = reinterpret_cast<cplx *>(smem);                               // [r][j][M], refilled every iteration by TMA
+    T *acc = reinterpret_cast<T *>(smem + LAT_OFF_ACC);                       // [K1][N]
+    cplx *buf1 = reinterpret_cast<cplx *>(smem + LAT_OFF_BUF1);               // [K1][BUF]; also D[r][M] between the transforms
+    cplx *buf2 = reinterpret_cast<cplx *>(smem + LAT_OFF_BUF2);
+    Fft3::Tables *tab = reinterpret_cast<Fft3::Tables *>(smem + LAT_OFF_TAB);
+    uint16_t *ahat = reinterpret_cast<uint16_t *>(smem + LAT_OFF_AHAT);
+    const uint32_t bar = smem_addr_u32(smem + LAT_OFF_MBAR);
+    const uint32_t key_s = smem_addr_u32(key);
+
+    const int tid = threadIdx.x, r = tid >> 6, t = tid & 63;
+    const int ct = blockIdx.x;
+    T *acc_r = acc + r * N;
+    cplx *buf1_r = buf1 + r * Fft3::BUF, *buf2_r = buf2 + r * Fft3::BUF;
+
+    if (tid == 0) {
+        mbarrier_init(bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    {   // twiddle tables: global -> shared, once
+        const int4 *src = reinterpret_cast<const int4 *>(tables_g);
+        int4 *dst = reinterpret_cast<int4 *>(tab);
+        for (int e = tid; e < (int)(sizeof(Fft3::Tables) / 16); e += LAT_THREADS) dst[e] = src[e];
+    }
+    // modulus switch of the whole input (fft_impl/common.rs:26-43)
+    const T *lwe = lwe_in + (size_t)ct * lwe_stride;
+    for (int i = tid; i <= n; i += LAT_THREADS) ahat[i] = (uint16_t)(modswitch<T>(lwe[i], 11) & (2 * N - 1));
+    __syncthreads();
+    auto fetch_key = [&](int i) {   // thread 0: this iteration's GGSW, four 16 KB rows
+        mbarrier_expect_tx(bar, (uint32_t)LAT_KEY_BYTES);
+        const unsigned char *src = reinterpret_cast<const unsigned char *>(bsk) + (size_t)i * LAT_KEY_BYTES;
+#pragma unroll
+        for (int q = 0; q < 4; q++) bulk_load(key_s + q * 16384u, src + q * 16384u, 16384u, bar);
+    };
+    if (tid == 0 && n > 0) fetch_key(0);
+    {   // acc <- LUT * X^{-b_hat}  (polynomial_algorithms.rs:315-354)
+        const T *lut = luts + (size_t)(lut_idx ? lut_idx[ct] : 0) * K1 * N + (size_t)r * N;
+        const int a0 = (2 * N - (int)ahat[n]) & (2 * N - 1);
+        for (int c = t; c < N; c += 64) acc_r[c] = rot_read<T, N>(lut, c, a0);
+    }
+    __syncthreads();
+
+    const unsigned char *accb = reinterpret_cast<const unsigned char *>(acc_r);
+    const cplx *key_own = key + (size_t)(r * K1 + r) * M + t;            // row r (own transform), column j = r
+    const cplx *key_oth = key + (size_t)((1 - r) * K1 + r) * M + t;      // row 1-r, column j = r
+    const cplx *d_oth = buf1 + (1 - r) * Fft3::BUF + t;
+    cplx *d_own = buf1_r + t;
+
+    for (int i = 0; i < n; i++) {
+        const int a = ahat[i];
+        cplx x[16];
+#pragma unroll 1
+        for (int dir = 0; dir < 2; dir++) {
+            const cplx *ta;
+            int ta_stride, ta_idx;
+            if (dir == 0) {
+                // rotate-subtract + one-level signed decomposition, as doubles; then the register part of the twist
+                const uint32_t s8 = 8u * (uint32_t)(t - a);
+                static_for<0, 16>([&](auto p) {
+                    constexpr int v = brev(decltype(p)::value, 4);
+                    const T own_re = acc_r[t + 64 * v], own_im = acc_r[t + 64 * v + M];
+                    x[decltype(p)::value].re = rot_digit_f64<LAT_BL>(accb, s8 + 8u * 64u * v, own_re);
+                    x[decltype(p)::value].im = rot_digit_f64<LAT_BL>(accb, s8 + 8u * 64u * v + 8u * M, own_im);
+                });
+                Fft3::pre_twist(x);
+                ta = &tab->ta_fwd[0][0]; ta_stride = 64; ta_idx = t;
+            } else {
+                // x holds D_r[t + 64 f1]; publish it, then F_j = G[r][j] D_r + G[1-r][j] D_{1-r} for j = r, conjugated, in
+                // the register order pass A wants (element brev4(p))
+                static_for<0, 16>([&](auto f1) { d_own[64 * decltype(f1)::value] = x[decltype(f1)::value]; });
+                __syncthreads();
+                mbarrier_wait(bar, (uint32_t)(i & 1));
+                cplx y[16];
+                static_for<0, 16>([&](auto p) {
+                    constexpr int v = brev(decltype(p)::value, 4);
+                    cplx f = cmul(key_own[64 * v], x[v]);
+                    BRCore<T, 32, 1, 1, LAT_BL>::mac_one(f, key_oth[64 * v], d_oth[64 * v]);
+                    y[decltype(p)::value] = cplx{f.re, -f.im};
+                });
+                static_for<0, 16>([&](auto p) { x[decltype(p)::value] = y[decltype(p)::value]; });
+                __syncthreads();   // both teams are done with D (buf1) and with the key
+                if (tid == 0 && i + 1 < n) fetch_key(i + 1);
+                ta = &tab->ta_inv[0][0]; ta_stride = 4; ta_idx = t >> 4;
+            }
+            Fft3::pass_a(t, x, ta, ta_stride, ta_idx, buf1_r);
+            named_bar_sync(1 + r, 64);
+            Fft3::pass_b(t, &tab->tb[dir][0][0], buf1_r, buf2_r);
+            named_bar_sync(1 + r, 64);
+            Fft3::pass_c(t, x, buf2_r);
+            if (dir == 1) {
+                Fft3::post_twist(x);
+                static_for<0, 16>([&](auto q) {
+                    const int c = t + 64 * decltype(q)::value;
+                    acc_r[c] += torus_from_double<T>(x[decltype(q)::value].re);
+                    acc_r[c + M] += torus_from_double<T>(-x[decltype(q)::value].im);
+                });
+                named_bar_sync(1 + r, 64);
+            }
+        }
+    }
+
+    T *o = out + (size_t)ct * out_stride;
+    if (mode == BR_MODE_GLWE) {
+        for (int c = t; c < N; c += 64) o[(size_t)r * N + c] = acc_r[c];
+    } else if (r == 0) {   // sample extract, coefficient 0 (algorithms/glwe_sample_extraction.rs:91-147), k = 1
+        for (int c = t; c < N; c += 64) o[c] = (c == 0) ? acc_r[0] : (T)(0 - acc_r[N - c]);
+    } else if (t == 0) {
+        o[N] = acc_r[0];
+    }
+#endif
+}
+
+// per-device copy of the twiddle tables, uploaded on first use
+const Fft3::Tables *lat_tables(cudaStream_t st, cudaError_t *err) {
+    static std::mutex mu;
+    static std::map<int, Fft3::Tables *> per_device;
+    static Fft3::Tables host;
+    static bool filled = false;
+    int dev = 0;
+    if ((*err = cudaGetDevice(&dev)) != cudaSuccess) return nullptr;
+    std::lock_guard<std::mutex> g(mu);
+    auto it = per_device.find(dev);
+    if (it != per_device.end()) return it->second;
+    if (!filled) { fill_fft3_tables(host); filled = true; }
+    Fft3::Tables *d = nullptr;
+    if ((*err = cudaMalloc(&d, sizeof(Fft3::Tables))) != cudaSuccess) return nullptr;
+    if ((*err = cudaMemcpyAsync(d, &host, sizeof(Fft3::Tables), cudaMemcpyHostToDevice, st)) != cudaSuccess ||
+        (*err = cudaStreamSynchronize(st)) != cudaSuccess) {
+        cudaFree(d);
+        return nullptr;
+    }
+    per_device[dev] = d;
+    return d;
+}
+
+}  // namespace
+
+int br_lat_supported(const Params &p) {
+    return p.bits == 64 && p.N == LAT_N && p.k == 1 && p.pbs_level == 1 && p.pbs_base_log == LAT_BL;
+}
+
+int br_lat_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
+    if (!br_lat_supported(p)) return -1;
+    if (a.batch <= 0) return 0;
+    cudaError_t e = cudaSuccess;
+    const Fft3::Tables *tab = lat_tables(st, &e);
+    if (!tab) return (int)e;
+    const size_t smem = lat_smem_bytes(a.n);
+    if ((e = ensure_dynamic_smem((const void *)blind_rotate_lat_kernel, smem)) != cudaSuccess) return (int)e;
+    blind_rotate_lat_kernel<<<a.batch, LAT_THREADS, smem, st>>>((const uint64_t *)a.lwe_in, a.lwe_stride, (const uint64_t *)a.luts,
+                                                               a.lut_idx, (const cplx *)a.bsk, (uint64_t *)a.out, a.out_stride, a.n,
+                                                               a.mode, tab);
+    return (int)cudaGetLastError();
+}
+
+}  // namespace b200tfhe

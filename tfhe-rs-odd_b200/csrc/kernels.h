@@ -59,6 +59,10 @@ int br_tmem_launch(const Params &p, const BRLaunch &a, cudaStream_t st);
 int br_ws_supported(const Params &p);
 int br_ws_launch(const Params &p, const BRLaunch &a, cudaStream_t st);
 
+// blind_rotate_lat.cu (same parameter set; ONE ciphertext per CTA spread over 128 threads: the single-PBS latency path)
+int br_lat_supported(const Params &p);
+int br_lat_launch(const Params &p, const BRLaunch &a, cudaStream_t st);
+
 // keyswitch.cu
 struct KSLaunch {
     const void *in;   size_t in_stride;    // [batch][in_stride], n_in+1 used

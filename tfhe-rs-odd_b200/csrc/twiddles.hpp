@@ -2,6 +2,7 @@
 #pragma once
 #include "fft_reg.cuh"
 #include "br_big.cuh"
+#include "fft3.cuh"
 #include <cmath>
 
 namespace b200tfhe {
@@ -44,6 +45,25 @@ inline void fill_big_tables(BigTables &t) {
             cplx q = root_2N(-(long long)lane * b * 256, N);         // w_256^{lane 4b}
             t.pf[4 + b][lane] = q; t.pi[4 + b][lane] = cplx{q.re, -q.im};
         }
+    }
+}
+
+// tables of the 64-thread three-pass FFT (fft3.cuh)
+inline void fill_fft3_tables(Fft3::Tables &t) {
+    const int N = Fft3::N, M = Fft3::M;
+    for (int g2 = 0; g2 < 16; g2++) {
+        for (int tau = 0; tau < 64; tau++) t.ta_fwd[g2][tau] = root_2N((long long)tau - 64LL * (tau >> 4) * g2, N);
+        for (int u = 0; u < 4; u++) t.ta_inv[g2][u] = root_2N(-64LL * u * g2, N);
+    }
+    for (int beta = 0; beta < 64; beta++) {
+        const int j1 = beta & 15, gq = beta >> 4;
+        for (int e = 0; e < 4; e++)
+            for (int g1 = 0; g1 < 4; g1++) {
+                const long long f2 = 16 * g1 + 4 * gq + e;
+                t.tb[0][e * 4 + g1][beta] = root_2N(-4LL * j1 * f2, N);
+                cplx z = root_2N(-4LL * j1 * f2 + f2, N);
+                t.tb[1][e * 4 + g1][beta] = cplx{z.re / M, z.im / M};    // exact: M is a power of two
+            }
     }
 }
 
