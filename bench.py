@@ -291,8 +291,9 @@ def main():
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     bsk_bytes, ksk_bytes = bbytes, kbytes
     hbm_alg = (B * (small + big) * 8 + bsk_bytes) / (ms_br * 1e-3) / 1e9   # minimum HBM traffic of one blind-rotation launch
-    br_kernel = ("blind_rotate_tmem_kernel" if args.batch >= 4 * 148 and not os.environ.get("B200TFHE_NO_TMEM")
-                 else "blind_rotate_kernel")
+    lat_max = int(os.environ.get("B200TFHE_LAT_MAX", 2 * 148))       # dispatch of csrc/blind_rotate.cu::br_launch
+    br_kernel = ("blind_rotate_lat_kernel" if args.batch <= lat_max
+                 else "blind_rotate_kernel" if os.environ.get("B200TFHE_NO_TMEM") else "blind_rotate_tmem_kernel")
     traffic = None   # DRAM bytes of one launch of that kernel, from the committed ncu capture (same kernel, same batch)
     try:
         tr = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json"))).get(br_kernel)

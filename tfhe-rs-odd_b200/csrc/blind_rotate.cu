@@ -206,11 +206,14 @@ int br_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
     static const bool no_tmem = getenv("B200TFHE_NO_TMEM") != nullptr;   // A/B switch for profiling
     static const bool force_tmem = getenv("B200TFHE_FORCE_TMEM") != nullptr;   // tests: exercise the TMEM kernel on small batches
     static const bool use_ws = getenv("B200TFHE_WS") != nullptr;               // warp-specialised variant (experimental)
-    if (use_ws && (force_tmem || a.batch >= 4 * 148) && br_ws_supported(p)) return br_ws_launch(p, a, st);
-    if (!no_tmem && (force_tmem || a.batch >= 4 * 148) && br_tmem_supported(p)) return br_tmem_launch(p, a, st);
-    // few ciphertexts: one per SM, spread over four warps (blind_rotate_lat.cu)
-    static const int lat_max = getenv("B200TFHE_LAT_MAX") ? atoi(getenv("B200TFHE_LAT_MAX")) : 148;
-    if (a.batch <= lat_max && br_lat_supported(p)) return br_lat_launch(p, a, st);
+    // Measured on one B200 at PARAM_MESSAGE_2_CARRY_2 (tools/sweep_small_batches.sh): up to two ciphertexts per SM the
+    // one-ciphertext-per-CTA latency kernel wins (148: 2.8 ms, 296: 5.6 ms); from there one wave of the TMEM kernel
+    // (4 ciphertexts per CTA, 7.4 ms for anything up to 592) beats both it and the generic kernel.
+    static const int lat_max = getenv("B200TFHE_LAT_MAX") ? atoi(getenv("B200TFHE_LAT_MAX")) : 2 * 148;
+    const bool lat = !force_tmem && a.batch <= lat_max && br_lat_supported(p);
+    if (!lat && use_ws && br_ws_supported(p)) return br_ws_launch(p, a, st);
+    if (!lat && !no_tmem && br_tmem_supported(p)) return br_tmem_launch(p, a, st);
+    if (lat) return br_lat_launch(p, a, st);
     if (a.batch < 3 * 148) {
 #define X(T, R, K, L, BL, CTS) \
     if (p.bits == (int)sizeof(T) * 8 && p.N == 2 * R * R && p.k == K && p.pbs_level == L && p.pbs_base_log == BL) \

@@ -104,6 +104,14 @@ blind_rotate_lat_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride, 
     const cplx *d_oth = buf1 + (1 - r) * Fft3::BUF + t;
     cplx *d_own = buf1_r + t;
 
+    // the 32 accumulator coefficients this thread rounds into (t + 64 q, and + M) stay in registers from one
+    // accumulation to the next decomposition; shared memory keeps the copy the rotated reads need
+    T own_re[16], own_im[16];
+    static_for<0, 16>([&](auto q) {
+        own_re[decltype(q)::value] = acc_r[t + 64 * decltype(q)::value];
+        own_im[decltype(q)::value] = acc_r[t + 64 * decltype(q)::value + M];
+    });
+
     for (int i = 0; i < n; i++) {
         const int a = ahat[i];
         cplx x[16];
@@ -116,9 +124,8 @@ blind_rotate_lat_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride, 
                 const uint32_t s8 = 8u * (uint32_t)(t - a);
                 static_for<0, 16>([&](auto p) {
                     constexpr int v = brev(decltype(p)::value, 4);
-                    const T own_re = acc_r[t + 64 * v], own_im = acc_r[t + 64 * v + M];
-                    x[decltype(p)::value].re = rot_digit_f64<LAT_BL>(accb, s8 + 8u * 64u * v, own_re);
-                    x[decltype(p)::value].im = rot_digit_f64<LAT_BL>(accb, s8 + 8u * 64u * v + 8u * M, own_im);
+                    x[decltype(p)::value].re = rot_digit_f64<LAT_BL>(accb, s8 + 8u * 64u * v, own_re[v]);
+                    x[decltype(p)::value].im = rot_digit_f64<LAT_BL>(accb, s8 + 8u * 64u * v + 8u * M, own_im[v]);
                 });
                 Fft3::pre_twist(x);
                 ta = &tab->ta_fwd[0][0]; ta_stride = 64; ta_idx = t;
@@ -149,8 +156,10 @@ blind_rotate_lat_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride, 
                 Fft3::post_twist(x);
                 static_for<0, 16>([&](auto q) {
                     const int c = t + 64 * decltype(q)::value;
-                    acc_r[c] += torus_from_double<T>(x[decltype(q)::value].re);
-                    acc_r[c + M] += torus_from_double<T>(-x[decltype(q)::value].im);
+                    own_re[decltype(q)::value] += torus_from_double<T>(x[decltype(q)::value].re);
+                    own_im[decltype(q)::value] += torus_from_double<T>(-x[decltype(q)::value].im);
+                    acc_r[c] = own_re[decltype(q)::value];
+                    acc_r[c + M] = own_im[decltype(q)::value];
                 });
                 named_bar_sync(1 + r, 64);
             }

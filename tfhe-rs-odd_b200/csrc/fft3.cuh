@@ -44,23 +44,29 @@ struct Fft3 {
 
     // ta: table base; entry g2 of this thread is ta[g2 * ta_stride + ta_idx] (forward: stride 64, idx tau; inverse: 4, tau>>4)
     HD static void pass_a(int tau, cplx (&x)[16], const cplx *ta, int ta_stride, int ta_idx, cplx *buf1) {
+        cplx w[16];   // fetched before the butterflies so that their latency hides behind the arithmetic
+        static_for<0, 16>([&](auto g2) { w[decltype(g2)::value] = ta[decltype(g2)::value * ta_stride + ta_idx]; });
         fft_dit<16, -1>(x);
         static_for<0, 16>([&](auto g2) {
             constexpr int g = decltype(g2)::value;
-            buf1[tau * ROW + g] = cmul(x[g], ta[g * ta_stride + ta_idx]);
+            buf1[tau * ROW + g] = cmul(x[g], w[g]);
         });
     }
     // team sync before and after
     HD static void pass_b(int beta, const cplx *tb, const cplx *buf1, cplx *buf2) {
         const int j1 = beta & 15, gq = beta >> 4;
+        cplx y[4][4], w[4][4];
+        static_for<0, 16>([&](auto i) {
+            constexpr int e = decltype(i)::value >> 2, pu = decltype(i)::value & 3;
+            y[e][pu] = buf1[(j1 + 16 * brev(pu, 2)) * ROW + 4 * gq + e];
+        });
+        static_for<0, 16>([&](auto i) { w[decltype(i)::value >> 2][decltype(i)::value & 3] = tb[decltype(i)::value * 64 + beta]; });
         static_for<0, 4>([&](auto e_) {
             constexpr int e = decltype(e_)::value;
-            cplx y[4];
-            static_for<0, 4>([&](auto pu) { y[decltype(pu)::value] = buf1[(j1 + 16 * brev(decltype(pu)::value, 2)) * ROW + 4 * gq + e]; });
-            fft_dit<4, -1>(y);
+            fft_dit<4, -1>(y[e]);
             static_for<0, 4>([&](auto g1) {
                 constexpr int g = decltype(g1)::value;
-                buf2[(16 * g + 4 * gq + e) * ROW + j1] = cmul(y[g], tb[(e * 4 + g) * 64 + beta]);
+                buf2[(16 * g + 4 * gq + e) * ROW + j1] = cmul(y[e][g], w[e][g]);
             });
         });
     }
