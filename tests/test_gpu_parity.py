@@ -310,3 +310,36 @@ def test_warp_specialised_blind_rotation_variant():
                         "(test_pbs_decrypts_like_oracle or test_ks_pbs_like_oracle) and (TOY_2_2 or MESSAGE_2_CARRY_2)"],
                        env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+@pytest.mark.parametrize("B", [1, 3, 149])
+def test_latency_kernel_batches(ctx, B):
+    """blind_rotate_lat.cu (one ciphertext per CTA, batches <= 296 at PARAM_MESSAGE_2_CARRY_2): per-ciphertext LUT index,
+    decrypted outputs equal to the oracle's where it is run (the first ciphertexts), LUT(msg) everywhere, and the GLWE
+    epilogue consistent with the sample-extracting one bit for bit."""
+    import tfhe_rs_odd_b200 as t
+    o, p, bsk, ksk, msgs, pts, luts, idx, expect = _pbs_case(ctx, "MESSAGE_2_CARRY_2", B, seed=31)
+    cts = o.encrypt(pts, "small", seed=0x1A7 + B)
+    got = t.programmable_bootstrap_lwe_ciphertext(cts, luts, bsk, lut_idx=idx)
+    dec = o.decode(o.phase(got, "big"))
+    assert np.array_equal(dec % o.pmod, expect)
+    m = min(B, 3)
+    ref = o.pbs(cts[:m], luts, None if idx is None else idx[:m])
+    ph_ref, ph_got = o.phase(ref, "big"), o.phase(got[:m], "big")
+    assert np.array_equal(o.decode(ph_ref), dec[:m])
+    assert (np.abs(_sdiff(ph_got, ph_ref, 64)).astype(np.float64) / 2.0 ** 64).max() < phase_bound(o)
+    glwe = t.programmable_bootstrap_lwe_ciphertext_without_sample_extract(cts, luts, bsk, lut_idx=idx)
+    assert np.array_equal(t.extract_lwe_sample_from_glwe_ciphertext(ctx, glwe, o.k, o.N, 64), got)
+    assert np.array_equal(t.programmable_bootstrap_lwe_ciphertext(cts, luts, bsk, lut_idx=idx), got)   # deterministic
+
+
+@pytest.mark.parametrize("env", [{"B200TFHE_LAT_MAX": "0"}, {"B200TFHE_LAT_MAX": "0", "B200TFHE_NO_TMEM": "1"}],
+                         ids=["tmem_kernel_small_batches", "generic_kernel"])
+def test_other_2_2_kernels_on_small_batches(env):
+    """The default dispatch sends small PARAM_MESSAGE_2_CARRY_2 batches to the latency kernel; the TMEM kernel (ghost
+    ciphertexts in its last CTA) and the generic kernel must stay parity-green on the same cases."""
+    import subprocess, sys, os
+    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-m", "gpu", __file__, "-k",
+                        "(test_pbs_decrypts_like_oracle or test_ks_pbs_like_oracle) and (TOY_2_2 or MESSAGE_2_CARRY_2)"],
+                       env=dict(os.environ, **env), capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
