@@ -32,11 +32,14 @@ def flop_per_pbs(n, k, N, l):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--only", default="", help="substring of the config names to run")
     args = ap.parse_args()
     ctx = t.Context(0)
     rng = np.random.default_rng(1)
     out = {}
     for name, (n, k, N, b, l, bks, lks, bits, B) in CONFIGS.items():
+        if args.only not in name:
+            continue
         dt = np.uint64 if bits == 64 else np.uint32
         p = t.core_crypto.make_params(n, k, N, b, l, bks, lks, bits)
         big = k * N
