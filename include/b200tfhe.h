@@ -83,6 +83,27 @@ int b200tfhe_bsk_alloc(b200tfhe_context *ctx, const b200tfhe_params *p, b200tfhe
 int b200tfhe_bsk_device_buffer(const b200tfhe_bsk *bsk, void **d_ptr, size_t *bytes);
 int b200tfhe_bsk_destroy(b200tfhe_bsk *bsk);
 
+/* ---- multi-bit bootstrap keys ----------------------------------------------------------------
+ * LweMultiBitBootstrapKey (core_crypto/entities/lwe_multi_bit_bootstrap_key.rs; generation
+ * algorithms/lwe_multi_bit_bootstrap_key_generation.rs:87-172): standard-domain layout
+ * [n/G][2^G][level 1..l][row 0..k][poly 0..k][N], G = LweBskGroupingFactor.  Replaces
+ * par_convert_standard_lwe_multi_bit_bootstrap_key_to_fourier (algorithms/lwe_multi_bit_bootstrap_key_conversion.rs).
+ * The returned handle is an ordinary b200tfhe_bsk: every pbs / blind_rotate / ks_pbs / pbs_ks / wave entry point accepts
+ * it and then computes multi_bit_(deterministic_)programmable_bootstrap_lwe_ciphertext
+ * (algorithms/lwe_multi_bit_programmable_bootstrapping.rs:1035-1224) with n/G sequential iterations, as shortint
+ * dispatches on ShortintBootstrappingKey::{Classic, MultiBit} (shortint/server_key/mod.rs:798-851).  The reference's
+ * thread_count / deterministic_execution knobs have no counterpart: groups are always consumed in ascending order.
+ * Only 64-bit sets exist in the reference (shortint/parameters/multi_bit.rs). */
+int b200tfhe_multibit_bsk_upload_u64(b200tfhe_context *ctx, const b200tfhe_params *p, uint32_t grouping_factor,
+                                     const uint64_t *std_bsk, b200tfhe_bsk **out);
+int b200tfhe_multibit_bsk_convert_dev(b200tfhe_context *ctx, const b200tfhe_params *p, uint32_t grouping_factor,
+                                      const void *d_std_bsk, b200tfhe_bsk **out);
+int b200tfhe_multibit_bsk_alloc(b200tfhe_context *ctx, const b200tfhe_params *p, uint32_t grouping_factor, b200tfhe_bsk **out);
+/* 1 for a classic key, G for a multi-bit key */
+uint32_t b200tfhe_bsk_grouping_factor(const b200tfhe_bsk *bsk);
+/* 1 if the multi-bit blind rotation is built for this parameter set and grouping factor, else 0 */
+int b200tfhe_multibit_params_supported(const b200tfhe_params *p, uint32_t grouping_factor);
+
 /* uploads an LweKeyswitchKey (input dim k*N, output dim n); uses p->{lwe_dimension, glwe_dimension,
  * polynomial_size, ks_*, torus_bits} */
 int b200tfhe_ksk_upload_u64(b200tfhe_context *ctx, const b200tfhe_params *p, const uint64_t *ksk, b200tfhe_ksk **out);

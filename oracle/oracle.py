@@ -32,11 +32,21 @@ PARAMS = {
     "TOY_2_2": (12, 1, 2048, 23, 1, 3, 5, 64, 1e-9, 0.00000000000000029403601535432533, 16, "ks_pbs"),
     "TOY_3_3": (6, 1, 8192, 15, 2, 3, 6, 64, 1e-9, 0.0000000000000000002168404344971009, 64, "ks_pbs"),
     "TOY_1_1": (12, 3, 512, 18, 1, 4, 3, 64, 1e-9, 0.0000000000034525330484572114, 4, "ks_pbs"),
+    # multi-bit PBS sets (shortint/parameters/multi_bit.rs:115-132 group 2, :173-190 group 3) and toy versions
+    "MULTI_BIT_2_2_GROUP_2": (818, 1, 2048, 22, 1, 5, 3, 64, 0.000002226459789930014, 0.0000000000000003152931493498455, 16, "ks_pbs"),
+    "MULTI_BIT_2_2_GROUP_3": (888, 1, 2048, 21, 1, 7, 2, 64, 0.0000006125031601933181, 0.0000000000000003152931493498455, 16, "ks_pbs"),
+    "TOY_MB_G2": (12, 1, 512, 12, 2, 4, 4, 64, 1e-9, 1e-15, 4, "ks_pbs"),
+    "TOY_MB_G3": (12, 1, 512, 12, 2, 4, 4, 64, 1e-9, 1e-15, 4, "ks_pbs"),
+    "TOY_MB22_G2": (12, 1, 2048, 22, 1, 5, 3, 64, 1e-9, 0.0000000000000003152931493498455, 16, "ks_pbs"),
+    "TOY_MB22_G3": (12, 1, 2048, 21, 1, 7, 2, 64, 1e-9, 0.0000000000000003152931493498455, 16, "ks_pbs"),
     # the sets of the committed golden fixtures (tests/golden/): n = 4 keeps the stored keys small
     "GOLD_U64": (4, 1, 512, 12, 2, 4, 4, 64, 1e-9, 1e-15, 4, "ks_pbs"),
     "GOLD_U32": (4, 2, 512, 6, 3, 3, 4, 32, 1e-7, 1e-8, 0, "pbs_ks"),
     "GOLD_2_2": (4, 1, 2048, 23, 1, 3, 5, 64, 1e-9, 0.00000000000000029403601535432533, 16, "ks_pbs"),
 }
+
+# LweBskGroupingFactor of the multi-bit sets (absent = classic bootstrap key)
+GROUPING = {"MULTI_BIT_2_2_GROUP_2": 2, "MULTI_BIT_2_2_GROUP_3": 3, "TOY_MB_G2": 2, "TOY_MB_G3": 3, "TOY_MB22_G2": 2, "TOY_MB22_G3": 3}
 
 
 def build(force=False):
@@ -80,6 +90,9 @@ class Oracle:
         self.n, self.k, self.N = t[0], t[1], t[2]
         self.l, self.b, self.l_ks, self.b_ks, self.bits = t[4], t[3], t[6], t[5], t[7]
         self.pmod, self.order = t[10], t[11]
+        self.grouping = GROUPING.get(name, 0)
+        # number of GGSW ciphertexts of the bootstrap key: n (classic) or n/G * 2^G (multi-bit)
+        self.n_ggsw = self.n if not self.grouping else self.n // self.grouping * (1 << self.grouping)
         self.seed = seed
         self.nthreads = nthreads or os.cpu_count()
         self.big = self.k * self.N
@@ -99,24 +112,31 @@ class Oracle:
             L.orc_gen_binary_key(C.c_uint64(self.seed), self.n, _p(self.small_key))
             L.orc_gen_binary_key(C.c_uint64(self.seed + 1), self.big, _p(self.glwe_key))
             self.ksk = np.zeros(self.big * self.l_ks * (self.n + 1), np.uint64)
-            self.bsk = np.zeros(self.n * self.l * (self.k + 1) ** 2 * self.N, np.uint64)
+            self.bsk = np.zeros(self.n_ggsw * self.l * (self.k + 1) ** 2 * self.N, np.uint64)
             L.orc_gen_ksk(C.byref(self.p), _p(self.glwe_key), _p(self.small_key), C.c_uint64(self.seed + 2), _p(self.ksk), self.nthreads)
-            L.orc_gen_bsk(C.byref(self.p), _p(self.small_key), _p(self.glwe_key), C.c_uint64(self.seed + 3), _p(self.bsk), self.nthreads)
+            if self.grouping:
+                L.orc_gen_multibit_bsk(C.byref(self.p), self.grouping, _p(self.small_key), _p(self.glwe_key), C.c_uint64(self.seed + 3), _p(self.bsk), self.nthreads)
+            else:
+                L.orc_gen_bsk(C.byref(self.p), _p(self.small_key), _p(self.glwe_key), C.c_uint64(self.seed + 3), _p(self.bsk), self.nthreads)
             try:
                 os.makedirs(os.path.dirname(cache), exist_ok=True)
                 np.savez(cache, s=self.small_key, g=self.glwe_key, ksk=self.ksk, bsk=self.bsk)
             except OSError:
                 pass
         if fourier:
-            self.fbsk = np.zeros(self.bsk.size, np.float64)
-            L.orc_bsk_to_fourier(C.byref(self.p), _p(self.bsk), _p(self.fbsk), self.nthreads)
+            self._to_fourier()
         return self
+
+    def _to_fourier(self):
+        pf = OrcParams(*[getattr(self.p, f) for f, _ in OrcParams._fields_])
+        pf.n = self.n_ggsw      # the conversion is per GGSW polynomial: same routine for classic and multi-bit keys
+        self.fbsk = np.zeros(self.bsk.size, np.float64)
+        lib().orc_bsk_to_fourier(C.byref(pf), _p(self.bsk), _p(self.fbsk), self.nthreads)
 
     def load_keys(self, small_key, glwe_key, ksk, bsk):
         """Install externally stored keys (golden fixtures) instead of generating them."""
         self.small_key, self.glwe_key, self.ksk, self.bsk = u64(small_key), u64(glwe_key), u64(ksk), u64(bsk)
-        self.fbsk = np.zeros(self.bsk.size, np.float64)
-        lib().orc_bsk_to_fourier(C.byref(self.p), _p(self.bsk), _p(self.fbsk), self.nthreads)
+        self._to_fourier()
         return self
 
     # ---- ciphertexts ------------------------------------------------------------------------
@@ -192,6 +212,9 @@ class Oracle:
 
     def ks_pbs(self, cts, luts, lut_idx=None):
         L = lib()
+        if self.grouping:
+            return self._batch(lambda *a: L.orc_multibit_batch(C.byref(self.p), self.grouping, 0, _p(self.ksk), _p(self.fbsk), *a),
+                               cts, luts, lut_idx, self.big + 1, self.big + 1)
         return self._batch(lambda *a: L.orc_ks_pbs_batch(C.byref(self.p), _p(self.ksk), _p(self.fbsk), *a),
                            cts, luts, lut_idx, self.big + 1, self.big + 1)
 
@@ -203,6 +226,9 @@ class Oracle:
     def pbs(self, cts, luts, lut_idx=None, sample_extract=True):
         L = lib()
         od = self.big + 1 if sample_extract else self.glwe_len
+        if self.grouping:
+            return self._batch(lambda *a: L.orc_multibit_batch(C.byref(self.p), self.grouping, 2 if sample_extract else 3, None, _p(self.fbsk), *a),
+                               cts, luts, lut_idx, self.n + 1, od)
         return self._batch(lambda *a: L.orc_pbs_batch(C.byref(self.p), _p(self.fbsk), *a, 1 if sample_extract else 0),
                            cts, luts, lut_idx, self.n + 1, od)
 

@@ -123,10 +123,70 @@ void orc_pbs(const orc_params *p, const double *fbsk, const uint64_t *lwe_in, co
     free(acc);
 }
 
+/* ---- multi-bit PBS: algorithms/lwe_multi_bit_programmable_bootstrapping.rs -------------------------------------------- */
+/* prepare_multi_bit_ggsw_mem_optimized :18-85.  group_f: the 2^G Fourier GGSWs of one group; out = GGSW_0 +
+ * sum_{idx>=1} GGSW_idx (.) FFT(X^{modswitch(sum of the selected mask elements)}).  The reference obtains the monomial's
+ * transform from Plan::fwd_monomial times a twist factor (fft/mod.rs:408-445); that is the forward transform of the
+ * monomial, which is what is computed here. */
+static void multibit_prepare_ggsw(const orc_params *p, int G, const double *group_f, const uint64_t *mask_elems, double *out,
+                                  uint64_t *mono, double *mono_f) {
+    int N = p->N, M = N / 2, k1 = p->k + 1, bits = p->bits;
+    int log2N = 0; while ((1 << log2N) < N) log2N++;
+    size_t npoly = (size_t)p->pbs_level * k1 * k1, ggsw_sz = npoly * N;
+    memcpy(out, group_f, sizeof(double) * ggsw_sz);
+    for (int idx = 1; idx < (1 << G); idx++) {
+        uint64_t deg = 0;
+        for (int b = 0; b < G; b++) if ((idx >> (G - (b + 1))) & 1) deg += mask_elems[b];
+        uint64_t sw = orc_modswitch(deg & maskw(bits), log2N, bits);       /* in [0, 2N] */
+        memset(mono, 0, sizeof(uint64_t) * N);
+        mono[sw % N] = ((sw / N) & 1) ? maskw(bits) : 1;                    /* X^N = -1 */
+        orc_fft_forward_integer(N, mono, bits, mono_f);
+        const double *g = group_f + (size_t)idx * ggsw_sz;
+        for (size_t q = 0; q < npoly; q++) orc_fourier_mac(M, out + q * N, g + q * N, mono_f);
+    }
+}
+
+/* multi_bit_deterministic_blind_rotate_assign :548-… (groups consumed in ascending order; the non-deterministic variant
+ * :295-546 consumes them in whatever order its producer threads deliver, which changes only f64 rounding).
+ * mb_fbsk: [n/G][2^G] Fourier GGSWs. */
+void orc_multibit_blind_rotate(const orc_params *p, int G, const double *mb_fbsk, const uint64_t *lwe, uint64_t *acc) {
+    int N = p->N, k1 = p->k + 1, n = p->n, bits = p->bits;
+    int log2N = 0; while ((1 << log2N) < N) log2N++;
+    size_t tot = (size_t)k1 * N;
+    size_t ggsw_sz = (size_t)p->pbs_level * k1 * k1 * N;
+    uint64_t *src = (uint64_t *)malloc(sizeof(uint64_t) * tot), *mono = (uint64_t *)malloc(sizeof(uint64_t) * N);
+    double *buf = (double *)malloc(sizeof(double) * ggsw_sz), *mono_f = (double *)malloc(sizeof(double) * N);
+    uint64_t bhat = orc_modswitch(lwe[n], log2N, bits);
+    for (int j = 0; j < k1; j++) orc_monomial_div(src + (size_t)j * N, acc + (size_t)j * N, N, bhat, bits);
+    for (int gi = 0; gi < n / G; gi++) {
+        multibit_prepare_ggsw(p, G, mb_fbsk + (size_t)gi * (1 << G) * ggsw_sz, lwe + (size_t)gi * G, buf, mono, mono_f);
+        memset(acc, 0, sizeof(uint64_t) * tot);                   /* dst_ct.as_mut().fill(ZERO) */
+        orc_add_external_product(p, acc, buf, src);
+        memcpy(src, acc, sizeof(uint64_t) * tot);
+    }
+    memcpy(acc, src, sizeof(uint64_t) * tot);
+    free(src); free(mono); free(buf); free(mono_f);
+}
+
+/* multi_bit_(deterministic_)programmable_bootstrap_lwe_ciphertext :1035-1224 */
+void orc_multibit_pbs(const orc_params *p, int G, const double *mb_fbsk, const uint64_t *lwe_in, const uint64_t *lut, uint64_t *lwe_out) {
+    size_t tot = (size_t)(p->k + 1) * p->N;
+    uint64_t *acc = (uint64_t *)malloc(sizeof(uint64_t) * tot);
+    memcpy(acc, lut, sizeof(uint64_t) * tot);
+    orc_multibit_blind_rotate(p, G, mb_fbsk, lwe_in, acc);
+    orc_sample_extract0(lwe_out, acc, p->k, p->N, p->bits);
+    free(acc);
+}
+
 typedef struct {
     const orc_params *p; const uint64_t *ksk; const double *fbsk; const uint64_t *in; const uint64_t *luts;
     const uint32_t *lut_idx; uint64_t *out; int mode; /* 0 ks->pbs, 1 pbs->ks, 2 pbs, 3 blind rotate only */
+    int grouping;     /* 0: classic bootstrap key; G >= 2: multi-bit key with grouping factor G */
 } batch_ctx;
+static void any_pbs(const batch_ctx *x, const uint64_t *in, const uint64_t *lut, uint64_t *out) {
+    if (x->grouping) orc_multibit_pbs(x->p, x->grouping, x->fbsk, in, lut, out);
+    else orc_pbs(x->p, x->fbsk, in, lut, out);
+}
 static void batch_one(void *c, int i) {
     batch_ctx *x = (batch_ctx *)c;
     const orc_params *p = x->p;
@@ -135,33 +195,42 @@ static void batch_one(void *c, int i) {
     if (x->mode == 0) {
         uint64_t *mid = (uint64_t *)malloc(sizeof(uint64_t) * small);
         orc_keyswitch(p, x->ksk, x->in + (size_t)i * big, mid);
-        orc_pbs(p, x->fbsk, mid, lut, x->out + (size_t)i * big);
+        any_pbs(x, mid, lut, x->out + (size_t)i * big);
         free(mid);
     } else if (x->mode == 1) {
         uint64_t *mid = (uint64_t *)malloc(sizeof(uint64_t) * big);
-        orc_pbs(p, x->fbsk, x->in + (size_t)i * small, lut, mid);
+        any_pbs(x, x->in + (size_t)i * small, lut, mid);
         orc_keyswitch(p, x->ksk, mid, x->out + (size_t)i * small);
         free(mid);
     } else if (x->mode == 2) {
-        orc_pbs(p, x->fbsk, x->in + (size_t)i * small, lut, x->out + (size_t)i * big);
+        any_pbs(x, x->in + (size_t)i * small, lut, x->out + (size_t)i * big);
     } else {
         uint64_t *acc = x->out + (size_t)i * glwe;
         memcpy(acc, lut, sizeof(uint64_t) * glwe);
-        orc_blind_rotate(p, x->fbsk, x->in + (size_t)i * small, acc);
+        if (x->grouping) orc_multibit_blind_rotate(p, x->grouping, x->fbsk, x->in + (size_t)i * small, acc);
+        else orc_blind_rotate(p, x->fbsk, x->in + (size_t)i * small, acc);
     }
 }
 void orc_ks_pbs_batch(const orc_params *p, const uint64_t *ksk, const double *fbsk, const uint64_t *in,
                       const uint64_t *luts, const uint32_t *lut_idx, uint64_t *out, int batch, int nthreads) {
-    batch_ctx c = { p, ksk, fbsk, in, luts, lut_idx, out, 0 };
+    batch_ctx c = { p, ksk, fbsk, in, luts, lut_idx, out, 0, 0 };
     orc_parallel_for(batch_one, &c, batch, nthreads);
 }
 void orc_pbs_ks_batch(const orc_params *p, const uint64_t *ksk, const double *fbsk, const uint64_t *in,
                       const uint64_t *luts, const uint32_t *lut_idx, uint64_t *out, int batch, int nthreads) {
-    batch_ctx c = { p, ksk, fbsk, in, luts, lut_idx, out, 1 };
+    batch_ctx c = { p, ksk, fbsk, in, luts, lut_idx, out, 1, 0 };
     orc_parallel_for(batch_one, &c, batch, nthreads);
 }
 void orc_pbs_batch(const orc_params *p, const double *fbsk, const uint64_t *in, const uint64_t *luts,
                    const uint32_t *lut_idx, uint64_t *out, int batch, int nthreads, int sample_extract) {
-    batch_ctx c = { p, NULL, fbsk, in, luts, lut_idx, out, sample_extract ? 2 : 3 };
+    batch_ctx c = { p, NULL, fbsk, in, luts, lut_idx, out, sample_extract ? 2 : 3, 0 };
+    orc_parallel_for(batch_one, &c, batch, nthreads);
+}
+
+/* shortint ServerKey with ShortintBootstrappingKey::MultiBit (shortint/server_key/mod.rs:829-851), batched.
+ * mode: 0 KS->PBS, 2 PBS, 3 blind rotation without sample extract */
+void orc_multibit_batch(const orc_params *p, int grouping, int mode, const uint64_t *ksk, const double *mb_fbsk, const uint64_t *in,
+                        const uint64_t *luts, const uint32_t *lut_idx, uint64_t *out, int batch, int nthreads) {
+    batch_ctx c = { p, ksk, mb_fbsk, in, luts, lut_idx, out, mode, grouping };
     orc_parallel_for(batch_one, &c, batch, nthreads);
 }

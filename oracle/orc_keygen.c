@@ -92,29 +92,58 @@ static void glwe_encrypt_assign(const orc_params *p, const uint64_t *glwe_key, u
     for (int t = 0; t < N; t++) body[t] = (body[t] + torus_noise(r, p->glwe_std, p->bits)) & m;
 }
 
-/* algorithms/lwe_bootstrap_key_generation.rs:113-133 + ggsw_encryption.rs:100-150,300-331.
- * Layout [n][level 1..l][row 0..k][poly 0..k][N] (entities/lwe_bootstrap_key.rs:99-106, ggsw_ciphertext.rs:185-197). */
-typedef struct { const orc_params *p; const uint64_t *small, *glwe_key; uint64_t seed; uint64_t *bsk; } bsk_ctx;
-static void bsk_one(void *c, int i) {
-    bsk_ctx *x = (bsk_ctx *)c; const orc_params *p = x->p;
+/* ggsw_encryption.rs:100-150,300-331 (encrypt_constant_ggsw_ciphertext): GGSW of the constant `msg`,
+ * layout [level 1..l][row 0..k][poly 0..k][N] (entities/ggsw_ciphertext.rs:185-197). */
+static void ggsw_encrypt_constant(const orc_params *p, const uint64_t *glwe_key, uint64_t msg, rng_t *r, uint64_t *ggsw, uint64_t *scratch) {
     int N = p->N, k = p->k, k1 = k + 1, L = p->pbs_level; uint64_t m = maskw(p->bits);
-    rng_t r; rng_seed(&r, x->seed, 0x2000000ULL + (uint64_t)i);
-    uint64_t *scratch = (uint64_t *)malloc(sizeof(uint64_t) * N);
-    uint64_t msg = x->small[i];
-    uint64_t *ggsw = x->bsk + (size_t)i * L * k1 * k1 * N;
     for (int lvl = 1; lvl <= L; lvl++) {
         uint64_t factor = ((0 - msg) << (p->bits - p->pbs_base_log * lvl)) & m; /* ggsw_encryption.rs:121-125 */
         for (int row = 0; row < k1; row++) {
             uint64_t *g = ggsw + ((size_t)(lvl - 1) * k1 + row) * k1 * N;
             uint64_t *body = g + (size_t)k * N;
-            if (row < k) for (int t = 0; t < N; t++) body[t] = (x->glwe_key[(size_t)row * N + t] * factor) & m;
+            if (row < k) for (int t = 0; t < N; t++) body[t] = (glwe_key[(size_t)row * N + t] * factor) & m;
             else { memset(body, 0, sizeof(uint64_t) * N); body[0] = (0 - factor) & m; }
-            glwe_encrypt_assign(p, x->glwe_key, g, &r, scratch);
+            glwe_encrypt_assign(p, glwe_key, g, r, scratch);
         }
     }
+}
+
+/* algorithms/lwe_bootstrap_key_generation.rs:113-133.
+ * Layout [n][level 1..l][row 0..k][poly 0..k][N] (entities/lwe_bootstrap_key.rs:99-106). */
+typedef struct { const orc_params *p; const uint64_t *small, *glwe_key; uint64_t seed; uint64_t *bsk; int grouping; } bsk_ctx;
+static void bsk_one(void *c, int i) {
+    bsk_ctx *x = (bsk_ctx *)c; const orc_params *p = x->p;
+    int N = p->N, k1 = p->k + 1, L = p->pbs_level;
+    rng_t r; rng_seed(&r, x->seed, 0x2000000ULL + (uint64_t)i);
+    uint64_t *scratch = (uint64_t *)malloc(sizeof(uint64_t) * N);
+    ggsw_encrypt_constant(p, x->glwe_key, x->small[i], &r, x->bsk + (size_t)i * L * k1 * k1 * N, scratch);
     free(scratch);
 }
 void orc_gen_bsk(const orc_params *p, const uint64_t *small_key, const uint64_t *glwe_key, uint64_t seed, uint64_t *bsk, int nthreads) {
-    bsk_ctx c = { p, small_key, glwe_key, seed, bsk };
+    bsk_ctx c = { p, small_key, glwe_key, seed, bsk, 0 };
     orc_parallel_for(bsk_one, &c, p->n, nthreads);
+}
+
+/* algorithms/lwe_multi_bit_bootstrap_key_generation.rs:87-172 + combine_key_bits :401-427.
+ * Layout [n/G][2^G][level][row][poly][N] (entities/lwe_multi_bit_bootstrap_key.rs): GGSW `idx` of a group encrypts
+ * prod_b (s_b XOR NOT bit_b(idx)), bit position of key element b = G - (b+1): idx 0 is prod (1 - s_b). */
+static void mb_bsk_one(void *c, int gi) {
+    bsk_ctx *x = (bsk_ctx *)c; const orc_params *p = x->p;
+    int N = p->N, k1 = p->k + 1, L = p->pbs_level, G = x->grouping, NG = 1 << G;
+    uint64_t *scratch = (uint64_t *)malloc(sizeof(uint64_t) * N);
+    for (int idx = 0; idx < NG; idx++) {
+        rng_t r; rng_seed(&r, x->seed, 0x3000000ULL + (uint64_t)gi * NG + idx);
+        uint64_t msg = 1;
+        for (int b = 0; b < G; b++) {
+            uint64_t inv = (uint64_t)(((idx >> (G - (b + 1))) & 1) ^ 1);
+            msg *= (x->small[(size_t)gi * G + b] ^ inv);
+        }
+        ggsw_encrypt_constant(p, x->glwe_key, msg, &r, x->bsk + ((size_t)gi * NG + idx) * L * k1 * k1 * N, scratch);
+    }
+    free(scratch);
+}
+void orc_gen_multibit_bsk(const orc_params *p, int grouping, const uint64_t *small_key, const uint64_t *glwe_key, uint64_t seed,
+                          uint64_t *bsk, int nthreads) {
+    bsk_ctx c = { p, small_key, glwe_key, seed, bsk, grouping };
+    orc_parallel_for(mb_bsk_one, &c, p->n / grouping, nthreads);
 }

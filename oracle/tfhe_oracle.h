@@ -82,6 +82,13 @@ void orc_pbs_ks_batch(const orc_params *p, const uint64_t *ksk, const double *fb
 void orc_pbs_batch(const orc_params *p, const double *fbsk, const uint64_t *in, const uint64_t *luts,
                    const uint32_t *lut_idx, uint64_t *out, int batch, int nthreads, int sample_extract);
 
+/* ---- multi-bit PBS (algorithms/lwe_multi_bit_programmable_bootstrapping.rs) ---- */
+/* mb_fbsk: [n/G][2^G] Fourier GGSWs (orc_bsk_to_fourier with n := n/G * 2^G) */
+void orc_multibit_blind_rotate(const orc_params *p, int grouping, const double *mb_fbsk, const uint64_t *lwe_in, uint64_t *acc);
+void orc_multibit_pbs(const orc_params *p, int grouping, const double *mb_fbsk, const uint64_t *lwe_in, const uint64_t *lut, uint64_t *lwe_out);
+void orc_multibit_batch(const orc_params *p, int grouping, int mode, const uint64_t *ksk, const double *mb_fbsk, const uint64_t *in,
+                        const uint64_t *luts, const uint32_t *lut_idx, uint64_t *out, int batch, int nthreads);
+
 /* ---- LUTs and gate glue ---- */
 /* shortint/engine/mod.rs:72-128 ; f_table has p = msg_mod*carry_mod entries */
 void orc_fill_accumulator(const orc_params *p, const uint64_t *f_table, int pmod, uint64_t *glwe_out);
@@ -96,6 +103,9 @@ void orc_lwe_encrypt(int dim, int bits, const uint64_t *key, uint64_t plaintext,
 uint64_t orc_lwe_phase(int dim, int bits, const uint64_t *key, const uint64_t *ct);
 void orc_gen_ksk(const orc_params *p, const uint64_t *big_key, const uint64_t *small_key, uint64_t seed, uint64_t *ksk, int nthreads);
 void orc_gen_bsk(const orc_params *p, const uint64_t *small_key, const uint64_t *glwe_key, uint64_t seed, uint64_t *bsk, int nthreads);
+/* lwe_multi_bit_bootstrap_key_generation.rs:87-172: [n/G][2^G][l][k+1][k+1][N] */
+void orc_gen_multibit_bsk(const orc_params *p, int grouping, const uint64_t *small_key, const uint64_t *glwe_key, uint64_t seed,
+                          uint64_t *bsk, int nthreads);
 /* exact negacyclic product of a torus poly by a binary poly (limb-split FFT), used by GLWE encryption */
 void orc_negacyclic_mul_binary(int N, const uint64_t *a, const uint64_t *s_binary, uint64_t *out, int bits);
 

@@ -296,3 +296,65 @@ extern "C" int emul_blind_rotate_lat(int n, const uint64_t *bsk_std, const uint6
     }
     return 0;
 }
+
+// ---- multi-bit blind rotation (blind_rotate_mb.cu): same stage sequence, lanes executed one after another ------------
+#include "br_multibit.cuh"
+template <typename T, int R, int K, int L, int BL, int G>
+static int run_mb(const uint64_t *bsk_std, int n, const uint64_t *lwe, int batch, const uint64_t *lut, uint64_t *out) {
+    typedef MBCore<T, R, K, L, BL, G> C;
+    static TwTables<R> tw; fill_tw_tables(tw);
+    const int N = C::N, K1 = C::K1, NG = C::NG, ngroups = n / G;
+    std::vector<cplx> fbsk;
+    convert_bsk<T, R, K, L, BL>(bsk_std, ngroups * NG, fbsk);   // the key conversion is per GGSW polynomial
+    cplx wr[R];
+    for (int m = 0; m < R; m++) wr[m] = C::wr_entry(m);
+    std::vector<T> acc((size_t)K1 * N), lutT((size_t)K1 * N), mask(n);
+    std::vector<cplx> fbuf((size_t)K1 * L * C::REGION);
+    static cplx x[R][R];
+    static cplx F[K + 1][R][R];
+    for (size_t c = 0; c < lutT.size(); c++) lutT[c] = (T)lut[c];
+    for (int b = 0; b < batch; b++) {
+        const uint64_t *ct = lwe + (size_t)b * (n + 1);
+        for (int i = 0; i < n; i++) mask[i] = (T)ct[i];
+        int bhat = (int)(modswitch<T>((T)ct[n], C::LOGN) & (2 * N - 1));
+        int a0 = (2 * N - bhat) & (2 * N - 1);
+        for (int r = 0; r < K1; r++)
+            for (int c = 0; c < N; c++) acc[(size_t)r * N + c] = rot_read<T, N>(&lutT[(size_t)r * N], c, a0);
+        for (int gi = 0; gi < ngroups; gi++) {
+            uint16_t deg[C::NMONO];
+            for (int idx = 1; idx < NG; idx++) deg[idx - 1] = C::group_degree(&mask[(size_t)gi * G], idx);
+            for (int r = 0; r < K1; r++)
+                for (int lane = 0; lane < R; lane++)
+                    C::digits_plain_fwd_pass1(lane, &acc[(size_t)r * N], &fbuf[(size_t)r * L * C::REGION], tw.fwd);
+            for (int r = 0; r < K1; r++)
+                for (int t = 0; t < L; t++) {
+                    cplx *reg = &fbuf[(size_t)(r * L + t) * C::REGION];
+                    for (int lane = 0; lane < R; lane++) C::fwd_pass2_load(lane, x[lane], reg);
+                    for (int lane = 0; lane < R; lane++) C::fwd_pass2_store(lane, x[lane], reg);
+                }
+            const cplx *group = &fbsk[(size_t)gi * C::GROUP_CPLX];
+            for (int j = 0; j < K1; j++)
+                for (int lane = 0; lane < R; lane++) C::mb_mac(lane, j, group, fbuf.data(), deg, wr, F[j][lane]);
+            for (int j = 0; j < K1; j++)
+                for (int lane = 0; lane < R; lane++) C::inv_pass1(lane, F[j][lane], &fbuf[(size_t)j * L * C::REGION], tw.inv);
+            for (int j = 0; j < K1; j++)
+                for (int lane = 0; lane < R; lane++) C::inv_pass2_store(lane, &fbuf[(size_t)j * L * C::REGION], &acc[(size_t)j * N]);
+        }
+        for (size_t c = 0; c < acc.size(); c++) out[(size_t)b * K1 * N + c] = (uint64_t)acc[c];
+    }
+    return 0;
+}
+
+extern "C" int emul_multibit_blind_rotate(int n, int k, int N, int base_log, int level, int bits, int grouping,
+                                          const uint64_t *bsk_std, const uint64_t *lwe, int batch, const uint64_t *lut,
+                                          uint64_t *out_glwe) {
+#define CASE(T, R, K, L, BL, G) \
+    if (bits == (int)sizeof(T) * 8 && N == 2 * R * R && k == K && level == L && base_log == BL && grouping == G) \
+        return run_mb<T, R, K, L, BL, G>(bsk_std, n, lwe, batch, lut, out_glwe);
+    CASE(uint64_t, 16, 1, 2, 12, 2)
+    CASE(uint64_t, 16, 1, 2, 12, 3)
+    CASE(uint64_t, 32, 1, 1, 22, 2)
+    CASE(uint64_t, 32, 1, 1, 21, 3)
+#undef CASE
+    return 1;
+}

@@ -33,6 +33,11 @@ _PROTOS = {
     "b200tfhe_bsk_upload_u32": [_VP, C.POINTER(Params), _VP, _PP],
     "b200tfhe_bsk_convert_dev": [_VP, C.POINTER(Params), _VP, _PP],
     "b200tfhe_bsk_alloc": [_VP, C.POINTER(Params), _PP],
+    "b200tfhe_multibit_bsk_upload_u64": [_VP, C.POINTER(Params), _U32, _VP, _PP],
+    "b200tfhe_multibit_bsk_convert_dev": [_VP, C.POINTER(Params), _U32, _VP, _PP],
+    "b200tfhe_multibit_bsk_alloc": [_VP, C.POINTER(Params), _U32, _PP],
+    "b200tfhe_bsk_grouping_factor": [_VP],
+    "b200tfhe_multibit_params_supported": [C.POINTER(Params), _U32],
     "b200tfhe_bsk_device_buffer": [_VP, _PP, C.POINTER(_SZ)],
     "b200tfhe_bsk_destroy": [_VP],
     "b200tfhe_ksk_upload_u64": [_VP, C.POINTER(Params), _VP, _PP],
@@ -65,7 +70,8 @@ for _s in ("u64", "u32"):
     _PROTOS[f"b200tfhe_pbs_ks_batch_{_s}"] = [_VP, _VP, _VP, _VP, _VP, _VP, _U32, _VP, _U32]
     _PROTOS[f"b200tfhe_modulus_switch_{_s}"] = [_VP, _VP, _VP, _SZ, _U32]
     _PROTOS[f"b200tfhe_sample_extract_batch_{_s}"] = [_VP, _VP, _VP, _U32, _U32, _U32]
-_RESTYPES = {"b200tfhe_last_error": C.c_char_p, "b200tfhe_context_stream": C.c_void_p, "b200tfhe_launch_count": C.c_uint64}
+_RESTYPES = {"b200tfhe_last_error": C.c_char_p, "b200tfhe_context_stream": C.c_void_p, "b200tfhe_launch_count": C.c_uint64,
+             "b200tfhe_bsk_grouping_factor": C.c_uint32}
 
 EXPORTED_SYMBOLS = tuple(sorted(_PROTOS))
 

@@ -8,6 +8,9 @@ Names and argument meaning follow the reference (paths relative to /root/referen
   convert_standard_lwe_bootstrap_key_to_fourier       algorithms/lwe_bootstrap_key_conversion.rs:21-152
   extract_lwe_sample_from_glwe_ciphertext      algorithms/glwe_sample_extraction.rs:91-147
   fast_pbs_modulus_switch                      fft_impl/common.rs:26-43
+  convert_standard_lwe_multi_bit_bootstrap_key_to_fourier   algorithms/lwe_multi_bit_bootstrap_key_conversion.rs
+  multi_bit_programmable_bootstrap_lwe_ciphertext, multi_bit_blind_rotate_assign
+                                               algorithms/lwe_multi_bit_programmable_bootstrapping.rs:295-546,1035-1127
 The reference API is one ciphertext per call; every function here also accepts a list (2-D array), which is
 the unit the GPU works on.  Errors: the reference panics on dimension / modulus mismatch; here the C ABI
 returns non-zero and this layer raises B200TfheError with the library's message.
@@ -89,10 +92,18 @@ class FourierLweBootstrapKey:
         self.ctx.check(self.ctx._lib.b200tfhe_bsk_device_buffer(self._h, C.byref(p), C.byref(n)))
         return p.value, n.value
 
+    @property
+    def grouping_factor(self):
+        """1 for a classic key, LweBskGroupingFactor for a multi-bit key."""
+        return int(self.ctx._lib.b200tfhe_bsk_grouping_factor(self._h))
+
     @classmethod
-    def alloc(cls, ctx, params):
+    def alloc(cls, ctx, params, grouping_factor=1):
         h = C.c_void_p()
-        ctx.check(ctx._lib.b200tfhe_bsk_alloc(ctx._h, C.byref(params), C.byref(h)))
+        if grouping_factor > 1:
+            ctx.check(ctx._lib.b200tfhe_multibit_bsk_alloc(ctx._h, C.byref(params), int(grouping_factor), C.byref(h)))
+        else:
+            ctx.check(ctx._lib.b200tfhe_bsk_alloc(ctx._h, C.byref(params), C.byref(h)))
         return cls(ctx, params, h)
 
     def close(self):
@@ -123,6 +134,27 @@ def convert_standard_lwe_bootstrap_key_to_fourier(ctx, params, std_bsk):
 def convert_standard_lwe_bootstrap_key_to_fourier_dev(ctx, params, d_std_bsk_ptr):
     h = C.c_void_p()
     ctx.check(ctx._lib.b200tfhe_bsk_convert_dev(ctx._h, C.byref(params), C.c_void_p(d_std_bsk_ptr), C.byref(h)))
+    return FourierLweBootstrapKey(ctx, params, h)
+
+
+# FourierLweMultiBitBootstrapKey (fft_impl/fft64/crypto/bootstrap ... entities/lwe_multi_bit_bootstrap_key.rs): the same
+# device handle type with grouping_factor > 1
+FourierLweMultiBitBootstrapKey = FourierLweBootstrapKey
+
+
+def convert_standard_lwe_multi_bit_bootstrap_key_to_fourier(ctx, params, std_bsk, grouping_factor):
+    """std_bsk: flat [n/G][2^G][l][k+1][k+1][N] scalars (entities/lwe_multi_bit_bootstrap_key.rs) -> device Fourier key."""
+    if params.torus_bits != 64:
+        raise B200TfheError("multi-bit bootstrap keys exist for 64-bit parameter sets only")
+    G = int(grouping_factor)
+    a = np.ascontiguousarray(std_bsk, dtype=np.uint64).reshape(-1)
+    if G < 2 or params.lwe_dimension % G:
+        raise B200TfheError(f"grouping factor {G} must be >= 2 and divide the LWE dimension {params.lwe_dimension}")
+    expect = (params.lwe_dimension // G << G) * params.pbs_level * (params.glwe_dimension + 1) ** 2 * params.polynomial_size
+    if a.size != expect:
+        raise B200TfheError(f"multi-bit bootstrap key has {a.size} scalars, parameters imply {expect}")
+    h = C.c_void_p()
+    ctx.check(ctx._lib.b200tfhe_multibit_bsk_upload_u64(ctx._h, C.byref(params), G, _ptr(a), C.byref(h)))
     return FourierLweBootstrapKey(ctx, params, h)
 
 
@@ -294,3 +326,23 @@ def extract_lwe_sample_from_glwe_ciphertext(ctx, glwe, glwe_dimension, polynomia
     fn = getattr(ctx._lib, f"b200tfhe_sample_extract_batch_{_suf(bits)}")
     ctx.check(fn(ctx._h, _ptr(a), _ptr(out), glwe_dimension, polynomial_size, a.shape[0]))
     return out[0] if single else out
+
+
+# ---- multi-bit entry points: same kernels behind the same C calls, the key handle carries the grouping factor ---------
+def multi_bit_programmable_bootstrap_lwe_ciphertext(input_lwe, accumulator, multi_bit_bsk, output_lwe=None, lut_idx=None,
+                                                    thread_count=None):
+    """algorithms/lwe_multi_bit_programmable_bootstrapping.rs:1035-1127.  thread_count (the reference's CPU producer
+    threads per ciphertext) is accepted and ignored: the batch is the unit of parallelism here."""
+    if multi_bit_bsk.grouping_factor < 2:
+        raise B200TfheError("multi_bit_programmable_bootstrap_lwe_ciphertext needs a multi-bit bootstrap key")
+    return programmable_bootstrap_lwe_ciphertext(input_lwe, accumulator, multi_bit_bsk, output_lwe, lut_idx)
+
+
+multi_bit_deterministic_programmable_bootstrap_lwe_ciphertext = multi_bit_programmable_bootstrap_lwe_ciphertext
+
+
+def multi_bit_blind_rotate_assign(input_lwe, accumulator_glwe, multi_bit_bsk, thread_count=None):
+    """:295-546 (and the deterministic variant :548-...): acc <- multi-bit blind rotation, in place."""
+    if multi_bit_bsk.grouping_factor < 2:
+        raise B200TfheError("multi_bit_blind_rotate_assign needs a multi-bit bootstrap key")
+    return blind_rotate_assign(input_lwe, accumulator_glwe, multi_bit_bsk)

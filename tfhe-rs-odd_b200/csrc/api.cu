@@ -60,6 +60,7 @@ struct b200tfhe_bsk {
     Params p;
     void *d_fourier;
     size_t bytes;
+    int grouping = 0;    // 0: classic key (one GGSW per mask element); G >= 2: multi-bit key, 2^G GGSWs per G elements
 };
 struct b200tfhe_ksk {
     b200tfhe_context *ctx;
@@ -199,28 +200,45 @@ static int check_ks_params(b200tfhe_context *ctx, const Params &p) {
             "invalid keyswitch decomposition (base_log must be <= 7)");
     return 0;
 }
-static size_t bsk_polys(const Params &p) { return (size_t)p.n * p.pbs_level * (p.k + 1) * (p.k + 1); }
+// number of GGSW ciphertexts of a bootstrap key: n (classic) or n/G * 2^G (entities/lwe_multi_bit_bootstrap_key.rs)
+static size_t bsk_ggsw_count(const Params &p, int grouping) {
+    return grouping ? (size_t)(p.n / grouping) << grouping : (size_t)p.n;
+}
+static size_t bsk_polys(const Params &p, int grouping) { return bsk_ggsw_count(p, grouping) * p.pbs_level * (p.k + 1) * (p.k + 1); }
+static int bsk_radix(const Params &p, int grouping) { return grouping ? br_mb_supported(p, grouping) : br_supported(p); }
+static int check_bsk_params(b200tfhe_context *ctx, const Params &p, int grouping) {
+    if (!grouping) return check_pbs_params(ctx, p);
+    REQUIRE(p.bits == 64 || p.bits == 32, "only native 2^64 / 2^32 ciphertext moduli are supported");
+    REQUIRE(p.n > 0 && p.k > 0 && is_pow2(p.N), "invalid dimensions");
+    REQUIRE(p.pbs_level > 0 && p.pbs_base_log > 0 && p.pbs_level * p.pbs_base_log < p.bits, "invalid PBS decomposition");
+    // the reference asserts the same divisibility when it builds the key (lwe_multi_bit_bootstrap_key.rs, from_container)
+    REQUIRE(grouping >= 2 && grouping <= 4 && p.n % grouping == 0, "grouping factor must be 2..4 and divide the LWE dimension");
+    REQUIRE(br_mb_supported(p, grouping) != 0, "multi-bit blind rotation is not built for this (N, k, level, base_log, bits, grouping) set");
+    return 0;
+}
 
-int b200tfhe_bsk_alloc(b200tfhe_context *ctx, const b200tfhe_params *pp, b200tfhe_bsk **out) {
+static int bsk_alloc(b200tfhe_context *ctx, const b200tfhe_params *pp, int grouping, b200tfhe_bsk **out) {
     REQUIRE(ctx && pp && out, "bsk_alloc: null argument");
     *out = nullptr;
     Params p = to_params(pp);
-    if (check_pbs_params(ctx, p)) return 1;
+    if (check_bsk_params(ctx, p, grouping)) return 1;
     std::lock_guard<std::mutex> g(ctx->mu);
     CK(cudaSetDevice(ctx->device));
-    b200tfhe_bsk *k = new b200tfhe_bsk{ctx, p, nullptr, bsk_polys(p) * (p.N / 2) * sizeof(cplx)};
+    b200tfhe_bsk *k = new b200tfhe_bsk{ctx, p, nullptr, bsk_polys(p, grouping) * (p.N / 2) * sizeof(cplx), grouping};
     cudaError_t e = cudaMalloc(&k->d_fourier, k->bytes);
     if (e != cudaSuccess) { delete k; return fail_cuda(ctx, "cudaMalloc(bsk)", e); }
     *out = k;
     return 0;
 }
 
-int b200tfhe_bsk_convert_dev(b200tfhe_context *ctx, const b200tfhe_params *pp, const void *d_std, b200tfhe_bsk **out) {
+static int bsk_convert_dev(b200tfhe_context *ctx, const b200tfhe_params *pp, int grouping, const void *d_std, b200tfhe_bsk **out) {
     REQUIRE(ctx && pp && out && d_std, "bsk_convert_dev: null argument");
-    if (b200tfhe_bsk_alloc(ctx, pp, out)) return 1;
+    if (bsk_alloc(ctx, pp, grouping, out)) return 1;
     std::lock_guard<std::mutex> g(ctx->mu);
     Params p = (*out)->p;
-    int rc = bsk_convert_launch(p, d_std, (*out)->d_fourier, tw_fwd(ctx, br_supported(p)), ctx->stream);
+    int R = bsk_radix(p, grouping);
+    int rc = grouping ? bsk_convert_polys_launch(R, p.bits, bsk_polys(p, grouping), d_std, (*out)->d_fourier, tw_fwd(ctx, R), ctx->stream)
+                      : bsk_convert_launch(p, d_std, (*out)->d_fourier, tw_fwd(ctx, R), ctx->stream);
     ctx->launches++;
     if (rc) { b200tfhe_bsk_destroy(*out); *out = nullptr; return fail(ctx, "bsk_convert launch failed: " + std::to_string(rc)); }
     cudaError_t e = cudaStreamSynchronize(ctx->stream);
@@ -228,24 +246,53 @@ int b200tfhe_bsk_convert_dev(b200tfhe_context *ctx, const b200tfhe_params *pp, c
     return 0;
 }
 
-static int bsk_upload(b200tfhe_context *ctx, const b200tfhe_params *pp, const void *std_bsk, int bits, b200tfhe_bsk **out) {
+static int bsk_upload(b200tfhe_context *ctx, const b200tfhe_params *pp, int grouping, const void *std_bsk, int bits, b200tfhe_bsk **out) {
     REQUIRE(ctx && pp && out && std_bsk, "bsk_upload: null argument");
     *out = nullptr;
     REQUIRE(pp->torus_bits == bits, "bsk_upload: torus_bits does not match the entry point");
     Params p = to_params(pp);
-    if (check_pbs_params(ctx, p)) return 1;
+    if (check_bsk_params(ctx, p, grouping)) return 1;
     void *d_std = nullptr;
-    size_t bytes = bsk_polys(p) * p.N * sz(p);
+    size_t bytes = bsk_polys(p, grouping) * p.N * sz(p);
     CK(cudaSetDevice(ctx->device));
     CK(cudaMalloc(&d_std, bytes));
     cudaError_t e = cudaMemcpy(d_std, std_bsk, bytes, cudaMemcpyHostToDevice);
     if (e != cudaSuccess) { cudaFree(d_std); return fail_cuda(ctx, "cudaMemcpy(bsk)", e); }
-    int rc = b200tfhe_bsk_convert_dev(ctx, pp, d_std, out);
+    int rc = bsk_convert_dev(ctx, pp, grouping, d_std, out);
     cudaFree(d_std);
     return rc;
 }
-int b200tfhe_bsk_upload_u64(b200tfhe_context *ctx, const b200tfhe_params *p, const uint64_t *s, b200tfhe_bsk **out) { return bsk_upload(ctx, p, s, 64, out); }
-int b200tfhe_bsk_upload_u32(b200tfhe_context *ctx, const b200tfhe_params *p, const uint32_t *s, b200tfhe_bsk **out) { return bsk_upload(ctx, p, s, 32, out); }
+int b200tfhe_bsk_alloc(b200tfhe_context *ctx, const b200tfhe_params *p, b200tfhe_bsk **out) { return bsk_alloc(ctx, p, 0, out); }
+int b200tfhe_bsk_convert_dev(b200tfhe_context *ctx, const b200tfhe_params *p, const void *d_std, b200tfhe_bsk **out) { return bsk_convert_dev(ctx, p, 0, d_std, out); }
+int b200tfhe_bsk_upload_u64(b200tfhe_context *ctx, const b200tfhe_params *p, const uint64_t *s, b200tfhe_bsk **out) { return bsk_upload(ctx, p, 0, s, 64, out); }
+int b200tfhe_bsk_upload_u32(b200tfhe_context *ctx, const b200tfhe_params *p, const uint32_t *s, b200tfhe_bsk **out) { return bsk_upload(ctx, p, 0, s, 32, out); }
+
+// multi-bit keys (ShortintBootstrappingKey::MultiBit, shortint/server_key/mod.rs:103-111): same handle type, so every
+// pbs / ks_pbs / blind_rotate / wave entry point accepts them and runs n/G iterations
+static int check_grouping(b200tfhe_context *ctx, uint32_t grouping) {
+    REQUIRE(grouping >= 2 && grouping <= 4, "multibit: grouping factor must be 2, 3 or 4");
+    return 0;
+}
+int b200tfhe_multibit_bsk_alloc(b200tfhe_context *ctx, const b200tfhe_params *p, uint32_t grouping, b200tfhe_bsk **out) {
+    if (out) *out = nullptr;
+    if (check_grouping(ctx, grouping)) return 1;
+    return bsk_alloc(ctx, p, (int)grouping, out);
+}
+int b200tfhe_multibit_bsk_convert_dev(b200tfhe_context *ctx, const b200tfhe_params *p, uint32_t grouping, const void *d_std, b200tfhe_bsk **out) {
+    if (out) *out = nullptr;
+    if (check_grouping(ctx, grouping)) return 1;
+    return bsk_convert_dev(ctx, p, (int)grouping, d_std, out);
+}
+int b200tfhe_multibit_bsk_upload_u64(b200tfhe_context *ctx, const b200tfhe_params *p, uint32_t grouping, const uint64_t *s, b200tfhe_bsk **out) {
+    if (out) *out = nullptr;
+    if (check_grouping(ctx, grouping)) return 1;
+    return bsk_upload(ctx, p, (int)grouping, s, 64, out);
+}
+int b200tfhe_multibit_params_supported(const b200tfhe_params *p, uint32_t grouping) {
+    if (!p || grouping < 2 || grouping > 4) return 0;
+    return br_mb_supported(to_params(p), (int)grouping) != 0;
+}
+uint32_t b200tfhe_bsk_grouping_factor(const b200tfhe_bsk *bsk) { return bsk && bsk->grouping ? (uint32_t)bsk->grouping : 1u; }
 
 int b200tfhe_bsk_device_buffer(const b200tfhe_bsk *bsk, void **d_ptr, size_t *bytes) {
     if (!bsk || !d_ptr || !bytes) return 1;
@@ -348,10 +395,10 @@ static int ks_dev_locked(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const v
 static int br_dev_locked(b200tfhe_context *ctx, const b200tfhe_bsk *bsk, const void *d_in, void *d_out, const void *d_luts,
                          const uint32_t *d_idx, uint32_t batch, int mode) {
     const Params &p = bsk->p;
-    int R = br_supported(p);
+    int R = bsk_radix(p, bsk->grouping);
     BRLaunch a{d_in, small_len(p), d_luts, d_idx, bsk->d_fourier, d_out, mode == BR_MODE_GLWE ? glwe_len(p) : big_len(p),
                p.n, (int)batch, mode, tw_fwd(ctx, R), tw_inv(ctx, R)};
-    int rc = br_launch(p, a, ctx->stream);
+    int rc = bsk->grouping ? br_mb_launch(p, bsk->grouping, a, ctx->stream) : br_launch(p, a, ctx->stream);
     ctx->launches++;
     if (rc) return fail(ctx, "blind_rotate launch failed: " + std::to_string(rc));
     return 0;

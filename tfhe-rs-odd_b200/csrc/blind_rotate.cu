@@ -229,17 +229,21 @@ int br_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
     return br_big_launch(p, a, st);
 }
 
+int bsk_convert_polys_launch(int R, int bits, size_t npoly, const void *std_bsk, void *out, const void *tw_fwd, cudaStream_t st) {
+    int grid = 148 * 4;
+    if (R == 32 && bits == 64) bsk_convert_kernel<uint64_t, 32><<<grid, 64, 0, st>>>((const uint64_t *)std_bsk, (cplx *)out, npoly, (const cplx *)tw_fwd);
+    else if (R == 16 && bits == 64) bsk_convert_kernel<uint64_t, 16><<<grid, 128, 0, st>>>((const uint64_t *)std_bsk, (cplx *)out, npoly, (const cplx *)tw_fwd);
+    else if (R == 32 && bits == 32) bsk_convert_kernel<uint32_t, 32><<<grid, 64, 0, st>>>((const uint32_t *)std_bsk, (cplx *)out, npoly, (const cplx *)tw_fwd);
+    else if (R == 16 && bits == 32) bsk_convert_kernel<uint32_t, 16><<<grid, 128, 0, st>>>((const uint32_t *)std_bsk, (cplx *)out, npoly, (const cplx *)tw_fwd);
+    else return -1;
+    return (int)cudaGetLastError();
+}
+
 int bsk_convert_launch(const Params &p, const void *std_bsk, void *out, const void *tw_fwd, cudaStream_t st) {
     size_t npoly = (size_t)p.n * p.pbs_level * (p.k + 1) * (p.k + 1);
     int R = br_supported(p);
     if (R == 256) return bsk_convert_big_launch(p, std_bsk, out, tw_fwd, st);
-    int grid = 148 * 4;
-    if (R == 32 && p.bits == 64) bsk_convert_kernel<uint64_t, 32><<<grid, 64, 0, st>>>((const uint64_t *)std_bsk, (cplx *)out, npoly, (const cplx *)tw_fwd);
-    else if (R == 16 && p.bits == 64) bsk_convert_kernel<uint64_t, 16><<<grid, 128, 0, st>>>((const uint64_t *)std_bsk, (cplx *)out, npoly, (const cplx *)tw_fwd);
-    else if (R == 32 && p.bits == 32) bsk_convert_kernel<uint32_t, 32><<<grid, 64, 0, st>>>((const uint32_t *)std_bsk, (cplx *)out, npoly, (const cplx *)tw_fwd);
-    else if (R == 16 && p.bits == 32) bsk_convert_kernel<uint32_t, 16><<<grid, 128, 0, st>>>((const uint32_t *)std_bsk, (cplx *)out, npoly, (const cplx *)tw_fwd);
-    else return -1;
-    return (int)cudaGetLastError();
+    return bsk_convert_polys_launch(R, p.bits, npoly, std_bsk, out, tw_fwd, st);
 }
 
 }  // namespace b200tfhe

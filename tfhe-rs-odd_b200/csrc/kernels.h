@@ -63,6 +63,12 @@ int br_ws_launch(const Params &p, const BRLaunch &a, cudaStream_t st);
 int br_lat_supported(const Params &p);
 int br_lat_launch(const Params &p, const BRLaunch &a, cudaStream_t st);
 
+// blind_rotate_mb.cu (multi-bit bootstrap keys: 2^G GGSWs per group of G mask elements, n/G iterations)
+int br_mb_supported(const Params &p, int grouping);   // returns team radix R or 0
+int br_mb_launch(const Params &p, int grouping, const BRLaunch &a, cudaStream_t st);
+// key conversion of `npoly` standard-domain polynomials with an explicit team radix (blind_rotate.cu)
+int bsk_convert_polys_launch(int R, int bits, size_t npoly, const void *std_bsk, void *out, const void *tw_fwd, cudaStream_t st);
+
 // keyswitch.cu
 struct KSLaunch {
     const void *in;   size_t in_stride;    // [batch][in_stride], n_in+1 used
