@@ -76,6 +76,8 @@ struct KSLaunch {
     const void *ksk;                       // device copy of the reference layout [n_in][l_ks][n_out+1]
     const void *colsum;                    // [n_out+1]  2^(b-1) * sum of all key rows (digit offset correction)
     int n_in, n_out, level, base_log, bits, batch;
+    int body_col = -1;                     // output column that receives the input body; -1: the last one (n_out).  The packing
+                                           // keyswitch (LWE -> GLWE) puts it on coefficient 0 of the body polynomial (k*N)
 };
 int ks_launch(const KSLaunch &a, cudaStream_t st);
 int ks_colsum_launch(const void *ksk, void *colsum, int n_in, int n_out, int level, int base_log, int bits, cudaStream_t st);

@@ -25,7 +25,7 @@ template <typename T>
 __global__ void __launch_bounds__(KS_THREADS)
 ks_kernel(const T *__restrict__ in, size_t in_stride, T *__restrict__ out, size_t out_stride,
           const T *__restrict__ ksk, const T *__restrict__ colsum, int n_in, int n_out, int level, int base_log,
-          int batch) {
+          int batch, int body_col) {
     // digits of the current chunk: dig[(ii*level + t)][b] as bytes, 4 ciphertexts packed per 32-bit word
     extern __shared__ __align__(16) unsigned char dig[];
     const int tid = threadIdx.x;
@@ -85,7 +85,7 @@ ks_kernel(const T *__restrict__ in, size_t in_stride, T *__restrict__ out, size_
             const int j = j0 + y;
             if (j >= width) continue;
             T v = (T)half_b * colsum[j] - acc[x][y];
-            if (j == n_out) v += in[(size_t)gb * in_stride + n_in];
+            if (j == body_col) v += in[(size_t)gb * in_stride + n_in];
             out[(size_t)gb * out_stride + j] = v;
         }
     }
@@ -118,11 +118,11 @@ int ks_launch(const KSLaunch &a, cudaStream_t st) {
     if (a.bits == 64)
         ks_kernel<uint64_t><<<grid, KS_THREADS, smem, st>>>((const uint64_t *)a.in, a.in_stride, (uint64_t *)a.out, a.out_stride,
                                                             (const uint64_t *)a.ksk, (const uint64_t *)a.colsum, a.n_in, a.n_out,
-                                                            a.level, a.base_log, a.batch);
+                                                            a.level, a.base_log, a.batch, a.body_col < 0 ? a.n_out : a.body_col);
     else
         ks_kernel<uint32_t><<<grid, KS_THREADS, smem, st>>>((const uint32_t *)a.in, a.in_stride, (uint32_t *)a.out, a.out_stride,
                                                             (const uint32_t *)a.ksk, (const uint32_t *)a.colsum, a.n_in, a.n_out,
-                                                            a.level, a.base_log, a.batch);
+                                                            a.level, a.base_log, a.batch, a.body_col < 0 ? a.n_out : a.body_col);
     return (int)cudaGetLastError();
 }
 

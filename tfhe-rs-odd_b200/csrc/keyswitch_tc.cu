@@ -88,7 +88,7 @@ constexpr uint32_t TC_IDESC = (2u << 4) | (1u << 7) | (0u << 10) | ((uint32_t)(T
 template <typename T>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 ks_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const T *__restrict__ in,
-             size_t in_stride, T *__restrict__ out, size_t out_stride, int n_in, int n_out, int k_blocks, int batch) {
+             size_t in_stride, T *__restrict__ out, size_t out_stride, int n_in, int n_out, int k_blocks, int batch, int body_col) {
 #if defined(__CUDA_ARCH__)
     constexpr int PL = sizeof(T);                 // byte planes per key word
     constexpr int COEF = TC_BN / PL;              // output coefficients per tile
@@ -167,7 +167,7 @@ ks_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
                         T sum = 0;
 #pragma unroll
                         for (int p = 0; p < PL; p++) sum += (T)(typename TorusTraits<T>::Signed)(int32_t)v[e * PL + p] << (8 * p);
-                        T base = (j == n_out) ? in[(size_t)row * in_stride + n_in] : (T)0;
+                        T base = (j == body_col) ? in[(size_t)row * in_stride + n_in] : (T)0;
                         out[(size_t)row * out_stride + j] = base - sum;
                     }
                 }
@@ -282,12 +282,12 @@ int ks_tc_launch(const KSLaunch &a, const KSTensorKey &tk, void *digits, cudaStr
         if ((e = ensure_dynamic_smem((const void *)ks_tc_kernel<uint64_t>, TC_SMEM)) != cudaSuccess) return (int)e;
         ks_digits_kernel<uint64_t><<<dgrid, 256, 0, st>>>((const uint64_t *)a.in, a.in_stride, (int8_t *)digits, kp, a.n_in, a.level, a.base_log, a.batch);
         ks_tc_kernel<uint64_t><<<grid, TC_THREADS, TC_SMEM, st>>>(map_a, map_b, (const uint64_t *)a.in, a.in_stride, (uint64_t *)a.out,
-                                                                 a.out_stride, a.n_in, a.n_out, k_blocks, a.batch);
+                                                                 a.out_stride, a.n_in, a.n_out, k_blocks, a.batch, a.body_col < 0 ? a.n_out : a.body_col);
     } else {
         if ((e = ensure_dynamic_smem((const void *)ks_tc_kernel<uint32_t>, TC_SMEM)) != cudaSuccess) return (int)e;
         ks_digits_kernel<uint32_t><<<dgrid, 256, 0, st>>>((const uint32_t *)a.in, a.in_stride, (int8_t *)digits, kp, a.n_in, a.level, a.base_log, a.batch);
         ks_tc_kernel<uint32_t><<<grid, TC_THREADS, TC_SMEM, st>>>(map_a, map_b, (const uint32_t *)a.in, a.in_stride, (uint32_t *)a.out,
-                                                                 a.out_stride, a.n_in, a.n_out, k_blocks, a.batch);
+                                                                 a.out_stride, a.n_in, a.n_out, k_blocks, a.batch, a.body_col < 0 ? a.n_out : a.body_col);
     }
     return (int)cudaGetLastError();
 }
