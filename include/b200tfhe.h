@@ -177,6 +177,32 @@ int b200tfhe_ks_pbs_batch_dev(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, co
 int b200tfhe_pbs_ks_batch_dev(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, const void *d_in,
                               void *d_out, const void *d_luts, const uint32_t *d_lut_idx, uint32_t batch);
 
+/* ---- gadget extras of the fork (tfhe/src/gadget/engine/bootstrapping.rs), 64-bit torus ---------------------
+ * LwePackingKeyswitchKey (core_crypto/entities/lwe_packing_keyswitch_key.rs; generation
+ * algorithms/lwe_packing_keyswitch_key_generation.rs:60-150): [kN][l_ks (level l_ks first)][(k+1)N], input key = the big LWE
+ * key, output key = the GLWE key, decomposition = p->ks_* (as the gadget server key builds it, bootstrapping.rs:355-363). */
+typedef struct b200tfhe_pksk b200tfhe_pksk;
+int b200tfhe_pksk_upload_u64(b200tfhe_context *ctx, const b200tfhe_params *p, const uint64_t *pksk, b200tfhe_pksk **out);
+int b200tfhe_pksk_destroy(b200tfhe_pksk *pksk);
+/* keyswitch_lwe_ciphertext_into_glwe_ciphertext (algorithms/lwe_packing_keyswitch.rs:100-187) over a list:
+ * in: batch x (kN+1), out: batch x (k+1)N.  Bit-exact.  Runs on the tensor-core keyswitch (same integer GEMM). */
+int b200tfhe_packing_keyswitch_batch_u64(b200tfhe_context *ctx, const b200tfhe_pksk *pksk, const uint64_t *in, uint64_t *out_glwe,
+                                         uint32_t batch);
+/* out[b][i] = extract_lwe_sample_from_glwe_ciphertext( glwe[b] * polys[i], 0 ): the post-processing of mvb_bootstrap
+ * (bootstrapping.rs:596-611: polynomial_karatsuba_wrapping_mul by the plaintext polynomial v_i, then sample extraction).
+ * glwe: batch x (k+1)N, polys: n_polys x N, out: batch x n_polys x (kN+1).  Bit-exact. */
+int b200tfhe_glwe_mul_plain_extract_batch_u64(b200tfhe_context *ctx, const b200tfhe_params *p, const uint64_t *glwe, const uint64_t *polys,
+                                              uint32_t n_polys, uint64_t *out, uint32_t batch);
+/* mvb_bootstrap (bootstrapping.rs:567-622) over a list: [keyswitch when ksk != NULL (Big key choice: in is batch x (kN+1),
+ * else batch x (n+1))] -> blind rotation of the common-factor accumulator (bootstrap_common_factor :451-500) ->
+ * n_polys polynomial products + sample extractions.  out: batch x n_polys x (kN+1). */
+int b200tfhe_mvb_batch_u64(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, const uint64_t *in,
+                           const uint64_t *common_acc, const uint64_t *polys, uint32_t n_polys, uint64_t *out, uint32_t batch);
+/* pack_into_new_accumulator (bootstrapping.rs:690-773) over a list of accumulators: lwes: batch x count x (kN+1) with
+ * 1 <= count <= p_mod (missing ones are zero ciphertexts), p_mod odd; out_glwe: batch x (k+1)N.  Bit-exact. */
+int b200tfhe_pack_into_accumulator_batch_u64(b200tfhe_context *ctx, const b200tfhe_pksk *pksk, const uint64_t *lwes, uint32_t count,
+                                             uint32_t p_mod, uint64_t *out_glwe, uint32_t batch);
+
 /* ---- device-resident waves over a ciphertext pool ---------------------------------------------
  * The reference evaluates a shortint / integer / Trivium circuit as rayon-parallel layers of
  *   leveled prologue (unchecked_add, unchecked_scalar_mul: core_crypto/algorithms/lwe_linear_algebra.rs:191-215,556-572;

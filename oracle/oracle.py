@@ -238,3 +238,31 @@ class Oracle:
         for i in range(a.shape[0]):
             lib().orc_boolean_gate_prologue(gate, self.n + 1, _p(a[i]), _p(b[i]), _p(out[i]))
         return out
+
+    # ---- gadget extras (gadget/engine/bootstrapping.rs) ----------------------------------------------
+    def gen_pksk(self):
+        """LwePackingKeyswitchKey big LWE key -> GLWE key with the keyswitch decomposition: [kN][l_ks][(k+1)N]."""
+        pksk = np.zeros(self.big * self.l_ks * self.glwe_len, np.uint64)
+        lib().orc_gen_pksk(C.byref(self.p), _p(self.glwe_key), _p(self.glwe_key), C.c_uint64(self.seed + 4), _p(pksk), self.nthreads)
+        return pksk
+
+    def packing_keyswitch(self, pksk, cts):
+        cts = u64(cts).reshape(-1, self.big + 1)
+        out = np.zeros((cts.shape[0], self.glwe_len), np.uint64)
+        for i in range(cts.shape[0]):
+            lib().orc_packing_keyswitch(C.byref(self.p), _p(pksk), _p(cts[i]), _p(out[i]))
+        return out
+
+    def glwe_mul_plain_extract(self, glwes, polys):
+        glwes, polys = u64(glwes).reshape(-1, self.glwe_len), u64(polys).reshape(-1, self.N)
+        out = np.zeros((glwes.shape[0], polys.shape[0], self.big + 1), np.uint64)
+        for b in range(glwes.shape[0]):
+            for i in range(polys.shape[0]):
+                lib().orc_glwe_mul_plain_extract(C.byref(self.p), _p(glwes[b]), _p(polys[i]), _p(out[b, i]))
+        return out
+
+    def pack_into_accumulator(self, pksk, lwes, pmod):
+        lwes = u64(lwes).reshape(-1, self.big + 1)
+        out = np.zeros(self.glwe_len, np.uint64)
+        lib().orc_pack_into_accumulator(C.byref(self.p), _p(pksk), _p(lwes), lwes.shape[0], int(pmod), _p(out))
+        return out

@@ -147,3 +147,27 @@ void orc_gen_multibit_bsk(const orc_params *p, int grouping, const uint64_t *sma
     bsk_ctx c = { p, small_key, glwe_key, seed, bsk, grouping };
     orc_parallel_for(mb_bsk_one, &c, p->n / grouping, nthreads);
 }
+
+/* algorithms/lwe_packing_keyswitch_key_generation.rs:60-150.  Block i holds l_ks GLWE ciphertexts (level l_ks first) of the
+ * constant polynomial  s_in[i] * 2^{bits - b*level}  under the GLWE key: [kN][l_ks][(k+1)N].  Noise: glwe_std, as the gadget
+ * server key passes it (gadget/engine/bootstrapping.rs:355-363). */
+typedef struct { const orc_params *p; const uint64_t *big, *glwe_key; uint64_t seed; uint64_t *pksk; } pksk_ctx;
+static void pksk_one(void *c, int i) {
+    pksk_ctx *x = (pksk_ctx *)c; const orc_params *p = x->p;
+    int N = p->N, k = p->k, L = p->ks_level; size_t glwe = (size_t)(k + 1) * N;
+    rng_t r; rng_seed(&r, x->seed, 0x4000000ULL + (uint64_t)i);
+    uint64_t *scratch = (uint64_t *)malloc(sizeof(uint64_t) * N);
+    for (int t = 0; t < L; t++) {
+        int level = L - t;
+        uint64_t *g = x->pksk + ((size_t)i * L + t) * glwe;
+        uint64_t *body = g + (size_t)k * N;
+        memset(body, 0, sizeof(uint64_t) * N);
+        body[0] = (x->big[i] << (p->bits - p->ks_base_log * level)) & maskw(p->bits);
+        glwe_encrypt_assign(p, x->glwe_key, g, &r, scratch);
+    }
+    free(scratch);
+}
+void orc_gen_pksk(const orc_params *p, const uint64_t *big_key, const uint64_t *glwe_key, uint64_t seed, uint64_t *pksk, int nthreads) {
+    pksk_ctx c = { p, big_key, glwe_key, seed, pksk };
+    orc_parallel_for(pksk_one, &c, p->k * p->N, nthreads);
+}

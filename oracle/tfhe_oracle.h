@@ -89,6 +89,14 @@ void orc_multibit_pbs(const orc_params *p, int grouping, const double *mb_fbsk, 
 void orc_multibit_batch(const orc_params *p, int grouping, int mode, const uint64_t *ksk, const double *mb_fbsk, const uint64_t *in,
                         const uint64_t *luts, const uint32_t *lut_idx, uint64_t *out, int batch, int nthreads);
 
+/* ---- gadget extras of the fork (gadget/engine/bootstrapping.rs) ---- */
+/* algorithms/lwe_packing_keyswitch.rs:100-187 ; pksk [kN][l_ks][(k+1)N] */
+void orc_packing_keyswitch(const orc_params *p, const uint64_t *pksk, const uint64_t *in, uint64_t *out_glwe);
+/* mvb_bootstrap post-processing :596-611 : sample_extract_0(glwe * poly) */
+void orc_glwe_mul_plain_extract(const orc_params *p, const uint64_t *glwe, const uint64_t *poly, uint64_t *lwe_out);
+/* pack_into_new_accumulator :690-773 */
+void orc_pack_into_accumulator(const orc_params *p, const uint64_t *pksk, const uint64_t *lwes, int count, int pmod, uint64_t *out_glwe);
+
 /* ---- LUTs and gate glue ---- */
 /* shortint/engine/mod.rs:72-128 ; f_table has p = msg_mod*carry_mod entries */
 void orc_fill_accumulator(const orc_params *p, const uint64_t *f_table, int pmod, uint64_t *glwe_out);
@@ -106,6 +114,8 @@ void orc_gen_bsk(const orc_params *p, const uint64_t *small_key, const uint64_t 
 /* lwe_multi_bit_bootstrap_key_generation.rs:87-172: [n/G][2^G][l][k+1][k+1][N] */
 void orc_gen_multibit_bsk(const orc_params *p, int grouping, const uint64_t *small_key, const uint64_t *glwe_key, uint64_t seed,
                           uint64_t *bsk, int nthreads);
+/* lwe_packing_keyswitch_key_generation.rs:60-150 */
+void orc_gen_pksk(const orc_params *p, const uint64_t *big_key, const uint64_t *glwe_key, uint64_t seed, uint64_t *pksk, int nthreads);
 /* exact negacyclic product of a torus poly by a binary poly (limb-split FFT), used by GLWE encryption */
 void orc_negacyclic_mul_binary(int N, const uint64_t *a, const uint64_t *s_binary, uint64_t *out, int bits);
 

@@ -60,6 +60,12 @@ _PROTOS = {
     "b200tfhe_pool_read": [_VP, _VP, _U32, _U32, _VP],
     "b200tfhe_pool_device_buffer": [_VP, _PP, C.POINTER(_SZ)],
     "b200tfhe_pool_set_luts": [_VP, _VP, _VP, _U32],
+    "b200tfhe_pksk_upload_u64": [_VP, C.POINTER(Params), _VP, _PP],
+    "b200tfhe_pksk_destroy": [_VP],
+    "b200tfhe_packing_keyswitch_batch_u64": [_VP, _VP, _VP, _VP, _U32],
+    "b200tfhe_glwe_mul_plain_extract_batch_u64": [_VP, C.POINTER(Params), _VP, _VP, _U32, _VP, _U32],
+    "b200tfhe_mvb_batch_u64": [_VP, _VP, _VP, _VP, _VP, _VP, _U32, _VP, _U32],
+    "b200tfhe_pack_into_accumulator_batch_u64": [_VP, _VP, _VP, _U32, _U32, _VP, _U32],
     "b200tfhe_wave_run": [_VP, _VP, _VP, _VP, _VP, _U32, _U32],
 }
 for _s in ("u64", "u32"):

@@ -69,6 +69,12 @@ struct b200tfhe_ksk {
     size_t bytes;
     bool finalized;
     KSTensorKey tk;      // byte-plane copy of the key for the tensor-core path (d_planes == nullptr: not available)
+    int body_col = -1;   // output column receiving the input body (-1: the last one); k*N for a packing keyswitch key
+};
+// LwePackingKeyswitchKey: the same integer GEMM with (k+1)N output columns and the body on coefficient 0 of the body polynomial
+struct b200tfhe_pksk {
+    b200tfhe_ksk *inner;
+    Params p;
 };
 
 static int fail(b200tfhe_context *ctx, const std::string &msg) {
@@ -378,6 +384,7 @@ static int ks_dev_locked(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const v
     REQUIRE(ksk->finalized, "keyswitch: key not finalized (call b200tfhe_ksk_finalize after filling the device buffer)");
     const Params &p = ksk->p;
     KSLaunch a{d_in, big_len(p), d_out, small_len(p), ksk->d_ksk, ksk->d_colsum, p.k * p.N, p.n, p.ks_level, p.ks_base_log, p.bits, (int)batch};
+    a.body_col = ksk->body_col;
     static const int tc_min = getenv("B200TFHE_KS_TC_MIN") ? atoi(getenv("B200TFHE_KS_TC_MIN")) : 1;
     int rc;
     if (ksk->tk.d_planes && (int)batch >= tc_min) {
@@ -690,6 +697,139 @@ int b200tfhe_sample_extract_batch_u64(b200tfhe_context *ctx, const uint64_t *g, 
 int b200tfhe_sample_extract_batch_u32(b200tfhe_context *ctx, const uint32_t *g, uint32_t *l, uint32_t k, uint32_t N, uint32_t b) { return sample_extract_host(ctx, g, l, k, N, b, 32); }
 
 
+
+// ---- gadget extras: packing keyswitch, multi-value bootstrap, accumulator packing -------------------
+int b200tfhe_pksk_upload_u64(b200tfhe_context *ctx, const b200tfhe_params *pp, const uint64_t *pksk, b200tfhe_pksk **out) {
+    REQUIRE(ctx && pp && out && pksk, "pksk_upload: null argument");
+    *out = nullptr;
+    REQUIRE(pp->torus_bits == 64, "pksk_upload: 64-bit torus only");
+    REQUIRE(pp->glwe_dimension > 0 && is_pow2(pp->polynomial_size), "invalid dimensions");
+    b200tfhe_params q = *pp;
+    q.lwe_dimension = (pp->glwe_dimension + 1) * pp->polynomial_size - 1;    // output "LWE" = the flat GLWE
+    b200tfhe_ksk *inner = nullptr;
+    if (b200tfhe_ksk_upload_u64(ctx, &q, pksk, &inner)) return 1;
+    inner->body_col = pp->glwe_dimension * pp->polynomial_size;
+    *out = new b200tfhe_pksk{inner, to_params(pp)};
+    return 0;
+}
+int b200tfhe_pksk_destroy(b200tfhe_pksk *k) {
+    if (!k) return 0;
+    b200tfhe_ksk_destroy(k->inner);
+    delete k;
+    return 0;
+}
+
+int b200tfhe_packing_keyswitch_batch_u64(b200tfhe_context *ctx, const b200tfhe_pksk *pksk, const uint64_t *in, uint64_t *out_glwe, uint32_t batch) {
+    REQUIRE(ctx && pksk, "packing_keyswitch: null argument");
+    REQUIRE(pksk->inner->ctx == ctx, "key handle belongs to another context");
+    if (batch == 0) return 0;
+    REQUIRE(in && out_glwe, "packing_keyswitch: null buffer");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    const Params &p = pksk->p;
+    const size_t in_b = (size_t)batch * big_len(p) * 8, out_b = (size_t)batch * glwe_len(p) * 8;
+    void *d_in, *d_out;
+    CK(ctx->ws.get(Workspace::IN, in_b, &d_in));
+    CK(ctx->ws.get(Workspace::OUT, out_b, &d_out));
+    CK(cudaMemcpyAsync(d_in, in, in_b, cudaMemcpyHostToDevice, ctx->stream));
+    if (ks_dev_locked(ctx, pksk->inner, d_in, d_out, batch)) return 1;
+    CK(cudaMemcpyAsync(out_glwe, d_out, out_b, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int b200tfhe_glwe_mul_plain_extract_batch_u64(b200tfhe_context *ctx, const b200tfhe_params *pp, const uint64_t *glwe, const uint64_t *polys,
+                                              uint32_t n_polys, uint64_t *out, uint32_t batch) {
+    REQUIRE(ctx && pp, "glwe_mul_plain_extract: null argument");
+    if (batch == 0 || n_polys == 0) return 0;
+    REQUIRE(glwe && polys && out, "glwe_mul_plain_extract: null buffer");
+    REQUIRE(pp->glwe_dimension > 0 && is_pow2(pp->polynomial_size) && pp->polynomial_size <= 8192, "invalid dimensions");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    Params p = to_params(pp);
+    const size_t in_b = (size_t)batch * glwe_len(p) * 8, pl_b = (size_t)n_polys * p.N * 8, out_b = (size_t)batch * n_polys * big_len(p) * 8;
+    void *d_in, *d_pl, *d_out;
+    CK(ctx->ws.get(Workspace::IN, in_b, &d_in));
+    CK(ctx->ws.get(Workspace::A, pl_b, &d_pl));
+    CK(ctx->ws.get(Workspace::OUT, out_b, &d_out));
+    CK(cudaMemcpyAsync(d_in, glwe, in_b, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d_pl, polys, pl_b, cudaMemcpyHostToDevice, ctx->stream));
+    int rc = glwe_mul_plain_extract_launch(d_in, d_pl, d_out, p.k, p.N, (int)n_polys, (int)batch, 64, ctx->stream);
+    ctx->launches++;
+    if (rc) return fail(ctx, "glwe_mul_plain_extract launch failed: " + std::to_string(rc));
+    CK(cudaMemcpyAsync(out, d_out, out_b, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int b200tfhe_mvb_batch_u64(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, const uint64_t *in,
+                           const uint64_t *common_acc, const uint64_t *polys, uint32_t n_polys, uint64_t *out, uint32_t batch) {
+    REQUIRE(ctx && bsk, "mvb: null argument");
+    REQUIRE(bsk->ctx == ctx, "key handle belongs to another context");
+    REQUIRE(bsk->p.bits == 64, "mvb: 64-bit torus only");
+    if (ksk && check_pair(ctx, ksk, bsk)) return 1;
+    if (batch == 0 || n_polys == 0) return 0;
+    REQUIRE(in && common_acc && polys && out, "mvb: null buffer");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    const Params &p = bsk->p;
+    const size_t in_len = ksk ? big_len(p) : small_len(p);
+    const size_t in_b = (size_t)batch * in_len * 8, pl_b = (size_t)n_polys * p.N * 8, out_b = (size_t)batch * n_polys * big_len(p) * 8;
+    void *d_in, *d_lut, *d_glwe, *d_pl, *d_out, *d_small = nullptr;
+    CK(ctx->ws.get(Workspace::IN, in_b, &d_in));
+    CK(ctx->ws.get(Workspace::LUTS, glwe_len(p) * 8, &d_lut));
+    CK(ctx->ws.get(Workspace::MID, (size_t)batch * glwe_len(p) * 8, &d_glwe));
+    CK(ctx->ws.get(Workspace::A, pl_b, &d_pl));
+    CK(ctx->ws.get(Workspace::OUT, out_b, &d_out));
+    CK(cudaMemcpyAsync(d_in, in, in_b, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d_lut, common_acc, glwe_len(p) * 8, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d_pl, polys, pl_b, cudaMemcpyHostToDevice, ctx->stream));
+    if (ksk) {   // EncryptionKeyChoice::Big: keyswitch first (gadget/engine/bootstrapping.rs:828-885)
+        CK(ctx->ws.get(Workspace::B, (size_t)batch * small_len(p) * 8, &d_small));
+        if (ks_dev_locked(ctx, ksk, d_in, d_small, batch)) return 1;
+    }
+    // bootstrap_common_factor :451-500 = blind rotation without sample extraction (entry a14)
+    if (br_dev_locked(ctx, bsk, ksk ? d_small : d_in, d_glwe, d_lut, nullptr, batch, BR_MODE_GLWE)) return 1;
+    int rc = glwe_mul_plain_extract_launch(d_glwe, d_pl, d_out, p.k, p.N, (int)n_polys, (int)batch, 64, ctx->stream);
+    ctx->launches++;
+    if (rc) return fail(ctx, "glwe_mul_plain_extract launch failed: " + std::to_string(rc));
+    CK(cudaMemcpyAsync(out, d_out, out_b, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int b200tfhe_pack_into_accumulator_batch_u64(b200tfhe_context *ctx, const b200tfhe_pksk *pksk, const uint64_t *lwes, uint32_t count,
+                                             uint32_t p_mod, uint64_t *out_glwe, uint32_t batch) {
+    REQUIRE(ctx && pksk, "pack_into_accumulator: null argument");
+    REQUIRE(pksk->inner->ctx == ctx, "key handle belongs to another context");
+    const Params &p = pksk->p;
+    // the reference asserts an odd output modulus (bootstrapping.rs:719); every slot must be at least two coefficients wide
+    REQUIRE(p_mod % 2 == 1 && p_mod >= 1 && (uint32_t)p.N / p_mod >= 2, "pack_into_accumulator: p must be odd with N / p >= 2");
+    REQUIRE(count >= 1 && count <= p_mod, "pack_into_accumulator: between 1 and p ciphertexts per accumulator");
+    if (batch == 0) return 0;
+    REQUIRE(lwes && out_glwe, "pack_into_accumulator: null buffer");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    const size_t len = big_len(p);
+    const size_t in_b = (size_t)batch * count * len * 8, el_b = (size_t)batch * p_mod * len * 8;
+    const size_t g_b = (size_t)batch * p_mod * glwe_len(p) * 8, out_b = (size_t)batch * glwe_len(p) * 8;
+    void *d_in, *d_el, *d_g, *d_out;
+    CK(ctx->ws.get(Workspace::IN, in_b, &d_in));
+    CK(ctx->ws.get(Workspace::A, el_b, &d_el));
+    CK(ctx->ws.get(Workspace::MID, g_b, &d_g));
+    CK(ctx->ws.get(Workspace::OUT, out_b, &d_out));
+    CK(cudaMemcpyAsync(d_in, lwes, in_b, cudaMemcpyHostToDevice, ctx->stream));
+    int rc = pack_elements_launch(d_in, d_el, (int)count, (int)p_mod, len, (int)batch, 64, ctx->stream);
+    ctx->launches++;
+    if (rc) return fail(ctx, "pack_elements launch failed: " + std::to_string(rc));
+    if (ks_dev_locked(ctx, pksk->inner, d_el, d_g, batch * p_mod)) return 1;
+    rc = pack_rotate_sum_launch(d_g, d_out, (int)p_mod, p.k, p.N, (int)batch, 64, ctx->stream);
+    ctx->launches++;
+    if (rc) return fail(ctx, "pack_rotate_sum launch failed: " + std::to_string(rc));
+    CK(cudaMemcpyAsync(out_glwe, d_out, out_b, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
 
 // ---- device-resident waves over a ciphertext pool -------------------------------------------------------------------
 static_assert(sizeof(b200tfhe_wave_op) == sizeof(WaveOp) && sizeof(WaveOp) == 72, "wave op layout");

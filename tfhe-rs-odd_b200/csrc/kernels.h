@@ -109,6 +109,12 @@ int wave_gather_launch(const void *pool, size_t len, const WaveOp *d_ops, int n_
 int wave_scatter_launch(void *pool, size_t len, const WaveOp *d_ops, int n_ops, int n_pbs, const void *pbs_out, const void *staging,
                         int bits, cudaStream_t st);
 
+// gadget_kernels.cu (multi-value bootstrap post-processing, accumulator packing: gadget/engine/bootstrapping.rs)
+int glwe_mul_plain_extract_launch(const void *glwe, const void *polys, void *out, int k, int N, int n_polys, int batch, int bits,
+                                  cudaStream_t st);
+int pack_elements_launch(const void *in, void *out, int count, int p, size_t len, int batch, int bits, cudaStream_t st);
+int pack_rotate_sum_launch(const void *G, void *out, int p, int k, int N, int batch, int bits, cudaStream_t st);
+
 // misc_kernels.cu
 int modswitch_launch(const void *in, uint32_t *out, size_t count, int log2N, int bits, cudaStream_t st);
 int sample_extract_launch(const void *glwe, void *lwe, int k, int N, int batch, int bits, cudaStream_t st);
