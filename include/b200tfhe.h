@@ -99,6 +99,12 @@ int b200tfhe_multibit_bsk_upload_u64(b200tfhe_context *ctx, const b200tfhe_param
 int b200tfhe_multibit_bsk_convert_dev(b200tfhe_context *ctx, const b200tfhe_params *p, uint32_t grouping_factor,
                                       const void *d_std_bsk, b200tfhe_bsk **out);
 int b200tfhe_multibit_bsk_alloc(b200tfhe_context *ctx, const b200tfhe_params *p, uint32_t grouping_factor, b200tfhe_bsk **out);
+/* Upload a bootstrap key that is already in the Fourier domain, in the reference's serialised order
+ * (FourierPolynomialList, fft_impl/fft64/math/fft/mod.rs:588-717: [ggsw][level][row][col] polynomials, each N/2 complex f64
+ * in natural frequency order, re/im interleaved; values as forward_as_torus produces them).  grouping_factor 1 = classic
+ * FourierLweBootstrapKey, >= 2 = FourierLweMultiBitBootstrapKey.  What deserialising a shortint ServerKey needs. */
+int b200tfhe_bsk_upload_fourier(b200tfhe_context *ctx, const b200tfhe_params *p, uint32_t grouping_factor, const double *fourier,
+                                b200tfhe_bsk **out);
 /* 1 for a classic key, G for a multi-bit key */
 uint32_t b200tfhe_bsk_grouping_factor(const b200tfhe_bsk *bsk);
 /* 1 if the multi-bit blind rotation is built for this parameter set and grouping factor, else 0 */

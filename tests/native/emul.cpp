@@ -358,3 +358,29 @@ extern "C" int emul_multibit_blind_rotate(int n, int k, int N, int base_log, int
 #undef CASE
     return 1;
 }
+
+// ---- device Fourier layout of one key polynomial (what bsk_convert writes): used to pin "position index == frequency index"
+// against numpy's FFT, which is what lets a Fourier-domain key in natural order be uploaded without conversion --------------
+extern "C" int emul_key_forward(int N, int bits, const uint64_t *poly, double *out) {
+    if (N == 8192) {
+        typedef BigCore<uint64_t, 1, 2, 15> C;
+        constexpr int TH = 256, P = C::P;
+        static BigTables tb; fill_big_tables(tb);
+        std::vector<cplx> S1(C::M);
+        static cplx x[TH][P];
+        for (int t = 0; t < TH; t++) C::key_input(t, poly, x[t]);
+        for (int t = 0; t < TH; t++) C::fwdA(t, x[t], S1.data(), &tb);
+        for (int t = 0; t < TH; t++) C::fwdB_load(t, x[t], S1.data());
+        for (int t = 0; t < TH; t++) C::fwdB_pass1(t, x[t], S1.data(), &tb);
+        for (int t = 0; t < TH; t++) C::fwdB_pass2(t, x[t], S1.data());
+        for (int t = 0; t < TH; t++) for (int p = 0; p < P; p++) { out[2 * (p * TH + t)] = x[t][p].re; out[2 * (p * TH + t) + 1] = x[t][p].im; }
+        return 0;
+    }
+    std::vector<cplx> f;
+    if (N == 2048 && bits == 64) convert_bsk<uint64_t, 32, 1, 1, 23>(poly, 1, f);
+    else if (N == 512 && bits == 64) convert_bsk<uint64_t, 16, 3, 1, 18>(poly, 1, f);
+    else if (N == 512 && bits == 32) convert_bsk<uint32_t, 16, 2, 3, 6>(poly, 1, f);
+    else return 1;
+    for (int i = 0; i < N / 2; i++) { out[2 * i] = f[i].re; out[2 * i + 1] = f[i].im; }   // first polynomial of the "key"
+    return 0;
+}

@@ -37,6 +37,7 @@ _PROTOS = {
     "b200tfhe_multibit_bsk_convert_dev": [_VP, C.POINTER(Params), _U32, _VP, _PP],
     "b200tfhe_multibit_bsk_alloc": [_VP, C.POINTER(Params), _U32, _PP],
     "b200tfhe_bsk_grouping_factor": [_VP],
+    "b200tfhe_bsk_upload_fourier": [_VP, C.POINTER(Params), _U32, _VP, _PP],
     "b200tfhe_multibit_params_supported": [C.POINTER(Params), _U32],
     "b200tfhe_bsk_device_buffer": [_VP, _PP, C.POINTER(_SZ)],
     "b200tfhe_bsk_destroy": [_VP],

@@ -106,6 +106,20 @@ class FourierLweBootstrapKey:
             ctx.check(ctx._lib.b200tfhe_bsk_alloc(ctx._h, C.byref(params), C.byref(h)))
         return cls(ctx, params, h)
 
+    @classmethod
+    def from_fourier(cls, ctx, params, fourier, grouping_factor=1):
+        """Key already in the Fourier domain, the reference's serialised order: [ggsw][l][k+1][k+1][N/2] complex f64 in natural
+        frequency order (what bincode-deserialising a FourierLweBootstrapKey yields)."""
+        f = np.ascontiguousarray(fourier, dtype=np.float64).reshape(-1)
+        G = int(grouping_factor)
+        ggsw = params.lwe_dimension if G <= 1 else (params.lwe_dimension // G << G)
+        expect = ggsw * params.pbs_level * (params.glwe_dimension + 1) ** 2 * params.polynomial_size
+        if f.size != expect:
+            raise B200TfheError(f"Fourier bootstrap key has {f.size} f64 values, parameters imply {expect}")
+        h = C.c_void_p()
+        ctx.check(ctx._lib.b200tfhe_bsk_upload_fourier(ctx._h, C.byref(params), G, _ptr(f), C.byref(h)))
+        return cls(ctx, params, h)
+
     def close(self):
         if getattr(self, "_h", None):
             self.ctx._lib.b200tfhe_bsk_destroy(self._h)

@@ -298,6 +298,33 @@ int b200tfhe_multibit_params_supported(const b200tfhe_params *p, uint32_t groupi
     if (!p || grouping < 2 || grouping > 4) return 0;
     return br_mb_supported(to_params(p), (int)grouping) != 0;
 }
+// Fourier-domain key in the reference's serialised (natural frequency) order: [ggsw][level][row][col][N/2] c64, values as
+// forward_as_torus produces them (fft/mod.rs:197-218).  For the team FFTs (N <= 2048) the device layout IS that order
+// (position index == frequency index); the N = 8192 kernel keeps frequency t_hi + 16 t_lo + 256 p at position 256 p + t.
+int b200tfhe_bsk_upload_fourier(b200tfhe_context *ctx, const b200tfhe_params *pp, uint32_t grouping, const double *fourier, b200tfhe_bsk **out) {
+    REQUIRE(ctx && pp && out && fourier, "bsk_upload_fourier: null argument");
+    *out = nullptr;
+    REQUIRE(grouping >= 1 && grouping <= 4, "bsk_upload_fourier: grouping factor must be 1 (classic) .. 4");
+    if (bsk_alloc(ctx, pp, grouping > 1 ? (int)grouping : 0, out)) return 1;
+    b200tfhe_bsk *k = *out;
+    const int R = bsk_radix(k->p, k->grouping);
+    const void *src = fourier;
+    std::vector<double> tmp;
+    if (R == 256) {
+        const size_t M = (size_t)k->p.N / 2, npoly = k->bytes / (M * sizeof(cplx));
+        tmp.resize(npoly * M * 2);
+        for (size_t q = 0; q < npoly; q++)
+            for (size_t pos = 0; pos < M; pos++) {
+                const size_t t = pos % 256, p = pos / 256, f = t / 16 + 16 * (t % 16) + 256 * p;
+                tmp[2 * (q * M + pos)] = fourier[2 * (q * M + f)];
+                tmp[2 * (q * M + pos) + 1] = fourier[2 * (q * M + f) + 1];
+            }
+        src = tmp.data();
+    }
+    cudaError_t e = cudaMemcpy(k->d_fourier, src, k->bytes, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) { b200tfhe_bsk_destroy(k); *out = nullptr; return fail_cuda(ctx, "cudaMemcpy(fourier bsk)", e); }
+    return 0;
+}
 uint32_t b200tfhe_bsk_grouping_factor(const b200tfhe_bsk *bsk) { return bsk && bsk->grouping ? (uint32_t)bsk->grouping : 1u; }
 
 int b200tfhe_bsk_device_buffer(const b200tfhe_bsk *bsk, void **d_ptr, size_t *bytes) {

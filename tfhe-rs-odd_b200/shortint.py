@@ -47,7 +47,8 @@ class CiphertextList:
 
 
 class ServerKey:
-    """shortint::ServerKey{key_switching_key, bootstrapping_key (Classic), message_modulus, carry_modulus, pbs_order}."""
+    """shortint::ServerKey{key_switching_key, bootstrapping_key (Classic or MultiBit: the device key handle carries the
+    grouping factor), message_modulus, carry_modulus, pbs_order}."""
 
     def __init__(self, ksk, bsk, message_modulus, carry_modulus, pbs_order="ks_pbs"):
         if bsk.params.torus_bits != 64:
@@ -55,6 +56,24 @@ class ServerKey:
         self.key_switching_key, self.bootstrapping_key = ksk, bsk
         self.message_modulus, self.carry_modulus, self.pbs_order = message_modulus, carry_modulus, pbs_order
         self.params = bsk.params
+
+    @classmethod
+    def from_bincode(cls, ctx, data):
+        """Load `bincode::serialize(&shortint::ServerKey)` bytes (serialization.py; server_key/mod.rs:283-297): the keyswitch key
+        goes to the device as is, the Fourier bootstrap key (Classic or MultiBit) is uploaded in its serialised order."""
+        from . import serialization as ser
+        d = ser.deserialize_shortint_server_key(data)
+        k, b = d["key_switching_key"], d["bootstrapping_key"]
+        glwe_dim, N = b["glwe_size"] - 1, b["polynomial_size"]
+        if k["input_lwe_dimension"] != glwe_dim * N or k["output_lwe_size"] != b["input_lwe_dimension"] + 1:
+            raise B200TfheError("server key: keyswitch key and bootstrap key dimensions differ")
+        params = cc.make_params(b["input_lwe_dimension"], glwe_dim, N, b["decomp_base_log"], b["decomp_level_count"],
+                                k["decomp_base_log"], k["decomp_level_count"], 64)
+        ksk = cc.LweKeyswitchKey.upload(ctx, params, k["data"])
+        bsk = cc.FourierLweBootstrapKey.from_fourier(ctx, params, b["fourier"], b["grouping_factor"])
+        sk = cls(ksk, bsk, d["message_modulus"], d["carry_modulus"], d["pbs_order"])
+        sk.max_degree, sk.max_noise_level = d["max_degree"], d["max_noise_level"]
+        return sk
 
     # ---- LUT generation: engine/mod.rs:72-128 -----------------------------------------------------------
     def generate_lookup_table(self, f):
