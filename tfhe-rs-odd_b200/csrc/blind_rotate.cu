@@ -106,8 +106,8 @@ blind_rotate_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const T *__
         const cplx *ggsw_i = bsk + (size_t)i * C::GGSW_CPLX;
         cplx F[R];
         C::template mac_prefetch_part<0>(lane, r, ggsw_i, F);
-#pragma unroll
-        for (int t = 0; t < L; t++) {
+#pragma unroll 1
+        for (int t = 0; t < L; t++) {   // rolled: one copy of the second pass in the instruction stream
             cplx x[R];
             C::fwd_pass2_load(lane, x, fbuf_r + t * REGION);
             __syncwarp();

@@ -89,7 +89,7 @@ blind_rotate_mb_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const T 
         if constexpr (CTS > 1) __syncthreads();   // keep the CTA's ciphertexts on the same key group (L1 reuse, I-cache)
         C::digits_plain_fwd_pass1(lane, acc_r, fbuf_r, twf);
         __syncwarp();
-#pragma unroll
+#pragma unroll 1
         for (int t = 0; t < L; t++) {
             cplx x[R];
             C::fwd_pass2_load(lane, x, fbuf_r + t * REGION);

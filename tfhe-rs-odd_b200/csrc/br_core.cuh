@@ -49,13 +49,35 @@ template <typename T, int R, int K, int L, int BASE_LOG> struct BRCore {
     // acc*X^a - acc at this lane's R folded points, run forward pass 1 for each level and leave the
     // transposed partial results in fbuf_r[t] (t = 0 is level L, the first one the recurrence emits).
     HD static void digits_fwd_pass1(int lane, const T *acc_r, int a, cplx *fbuf_r, const cplx (*twf)[R]) {
-        int32_t dre[L][R], dim[L][R];
-        digits(lane, acc_r, a, dre, dim);
-        static_for<0, L>([&](auto t) {
+        if constexpr (L == 1) {
+            int32_t dre[L][R], dim[L][R];
+            digits(lane, acc_r, a, dre, dim);
             cplx x[R];
-            digits_to_cplx<decltype(t)::value>(dre, dim, x);
-            FFT::fwd_pass1(lane, x, fbuf_r + decltype(t)::value * REGION, twf);
-        });
+            digits_to_cplx<0>(dre, dim, x);
+            FFT::fwd_pass1(lane, x, fbuf_r, twf);
+        } else {
+            // several levels: the decomposition states of this lane's 2R coefficients stay in registers and ONE rolled loop
+            // emits a level's digits and transforms them, so the instruction stream holds a single copy of the radix-R FFT
+            // (the unrolled form missed the instruction cache: profiles/r01_ncu_other_kernels.json, boolean: no_instruction 1.5/issue)
+            T s0[R], s1[R];
+            static_for<0, R>([&](auto p) {
+                constexpr int m = brev(decltype(p)::value, FFT::LOGR);
+                const int c = lane + R * m;
+                s0[decltype(p)::value] = decomp_init_state<T>(rot_read<T, N>(acc_r, c, a) - acc_r[c], BASE_LOG, L);
+                s1[decltype(p)::value] = decomp_init_state<T>(rot_read<T, N>(acc_r, c + M, a) - acc_r[c + M], BASE_LOG, L);
+            });
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
+            for (int t = 0; t < L; t++) {
+                cplx x[R];
+                static_for<0, R>([&](auto p) {
+                    x[decltype(p)::value] = cplx{int_to_double((int32_t)decomp_next_digit<T>(s0[decltype(p)::value], BASE_LOG)),
+                                                 int_to_double((int32_t)decomp_next_digit<T>(s1[decltype(p)::value], BASE_LOG))};
+                });
+                FFT::fwd_pass1(lane, x, fbuf_r + t * REGION, twf);
+            }
+        }
     }
     HD static void digits(int lane, const T *acc_r, int a, int32_t (&dre)[L][R], int32_t (&dim)[L][R]) {
         digits_range<0, R>(lane, acc_r, a, dre, dim);
