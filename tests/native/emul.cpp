@@ -140,7 +140,7 @@ static int run_big(const uint64_t *bsk_std, int n, const uint64_t *lwe, int batc
     std::vector<cplx> fbsk(npoly * M);
     std::vector<T> poly(N);
     auto forward = [&]() {
-        for (int t = 0; t < TH; t++) C::fwdA(t, x[t], S1.data(), &tb);
+        for (int t = 0; t < TH; t++) C::fwdA(t, x[t], S1.data(), tb.ta, tb.tq);
         for (int t = 0; t < TH; t++) C::fwdB_load(t, x[t], S1.data());
         for (int t = 0; t < TH; t++) C::fwdB_pass1(t, x[t], S1.data(), &tb);
         for (int t = 0; t < TH; t++) C::fwdB_pass2(t, x[t], S1.data());
@@ -180,7 +180,7 @@ static int run_big(const uint64_t *bsk_std, int n, const uint64_t *lwe, int batc
                 for (int t = 0; t < TH; t++) C::invA(t, x[t], S1.data(), &tb);
                 for (int t = 0; t < TH; t++) C::invB_load(t, x[t], S1.data());
                 for (int t = 0; t < TH; t++) C::invB_store(t, x[t], S1.data());
-                for (int t = 0; t < TH; t++) { C::invC(t, x[t], S1.data(), &tb); C::accumulate(t, x[t], &acc[(size_t)j * N]); }
+                for (int t = 0; t < TH; t++) { C::invC(t, x[t], S1.data(), tb.ta, tb.tq); C::accumulate(t, x[t], &acc[(size_t)j * N]); }
             }
         }
         for (size_t c = 0; c < acc.size(); c++) out[(size_t)b * K1 * N + c] = (uint64_t)acc[c];
@@ -369,7 +369,7 @@ extern "C" int emul_key_forward(int N, int bits, const uint64_t *poly, double *o
         std::vector<cplx> S1(C::M);
         static cplx x[TH][P];
         for (int t = 0; t < TH; t++) C::key_input(t, poly, x[t]);
-        for (int t = 0; t < TH; t++) C::fwdA(t, x[t], S1.data(), &tb);
+        for (int t = 0; t < TH; t++) C::fwdA(t, x[t], S1.data(), tb.ta, tb.tq);
         for (int t = 0; t < TH; t++) C::fwdB_load(t, x[t], S1.data());
         for (int t = 0; t < TH; t++) C::fwdB_pass1(t, x[t], S1.data(), &tb);
         for (int t = 0; t < TH; t++) C::fwdB_pass2(t, x[t], S1.data());

@@ -15,8 +15,12 @@
 namespace b200tfhe {
 
 struct BigTables {
-    cplx t1f[16][256];  // u_t * w_4096^{t k1}       u_t = e^{i pi t/N}, w_4096 = e^{-2 pi i/4096}
-    cplx t1i[16][256];  // conj(t1f) / M
+    // middle twiddle of the 16 x 256 split, u_t * w_4096^{t k1} (u_t = e^{i pi t/N}, w_4096 = e^{-2 pi i/4096}), factored as
+    // ta[k1 & 3][t] * tq[k1 >> 2][t] so that both factors (32 KB) live in shared memory: the full 2 x 64 KB tables were read
+    // from L2 on every transform (96 of 224 global loads per thread and iteration, profiles/r01_ncu_other_kernels.json).
+    // The inverse uses the conjugate; its 1/M is folded into the digit conversion (an exact power of two).
+    cplx ta[4][256];    // u_t * w_4096^{t b}
+    cplx tq[4][256];    // w_4096^{4 t a}
     cplx pf[8][16];     // plain 256-point team DFT: [b<4][lane] = w_256^{lane b}, [4+a][lane] = w_256^{lane 4a}
     cplx pi[8][16];     // conjugates
 };
@@ -42,7 +46,23 @@ template <typename T, int K, int L, int BASE_LOG> struct BigCore {
                 g0 = (int32_t)decomp_next_digit<T>(s0, BASE_LOG);
                 g1 = (int32_t)decomp_next_digit<T>(s1, BASE_LOG);
             });
-            x[decltype(p)::value] = cplx{int_to_double(g0), int_to_double(g1)};
+            x[decltype(p)::value] = cplx{int_to_double_scaled<12>(g0), int_to_double_scaled<12>(g1)};   // digits / M
+        });
+    }
+    // same with the level index at run time (rolled level loop of the kernel: one copy of the forward transform)
+    HD static void digits_rt(int tid, const T *acc_r, int a, int tl, cplx (&x)[P]) {
+        static_for<0, P>([&](auto p) {
+            constexpr int m = brev(decltype(p)::value, LOGP);
+            const int c = tid + TH * m;
+            T d0 = rot_read<T, N>(acc_r, c, a) - acc_r[c];
+            T d1 = rot_read<T, N>(acc_r, c + M, a) - acc_r[c + M];
+            T s0 = decomp_init_state<T>(d0, BASE_LOG, L), s1 = decomp_init_state<T>(d1, BASE_LOG, L);
+            int32_t g0 = 0, g1 = 0;
+            static_for<0, L>([&](auto e) {    // every level's digit is a few integer instructions: compute all, select one
+                const int32_t e0 = (int32_t)decomp_next_digit<T>(s0, BASE_LOG), e1 = (int32_t)decomp_next_digit<T>(s1, BASE_LOG);
+                if (tl == decltype(e)::value) { g0 = e0; g1 = e1; }
+            });
+            x[decltype(p)::value] = cplx{int_to_double_scaled<12>(g0), int_to_double_scaled<12>(g1)};   // digits / M
         });
     }
     HD static void key_input(int tid, const T *poly, cplx (&x)[P]) {
@@ -54,14 +74,19 @@ template <typename T, int K, int L, int BASE_LOG> struct BigCore {
     }
 
     // ---- forward: fwdA | CTA sync | fwdB_load | team sync | fwdB_pass1 | team sync | fwdB_pass2 | (CTA sync before next fwdA)
-    HD static void fwdA(int tid, cplx (&x)[P], cplx *S1, const BigTables *tb) {
+    // ta / tq: the two factor tables ([4][256] each), in shared memory for the blind rotation
+    template <int K1_> HD static cplx mid_tw(int tid, const cplx (*ta)[TH], const cplx (*tq)[TH]) {
+        if constexpr ((K1_ >> 2) == 0) return ta[K1_ & 3][tid];
+        else return cmul(ta[K1_ & 3][tid], tq[K1_ >> 2][tid]);
+    }
+    HD static void fwdA(int tid, cplx (&x)[P], cplx *S1, const cplx (*ta)[TH], const cplx (*tq)[TH]) {
         static_for<0, P>([&](auto p) {
             constexpr int m = brev(decltype(p)::value, LOGP);
             x[decltype(p)::value] = cmul_root<m * TWQ>(x[decltype(p)::value]);
         });
         fft_dit<P, -1>(x);
         static_for<0, P>([&](auto k1) {
-            S1[decltype(k1)::value * TH + tid] = cmul(x[decltype(k1)::value], tb->t1f[decltype(k1)::value][tid]);
+            S1[decltype(k1)::value * TH + tid] = cmul(x[decltype(k1)::value], mid_tw<decltype(k1)::value>(tid, ta, tq));
         });
     }
     HD static void fwdB_load(int tid, cplx (&x)[P], const cplx *S1) {
@@ -114,6 +139,18 @@ template <typename T, int K, int L, int BASE_LOG> struct BigCore {
         });
     }
 
+    // f[p] += g[p] * x[p] for one output polynomial (same operation order as mac)
+    HD static void mac_one_poly(const cplx (&g)[P], const cplx (&x)[P], cplx (&f)[P]) {
+        static_for<0, P>([&](auto p) {
+            const cplx a = g[decltype(p)::value], d = x[decltype(p)::value];
+            cplx &o = f[decltype(p)::value];
+            o.re = fma_(a.re, d.re, o.re);
+            o.re = fma_(-a.im, d.im, o.re);
+            o.im = fma_(a.re, d.im, o.im);
+            o.im = fma_(a.im, d.re, o.im);
+        });
+    }
+
     // ---- inverse: (x[pp] = F[brev(pp)]) invA | team sync | invB_load | team sync | invB_store | CTA sync | invC
     HD static void invA(int tid, cplx (&x)[P], cplx *S1, const BigTables *tb) {
         const int team = tid >> 4, lane = tid & 15;
@@ -130,11 +167,12 @@ template <typename T, int K, int L, int BASE_LOG> struct BigCore {
         fft_dit<P, +1>(x);
         static_for<0, P>([&](auto m2) { S1[team * TH + lane + 16 * decltype(m2)::value] = x[decltype(m2)::value]; });
     }
-    // result: x[m].re -> coefficient tid + 256 m, x[m].im -> that + M, already scaled by 1/M and un-twisted
-    HD static void invC(int tid, cplx (&x)[P], const cplx *S1, const BigTables *tb) {
+    // result: x[m].re -> coefficient tid + 256 m, x[m].im -> that + M, un-twisted (the 1/M was applied to the digits)
+    HD static void invC(int tid, cplx (&x)[P], const cplx *S1, const cplx (*ta)[TH], const cplx (*tq)[TH]) {
         static_for<0, P>([&](auto pp) {
             constexpr int k1 = brev(decltype(pp)::value, LOGP);
-            x[decltype(pp)::value] = cmul(S1[k1 * TH + tid], tb->t1i[k1][tid]);
+            const cplx w = mid_tw<k1>(tid, ta, tq);
+            x[decltype(pp)::value] = cmul(S1[k1 * TH + tid], cplx{w.re, -w.im});
         });
         fft_dit<P, +1>(x);
         static_for<0, P>([&](auto m) { x[decltype(m)::value] = cmul_root<-decltype(m)::value * TWQ>(x[decltype(m)::value]); });

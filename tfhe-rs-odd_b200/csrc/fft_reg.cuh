@@ -228,6 +228,15 @@ HD double int_to_double(int32_t d) {
 #endif
 }
 
+// same, divided by 2^SHIFT (exact): lets a kernel fold the 1/M of the inverse transform into the digit conversion
+template <int SHIFT> HD double int_to_double_scaled(int32_t d) {
+#if defined(__CUDA_ARCH__)
+    return __hiloint2double(0x43300000 - (SHIFT << 20), (int)((uint32_t)d ^ 0x80000000u)) - 4503601774854144.0 / (double)(1 << SHIFT);
+#else
+    return (double)d / (double)(1 << SHIFT);
+#endif
+}
+
 // from_torus (commons/math/torus/mod.rs:72-78) followed by the signed wrapping cast (fft/mod.rs:285-304)
 template <typename T> HD T torus_from_double(double t) {
     const double MAGIC = 6755399441055744.0;  // 1.5 * 2^52 : round to nearest integer for |t| < 2^51

@@ -32,11 +32,11 @@ template <int R> void fill_tw_tables(TwTables<R> &t) {
 
 inline void fill_big_tables(BigTables &t) {
     const int N = 8192, M = 4096;
-    for (int k1 = 0; k1 < 16; k1++)
+    (void)M;
+    for (int b = 0; b < 4; b++)
         for (int th = 0; th < 256; th++) {
-            cplx z = root_2N((long long)th * (1 - 4 * k1), N);      // u_t * w_4096^{t k1}
-            t.t1f[k1][th] = z;
-            t.t1i[k1][th] = cplx{z.re / M, -z.im / M};
+            t.ta[b][th] = root_2N((long long)th * (1 - 4 * b), N);   // u_t * w_4096^{t b}
+            t.tq[b][th] = root_2N(-16LL * th * b, N);                // w_4096^{4 t b}
         }
     for (int lane = 0; lane < 16; lane++) {
         for (int b = 0; b < 4; b++) {
