@@ -343,3 +343,35 @@ def test_other_2_2_kernels_on_small_batches(env):
                         "(test_pbs_decrypts_like_oracle or test_ks_pbs_like_oracle) and (TOY_2_2 or MESSAGE_2_CARRY_2)"],
                        env=dict(os.environ, **env), capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_pbs_output_error_variance_matches_oracle_and_theory(ctx):
+    """BASELINE north_star asks for "a measured error variance" of the blind-rotation output.  At the real
+    PARAM_MESSAGE_2_CARRY_2 set: the error of the bootstrapped phase against the noiseless expectation delta * f(m) is measured
+    over 1536 ciphertexts on the GPU and over 192 on the oracle; both must be centred, agree with each other (two samples of the
+    same distribution) and sit between half and twice the analytic law  n/2 (1 + kN/2) 2^(-2bl) / 12 + n l (k+1) N (B^2+2)/12
+    sigma_glwe^2  (decomposition rounding + key noise; binary key of Hamming weight ~ n/2).  The figures are printed
+    (pytest -s) and recorded in profiles/ by tools/measure_noise.py."""
+    import tfhe_rs_odd_b200 as t
+    o = get_oracle("MESSAGE_2_CARRY_2")
+    p, bsk, ksk = _keys(ctx, o)
+    rng = np.random.default_rng(21)
+    B, B_ref = 1536, 192
+    msgs = rng.integers(0, o.pmod, B)
+    f = lambda x: (5 * x + 3) % o.pmod
+    lut = o.lut(f)
+    cts = o.encrypt(o.encode(msgs), "small")
+    got = t.programmable_bootstrap_lwe_ciphertext(cts, lut, bsk)
+    ref = o.pbs(cts[:B_ref], lut)
+    want = o.encode(np.array([f(int(m)) for m in msgs]))
+    err_gpu = _sdiff(o.phase(got), want, 64).astype(np.float64) / 2.0 ** 64
+    err_ref = _sdiff(o.phase(ref), want[:B_ref], 64).astype(np.float64) / 2.0 ** 64
+    B2 = 2.0 ** (2 * o.b)
+    theory = o.n / 2 * (1 + o.k * o.N / 2) / (12 * B2 ** o.l) + o.n * o.l * (o.k + 1) * o.N * (B2 + 2) / 12 * o.p.glwe_std ** 2
+    v_gpu, v_ref = err_gpu.var(), err_ref.var()
+    print(f"\nPBS output error at 2_2: GPU var 2^{np.log2(v_gpu):.2f} (n={B}), oracle var 2^{np.log2(v_ref):.2f} (n={B_ref}), "
+          f"analytic 2^{np.log2(theory):.2f}; max |err| GPU 2^{np.log2(np.abs(err_gpu).max()):.2f}")
+    assert abs(err_gpu.mean()) < 5 * (v_gpu / B) ** 0.5 and abs(err_ref.mean()) < 5 * (v_ref / B_ref) ** 0.5
+    assert 0.6 < v_gpu / v_ref < 1.6          # F-ratio of two samples of one distribution (192 vs 1536 draws: sd ~ 11 %)
+    assert 0.5 < v_gpu / theory < 2.0
+    assert np.abs(err_gpu).max() < 2.0 ** -7   # half the decoding step 2^-5 / 2 with margin: every output decodes
