@@ -43,10 +43,13 @@ PARAMS = {
     "GOLD_U64": (4, 1, 512, 12, 2, 4, 4, 64, 1e-9, 1e-15, 4, "ks_pbs"),
     "GOLD_U32": (4, 2, 512, 6, 3, 3, 4, 32, 1e-7, 1e-8, 0, "pbs_ks"),
     "GOLD_2_2": (4, 1, 2048, 23, 1, 3, 5, 64, 1e-9, 0.00000000000000029403601535432533, 16, "ks_pbs"),
+    "GOLD_MB": (4, 1, 512, 12, 2, 4, 4, 64, 1e-9, 1e-15, 4, "ks_pbs"),        # multi-bit, grouping factor 2
+    "GOLD_PK": (4, 1, 64, 12, 2, 4, 2, 64, 1e-9, 1e-15, 4, "ks_pbs"),          # packing keyswitch / gadget integer ops (tiny N)
 }
 
 # LweBskGroupingFactor of the multi-bit sets (absent = classic bootstrap key)
-GROUPING = {"MULTI_BIT_2_2_GROUP_2": 2, "MULTI_BIT_2_2_GROUP_3": 3, "TOY_MB_G2": 2, "TOY_MB_G3": 3, "TOY_MB22_G2": 2, "TOY_MB22_G3": 3}
+GROUPING = {"MULTI_BIT_2_2_GROUP_2": 2, "MULTI_BIT_2_2_GROUP_3": 3, "TOY_MB_G2": 2, "TOY_MB_G3": 3, "TOY_MB22_G2": 2, "TOY_MB22_G3": 3,
+            "GOLD_MB": 2}
 
 
 def build(force=False):

@@ -101,3 +101,78 @@ def test_cuda_path_matches_golden_boolean(ctx, z):
     assert np.array_equal(bits, z[f"{name}.nand_bits"])
     ref_ph = o.phase(z[f"{name}.nand_out"].astype(np.uint64), "small")
     assert _phase_close(o, o.phase(out.astype(np.uint64), "small"), ref_ph, 32)
+
+
+# ---- multi-bit PBS and the gadget engine's integer operations (tests/golden/next_rows_golden.npz) -----------
+GOLD_NEXT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "next_rows_golden.npz")
+
+
+@pytest.fixture(scope="module")
+def zn():
+    return np.load(GOLD_NEXT)
+
+
+def _oracle_pk(zn):
+    from oracle.oracle import Oracle
+    o = Oracle("GOLD_PK")
+    o.glwe_key = zn["GOLD_PK.glwe_key"].astype(np.uint64)
+    return o
+
+
+def test_oracle_reproduces_golden_multibit(zn):
+    name = "GOLD_MB"
+    o = _oracle(zn, name)
+    assert o.grouping == 2 and o.bsk.size == (o.n // 2 * 4) * o.l * (o.k + 1) ** 2 * o.N
+    out = o.ks_pbs(zn[f"{name}.cts"], zn[f"{name}.luts"], zn[f"{name}.lut_idx"])
+    ph = o.phase(out, "big")
+    assert np.array_equal(o.decode(ph) % o.pmod, zn[f"{name}.ks_pbs_msgs"])
+    assert _phase_close(o, ph, zn[f"{name}.ks_pbs_phase"], 64)
+    msgs, idx = zn[f"{name}.msgs"], zn[f"{name}.lut_idx"]
+    assert np.array_equal(zn[f"{name}.ks_pbs_msgs"], np.where(idx == 0, msgs, (3 * msgs + 1) % o.pmod))
+
+
+def test_oracle_reproduces_golden_gadget_integer_ops(zn):
+    o = _oracle_pk(zn)
+    pksk, lwes = zn["GOLD_PK.pksk"], zn["GOLD_PK.lwes"]
+    glwes = o.packing_keyswitch(pksk, lwes)
+    assert np.array_equal(glwes, zn["GOLD_PK.pks_out"])
+    assert np.array_equal(o.glwe_mul_plain_extract(glwes, zn["GOLD_PK.polys"]), zn["GOLD_PK.mul_extract_out"])
+    assert np.array_equal(o.pack_into_accumulator(pksk, lwes[2:4], 3), zn["GOLD_PK.packed_p3_count2"])
+    assert np.array_equal(o.pack_into_accumulator(pksk, lwes[:5], 5), zn["GOLD_PK.packed_p5_count5"])
+
+
+@pytest.mark.gpu
+def test_cuda_path_matches_golden_multibit(ctx, zn):
+    import tfhe_rs_odd_b200 as t
+    name = "GOLD_MB"
+    o = _oracle(zn, name)
+    p = params_of(o)
+    bsk = t.core_crypto.convert_standard_lwe_multi_bit_bootstrap_key_to_fourier(ctx, p, zn[f"{name}.bsk"], 2)
+    ksk = t.LweKeyswitchKey.upload(ctx, p, zn[f"{name}.ksk"])
+    out = t.keyswitch_programmable_bootstrap(ksk, bsk, zn[f"{name}.cts"], zn[f"{name}.luts"], lut_idx=zn[f"{name}.lut_idx"])
+    ph = o.phase(out, "big")
+    assert np.array_equal(o.decode(ph) % o.pmod, zn[f"{name}.ks_pbs_msgs"])
+    assert _phase_close(o, ph, zn[f"{name}.ks_pbs_phase"], 64)
+
+
+@pytest.mark.gpu
+def test_cuda_path_matches_golden_gadget_integer_ops(ctx, zn):
+    """Bit for bit against the stored vectors: packing keyswitch (tensor-core path, N = 64: ragged against every tile size),
+    GLWE x plaintext polynomial + extraction, pack_into_new_accumulator."""
+    import tfhe_rs_odd_b200 as t
+    from tfhe_rs_odd_b200 import gadget
+    o = _oracle_pk(zn)
+    p = params_of(o)
+    pksk = gadget.LwePackingKeyswitchKey.upload(ctx, p, zn["GOLD_PK.pksk"])
+    lwes = zn["GOLD_PK.lwes"]
+    glwes = gadget.keyswitch_lwe_ciphertext_into_glwe_ciphertext(pksk, lwes)
+    assert np.array_equal(glwes, zn["GOLD_PK.pks_out"])
+    assert np.array_equal(gadget.glwe_mul_plain_extract(ctx, p, zn["GOLD_PK.pks_out"], zn["GOLD_PK.polys"]), zn["GOLD_PK.mul_extract_out"])
+
+    class _Key:                     # Bootstrapper only needs params / ctx of the bootstrap key for the packing entry point
+        params, ctx = p, None
+    k = _Key()
+    k.ctx = ctx
+    bs = gadget.Bootstrapper(k, None, pksk)
+    assert np.array_equal(bs.pack_into_new_accumulator(lwes[2:4], 3), zn["GOLD_PK.packed_p3_count2"])
+    assert np.array_equal(bs.pack_into_new_accumulator(lwes[:5], 5), zn["GOLD_PK.packed_p5_count5"])
