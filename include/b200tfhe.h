@@ -209,6 +209,16 @@ int b200tfhe_mvb_batch_u64(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const
 int b200tfhe_pack_into_accumulator_batch_u64(b200tfhe_context *ctx, const b200tfhe_pksk *pksk, const uint64_t *lwes, uint32_t count,
                                              uint32_t p_mod, uint64_t *out_glwe, uint32_t batch);
 
+/* ---- bit extraction, the first half of the WoP-PBS -------------------------------------------
+ * Replaces extract_bits_from_lwe_ciphertext_mem_optimized (core_crypto/algorithms/lwe_wopbs.rs:321-364 ->
+ * fft64/crypto/wop_pbs/mod.rs:66-225) over a ciphertext list.  in: batch x (kN+1) under the big key; out: batch x nbits x (n+1)
+ * under the small key, the most significant extracted bit FIRST, every bit scaled by q/2.  Bits delta_log ..
+ * delta_log + nbits - 1 of the plaintext are extracted from the lowest upwards: nbits keyswitches and nbits - 1 bootstraps
+ * per ciphertext, all rounds device-resident.  delta_log + nbits <= 64 (the reference's debug_assert :86-94).  The first
+ * extracted ciphertext (index nbits - 1) is bit-identical to the reference's; the later ones depend on bootstraps. */
+int b200tfhe_extract_bits_batch_u64(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, const uint64_t *in,
+                                    uint32_t delta_log, uint32_t nbits, uint64_t *out, uint32_t batch);
+
 /* ---- device-resident waves over a ciphertext pool ---------------------------------------------
  * The reference evaluates a shortint / integer / Trivium circuit as rayon-parallel layers of
  *   leveled prologue (unchecked_add, unchecked_scalar_mul: core_crypto/algorithms/lwe_linear_algebra.rs:191-215,556-572;

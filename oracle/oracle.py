@@ -269,3 +269,13 @@ class Oracle:
         out = np.zeros(self.glwe_len, np.uint64)
         lib().orc_pack_into_accumulator(C.byref(self.p), _p(pksk), _p(lwes), lwes.shape[0], int(pmod), _p(out))
         return out
+
+    # ---- bit extraction (fft64/crypto/wop_pbs/mod.rs:66-225) -----------------------------------------
+    def extract_bits(self, cts, delta_log, nbits):
+        """[B][kN+1] under the big key -> [B][nbits][n+1] under the small key, most significant extracted bit first."""
+        assert not self.grouping, "the reference's extract_bits takes a classic Fourier bootstrap key"
+        cts = u64(cts).reshape(-1, self.big + 1)
+        out = np.zeros((cts.shape[0], int(nbits), self.n + 1), np.uint64)
+        for i in range(cts.shape[0]):
+            lib().orc_extract_bits(C.byref(self.p), _p(self.ksk), _p(self.fbsk), _p(cts[i]), int(delta_log), int(nbits), _p(out[i]))
+        return out

@@ -97,6 +97,10 @@ void orc_glwe_mul_plain_extract(const orc_params *p, const uint64_t *glwe, const
 /* pack_into_new_accumulator :690-773 */
 void orc_pack_into_accumulator(const orc_params *p, const uint64_t *pksk, const uint64_t *lwes, int count, int pmod, uint64_t *out_glwe);
 
+/* extract_bits, fft64/crypto/wop_pbs/mod.rs:66-225 ; out [nbits][n+1], most significant extracted bit first */
+void orc_extract_bits(const orc_params *p, const uint64_t *ksk, const double *fbsk, const uint64_t *in, int delta_log, int nbits,
+                      uint64_t *out);
+
 /* ---- LUTs and gate glue ---- */
 /* shortint/engine/mod.rs:72-128 ; f_table has p = msg_mod*carry_mod entries */
 void orc_fill_accumulator(const orc_params *p, const uint64_t *f_table, int pmod, uint64_t *glwe_out);

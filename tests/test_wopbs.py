@@ -1,0 +1,139 @@
+"""Bit extraction, the first half of the WoP-PBS (reference core_crypto/fft_impl/fft64/crypto/wop_pbs/mod.rs:66-225,
+test it mirrors: wop_pbs/tests.rs:101-268 -- 5 bits including padding, every bit extracted, each decrypted with a 1-bit decomposer).
+The reference's own toy set (N = 1024) has no team-FFT instance here (N = 2 R^2 only), so the test runs on the sets of the path."""
+import numpy as np
+import pytest
+
+from conftest import get_oracle, params_of, phase_bound
+
+U64 = 1 << 64
+
+
+def _bits_msb_first(msgs, nbits):
+    return np.array([[(int(m) >> (nbits - 1 - i)) & 1 for i in range(nbits)] for m in msgs])
+
+
+def _diff_bound(o, nbits):
+    """|phase_gpu - phase_oracle| of an extracted ciphertext after the first round: the running buffer holds the outputs of
+    earlier bootstraps (two f64 FFT orders -> independent rounding draws, conftest.phase_bound), shifted left by up to nbits - 1
+    bits, and the keyswitch of two different buffers draws its decomposition rounding (kN terms of 2^-(b_ks l_ks)) twice."""
+    ks_var = o.k * o.N * 2.0 ** (-2 * o.b_ks * o.l_ks) / 12.0
+    return phase_bound(o) * 2.0 ** nbits + 8.0 * (2.0 * ks_var) ** 0.5
+
+
+def _decrypt_bits(o, out):
+    """phase of every extracted ciphertext under the small key, rounded to one bit (SignedDecomposer(1, 1) of tests.rs:189)."""
+    B, nb, _ = out.shape
+    ph = o.phase(out.reshape(B * nb, o.n + 1), under="small").reshape(B, nb)
+    bits = ((ph.astype(np.uint64) + np.uint64(1 << 62)) >> np.uint64(63)).astype(int) & 1
+    return bits, ph
+
+
+# ---- CPU: the oracle restatement against the definition ------------------------------------------------------------
+@pytest.mark.parametrize("name,nbits", [("TOY_U64", 5), ("TOY_2_2", 4)])
+def test_oracle_extract_bits_decrypts_every_bit(name, nbits):
+    o = get_oracle(name)
+    delta_log = 64 - nbits
+    msgs = np.arange(1 << nbits, dtype=np.uint64)
+    cts = o.encrypt(msgs << np.uint64(delta_log), under="big", seed=41)
+    out = o.extract_bits(cts, delta_log, nbits)
+    bits, ph = _decrypt_bits(o, out)
+    assert np.array_equal(bits, _bits_msb_first(msgs, nbits))
+    err = (ph - (bits.astype(np.uint64) << np.uint64(63))).astype(np.int64) / 2.0 ** 64
+    assert np.abs(err).max() < 2.0 ** -6
+
+
+def test_oracle_extract_bits_partial_window_and_first_round():
+    """Fewer bits than the message holds: the window starts at delta_log; the first extracted ciphertext (last slot) is the
+    keyswitch of the shifted input (mod.rs:160-184) and a single-bit extraction does no bootstrap at all."""
+    o = get_oracle("TOY_U64")
+    msgs = np.array([0b10110, 0b01101, 0b11111, 0], dtype=np.uint64)
+    cts = o.encrypt(msgs << np.uint64(59), under="big", seed=43)
+    out = o.extract_bits(cts, 59, 2)                      # bits 59 and 60 = the two low bits of the message
+    bits, _ = _decrypt_bits(o, out)
+    assert np.array_equal(bits, np.stack([(msgs >> np.uint64(1)) & np.uint64(1), msgs & np.uint64(1)], 1).astype(int))
+    shifted = cts << np.uint64(64 - 59 - 1)
+    assert np.array_equal(out[:, 1], o.keyswitch(shifted))
+    assert np.array_equal(o.extract_bits(cts, 59, 1)[:, 0], o.keyswitch(shifted))
+
+
+# ---- GPU: through the C ABI ----------------------------------------------------------------------------------------------
+def _keys(ctx, o):
+    import tfhe_rs_odd_b200 as t
+    p = params_of(o)
+    if o.grouping:
+        bsk = t.core_crypto.convert_standard_lwe_multi_bit_bootstrap_key_to_fourier(ctx, p, o.bsk, o.grouping)
+    else:
+        bsk = t.convert_standard_lwe_bootstrap_key_to_fourier(ctx, p, o.bsk)
+    return t, bsk, t.LweKeyswitchKey.upload(ctx, p, o.ksk)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,nbits,B", [("TOY_U64", 5, 64), ("TOY_1_1", 3, 16), ("TOY_2_2", 4, 600), ("TOY_3_3", 6, 8)])
+def test_gpu_extract_bits_matches_oracle(ctx, name, nbits, B):
+    o = get_oracle(name)
+    t, bsk, ksk = _keys(ctx, o)
+    delta_log = 64 - nbits
+    msgs = (np.arange(B, dtype=np.uint64) * np.uint64(7) + np.uint64(3)) % np.uint64(1 << nbits)
+    cts = o.encrypt(msgs << np.uint64(delta_log), under="big", seed=47)
+    got = t.core_crypto.extract_bits_from_lwe_ciphertext_mem_optimized(cts, bsk, ksk, delta_log, nbits)
+    assert got.shape == (B, nbits, o.n + 1)
+    bits, ph = _decrypt_bits(o, got)
+    assert np.array_equal(bits, _bits_msb_first(msgs, nbits))                 # every bit of every message
+    nref = min(B, 24)
+    ref = o.extract_bits(cts[:nref], delta_log, nbits)
+    assert np.array_equal(got[:nref, nbits - 1], ref[:, nbits - 1])           # first round: integer only, memcmp-exact
+    _, ph_ref = _decrypt_bits(o, ref)
+    d = (ph[:nref] - ph_ref).astype(np.int64) / 2.0 ** 64                     # later rounds go through bootstraps (f64 FFT)
+    assert np.abs(d).max() < _diff_bound(o, nbits) < 0.125
+    # a single ciphertext, and fewer bits than the window: same slots
+    one = t.core_crypto.extract_bits_from_lwe_ciphertext_mem_optimized(cts[5], bsk, ksk, delta_log, nbits)
+    b1, _ = _decrypt_bits(o, one[None])
+    assert np.array_equal(b1[0], _bits_msb_first(msgs[5:6], nbits)[0])
+    two = t.core_crypto.extract_bits_from_lwe_ciphertext_mem_optimized(cts[:4], bsk, ksk, delta_log, 2)
+    assert np.array_equal(two[:, 1], got[:4, nbits - 1])                      # the lowest bit does not depend on the count
+    b2, _ = _decrypt_bits(o, two)
+    assert np.array_equal(b2, _bits_msb_first(msgs[:4] & np.uint64(3), 2))
+
+
+@pytest.mark.gpu
+def test_gpu_extract_bits_multibit_key_and_errors(ctx):
+    """The key handle carries the grouping factor: the same entry runs on a multi-bit bootstrap key.  Argument validation
+    mirrors the reference's assertions (mod.rs:86-118)."""
+    o = get_oracle("TOY_MB22_G2")
+    t, bsk, ksk = _keys(ctx, o)
+    msgs = np.arange(16, dtype=np.uint64)
+    cts = o.encrypt(msgs << np.uint64(60), under="big", seed=53)
+    got = t.core_crypto.extract_bits_from_lwe_ciphertext_mem_optimized(cts, bsk, ksk, 60, 4)
+    bits, _ = _decrypt_bits(o, got)
+    assert np.array_equal(bits, _bits_msb_first(msgs, 4))
+    with pytest.raises(t.B200TfheError, match="exceeds"):
+        t.core_crypto.extract_bits_from_lwe_ciphertext_mem_optimized(cts, bsk, ksk, 60, 5)
+    with pytest.raises(t.B200TfheError):
+        t.core_crypto.extract_bits_from_lwe_ciphertext_mem_optimized(cts[:, :-1], bsk, ksk, 60, 4)
+    assert t.core_crypto.extract_bits_from_lwe_ciphertext_mem_optimized(cts, bsk, ksk, 60, 0).shape == (16, 0, o.n + 1)
+    o2 = get_oracle("TOY_U64")
+    _, bsk2, _ = _keys(ctx, o2)
+    with pytest.raises(t.B200TfheError, match="length"):                       # host mirror: lwe_in size vs the bootstrap key (:107-112)
+        t.core_crypto.extract_bits_from_lwe_ciphertext_mem_optimized(cts, bsk2, ksk, 60, 4)
+    cts2 = o2.encrypt(np.zeros(2, np.uint64), under="big")
+    with pytest.raises(t.B200TfheError, match="dimensions differ"):            # C ABI: ksk output vs bsk input dimension (:113-118)
+        t.core_crypto.extract_bits_from_lwe_ciphertext_mem_optimized(cts2, bsk2, ksk, 60, 4)
+
+
+@pytest.mark.gpu
+def test_gpu_extract_bits_full_size_2_2(ctx):
+    """PARAM_MESSAGE_2_CARRY_2 keys at full size: all 5 bits (padding included) of 296 ciphertexts decrypt to the message bits;
+    the oracle runs the first 2 ciphertexts (4 bootstraps each)."""
+    o = get_oracle("MESSAGE_2_CARRY_2")
+    t, bsk, ksk = _keys(ctx, o)
+    B, nbits = 296, 5
+    msgs = (np.arange(B, dtype=np.uint64) * np.uint64(11)) % np.uint64(32)
+    cts = o.encrypt(msgs << np.uint64(59), under="big", seed=59)
+    got = t.core_crypto.extract_bits_from_lwe_ciphertext_mem_optimized(cts, bsk, ksk, 59, nbits)
+    bits, ph = _decrypt_bits(o, got)
+    assert np.array_equal(bits, _bits_msb_first(msgs, nbits))
+    ref = o.extract_bits(cts[:2], 59, nbits)
+    assert np.array_equal(got[:2, nbits - 1], ref[:, nbits - 1])
+    _, ph_ref = _decrypt_bits(o, ref)
+    assert np.abs((ph[:2] - ph_ref).astype(np.int64) / 2.0 ** 64).max() < _diff_bound(o, nbits) < 0.125

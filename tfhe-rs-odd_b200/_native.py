@@ -67,6 +67,7 @@ _PROTOS = {
     "b200tfhe_glwe_mul_plain_extract_batch_u64": [_VP, C.POINTER(Params), _VP, _VP, _U32, _VP, _U32],
     "b200tfhe_mvb_batch_u64": [_VP, _VP, _VP, _VP, _VP, _VP, _U32, _VP, _U32],
     "b200tfhe_pack_into_accumulator_batch_u64": [_VP, _VP, _VP, _U32, _U32, _VP, _U32],
+    "b200tfhe_extract_bits_batch_u64": [_VP, _VP, _VP, _VP, _U32, _U32, _VP, _U32],
     "b200tfhe_wave_run": [_VP, _VP, _VP, _VP, _VP, _U32, _U32],
 }
 for _s in ("u64", "u32"):

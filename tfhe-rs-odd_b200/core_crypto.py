@@ -360,3 +360,24 @@ def multi_bit_blind_rotate_assign(input_lwe, accumulator_glwe, multi_bit_bsk, th
     if multi_bit_bsk.grouping_factor < 2:
         raise B200TfheError("multi_bit_blind_rotate_assign needs a multi-bit bootstrap key")
     return blind_rotate_assign(input_lwe, accumulator_glwe, multi_bit_bsk)
+
+
+# ---- bit extraction (first half of the WoP-PBS) -------------------------------------------------------------------------
+def extract_bits_from_lwe_ciphertext_mem_optimized(lwe_in, fourier_bsk, ksk, delta_log, number_of_bits_to_extract, lwe_list_out=None):
+    """algorithms/lwe_wopbs.rs:321-364 -> fft64/crypto/wop_pbs/mod.rs:66-225 (argument order of the reference; fft and stack
+    have no counterpart).  lwe_in: [kN+1] or [B][kN+1] under the big key; result [number_of_bits][n+1] per ciphertext under the
+    small key, most significant extracted bit first, every bit scaled by q/2."""
+    p, ctx = fourier_bsk.params, fourier_bsk.ctx
+    if p.torus_bits != 64:
+        raise B200TfheError("extract_bits: 64-bit torus only")
+    a, single = _as_list(lwe_in, p.glwe_dimension * p.polynomial_size + 1, 64, "extract_bits input")
+    nb = int(number_of_bits_to_extract)
+    if nb < 0 or int(delta_log) < 0:
+        raise B200TfheError("extract_bits: negative delta_log / bit count")
+    out = np.zeros((a.shape[0], nb, p.lwe_dimension + 1), np.uint64)
+    ctx.check(ctx._lib.b200tfhe_extract_bits_batch_u64(ctx._h, ksk._h, fourier_bsk._h, _ptr(a), int(delta_log), nb, _ptr(out), a.shape[0]))
+    res = out[0] if single else out
+    if lwe_list_out is not None:
+        np.copyto(lwe_list_out, res)
+        return lwe_list_out
+    return res

@@ -858,6 +858,58 @@ int b200tfhe_pack_into_accumulator_batch_u64(b200tfhe_context *ctx, const b200tf
     return 0;
 }
 
+// extract_bits (fft64/crypto/wop_pbs/mod.rs:66-225) over a batch: nbits rounds of {shift, keyswitch, store, bootstrap with a
+// constant accumulator, subtract}, all device-resident; the ciphertexts of the batch advance through the rounds together.
+int b200tfhe_extract_bits_batch_u64(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, const uint64_t *in,
+                                    uint32_t delta_log, uint32_t nbits, uint64_t *out, uint32_t batch) {
+    REQUIRE(ctx, "extract_bits: null context");
+    if (check_pair(ctx, ksk, bsk)) return 1;
+    const Params &p = bsk->p;
+    REQUIRE(p.bits == 64, "extract_bits: 64-bit torus only");
+    // debug_assert of the reference (:86-94): the extracted window has to fit the scalar
+    REQUIRE((uint64_t)delta_log + nbits <= 64, "extract_bits: delta_log + number_of_bits_to_extract exceeds the 64 bits of the ciphertext");
+    // round bit_idx >= 1 uses alpha = 2^(delta_log + bit_idx - 1), round 0 with more than one bit 2^(delta_log - 1)   (:204)
+    REQUIRE(nbits <= 1 || delta_log >= 1, "extract_bits: delta_log must be at least 1 to extract more than one bit");
+    if (batch == 0 || nbits == 0) return 0;
+    REQUIRE(in && out, "extract_bits: null buffer");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    const size_t blen = big_len(p), slen = small_len(p), glen = glwe_len(p);
+    const size_t in_b = (size_t)batch * blen * 8, out_b = (size_t)batch * nbits * slen * 8;
+    void *d_buf, *d_shift, *d_ks, *d_pbs, *d_out, *d_lut;
+    CK(ctx->ws.get(Workspace::IN, in_b, &d_buf));
+    CK(ctx->ws.get(Workspace::A, in_b, &d_shift));
+    CK(ctx->ws.get(Workspace::B, (size_t)batch * slen * 8, &d_ks));
+    CK(ctx->ws.get(Workspace::MID, in_b, &d_pbs));
+    CK(ctx->ws.get(Workspace::OUT, out_b, &d_out));
+    CK(ctx->ws.get(Workspace::LUTS, (size_t)nbits * glen * 8, &d_lut));
+    CK(cudaMemcpyAsync(d_buf, in, in_b, cudaMemcpyHostToDevice, ctx->stream));
+    if (nbits > 1) {   // accumulator of round bit_idx: zero mask, body constant -2^(delta_log - 1 + bit_idx)   (:196-205)
+        std::vector<uint64_t> luts((size_t)(nbits - 1) * glen, 0);
+        for (uint32_t r = 0; r + 1 < nbits; r++)
+            for (int c = 0; c < p.N; c++) luts[(size_t)r * glen + (size_t)p.k * p.N + c] = 0 - (1ULL << (delta_log - 1 + r));
+        CK(cudaMemcpyAsync(d_lut, luts.data(), luts.size() * 8, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));   // luts is a local
+    }
+    for (uint32_t r = 0; r < nbits; r++) {
+        const int sh = (int)(64 - delta_log - r - 1);
+        const uint64_t alpha = r ? 1ULL << (delta_log + r - 2) : 0;   // added to the body of the PREVIOUS round's bootstrap (:219)
+        int rc = eb_update_shift_launch(d_buf, r ? d_pbs : nullptr, d_shift, blen, (int)batch, sh, alpha, 64, ctx->stream);
+        ctx->launches++;
+        if (rc) return fail(ctx, "extract_bits shift launch failed: " + std::to_string(rc));
+        if (ks_dev_locked(ctx, ksk, d_shift, d_ks, batch)) return 1;
+        const bool last = r + 1 == nbits;
+        rc = eb_store_launch(d_ks, d_out, slen, (int)batch, (int)nbits, (int)(nbits - 1 - r), last ? 0 : 1, 64, ctx->stream);
+        ctx->launches++;
+        if (rc) return fail(ctx, "extract_bits store launch failed: " + std::to_string(rc));
+        if (last) break;
+        if (br_dev_locked(ctx, bsk, d_ks, d_pbs, (const uint64_t *)d_lut + (size_t)r * glen, nullptr, batch, BR_MODE_LWE)) return 1;
+    }
+    CK(cudaMemcpyAsync(out, d_out, out_b, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
 // ---- device-resident waves over a ciphertext pool -------------------------------------------------------------------
 static_assert(sizeof(b200tfhe_wave_op) == sizeof(WaveOp) && sizeof(WaveOp) == 72, "wave op layout");
 struct b200tfhe_pool {

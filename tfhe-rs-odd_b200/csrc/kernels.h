@@ -115,6 +115,11 @@ int glwe_mul_plain_extract_launch(const void *glwe, const void *polys, void *out
 int pack_elements_launch(const void *in, void *out, int count, int p, size_t len, int batch, int bits, cudaStream_t st);
 int pack_rotate_sum_launch(const void *G, void *out, int p, int k, int N, int batch, int bits, cudaStream_t st);
 
+// wopbs_kernels.cu (element-wise steps of the bit extraction: fft64/crypto/wop_pbs/mod.rs:66-225)
+int eb_update_shift_launch(void *buffer, const void *pbs, void *shifted, size_t len, int batch, int sh, uint64_t alpha, int bits,
+                           cudaStream_t st);
+int eb_store_launch(void *ks, void *out, size_t len, int batch, int nbits, int slot, int add_quarter, int bits, cudaStream_t st);
+
 // misc_kernels.cu
 int modswitch_launch(const void *in, uint32_t *out, size_t count, int log2N, int bits, cudaStream_t st);
 int sample_extract_launch(const void *glwe, void *lwe, int k, int N, int batch, int bits, cudaStream_t st);
