@@ -188,6 +188,7 @@ int b200tfhe_pbs_ks_batch_dev(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, co
  * algorithms/lwe_packing_keyswitch_key_generation.rs:60-150): [kN][l_ks (level l_ks first)][(k+1)N], input key = the big LWE
  * key, output key = the GLWE key, decomposition = p->ks_* (as the gadget server key builds it, bootstrapping.rs:355-363). */
 typedef struct b200tfhe_pksk b200tfhe_pksk;
+typedef struct b200tfhe_pfpksk b200tfhe_pfpksk;   /* circuit-bootstrap private functional packing keyswitch key list */
 int b200tfhe_pksk_upload_u64(b200tfhe_context *ctx, const b200tfhe_params *p, const uint64_t *pksk, b200tfhe_pksk **out);
 int b200tfhe_pksk_destroy(b200tfhe_pksk *pksk);
 /* keyswitch_lwe_ciphertext_into_glwe_ciphertext (algorithms/lwe_packing_keyswitch.rs:100-187) over a list:
@@ -218,6 +219,29 @@ int b200tfhe_pack_into_accumulator_batch_u64(b200tfhe_context *ctx, const b200tf
  * extracted ciphertext (index nbits - 1) is bit-identical to the reference's; the later ones depend on bootstraps. */
 int b200tfhe_extract_bits_batch_u64(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, const uint64_t *in,
                                     uint32_t delta_log, uint32_t nbits, uint64_t *out, uint32_t batch);
+
+/* ---- circuit bootstrap + vertical packing, the second half of the WoP-PBS ---------------------
+ * Key list of generate_circuit_bootstrap_lwe_pfpksk_list (core_crypto/algorithms/lwe_wopbs.rs:80-160) in the reference layout
+ * LwePrivateFunctionalPackingKeyswitchKeyList: [k+1 keys][kN+1 input elements, the body's last][level 1..pfks_level][(k+1)N].
+ * p gives k, N and the torus width; pfks_base_log up to 28. */
+int b200tfhe_cbs_pfpksk_upload_u64(b200tfhe_context *ctx, const b200tfhe_params *p, uint32_t pfks_base_log, uint32_t pfks_level,
+                                   const uint64_t *list, b200tfhe_pfpksk **out);
+int b200tfhe_cbs_pfpksk_destroy(b200tfhe_pfpksk *k);
+/* private_functional_keyswitch_lwe_ciphertext_into_glwe_ciphertext
+ * (core_crypto/algorithms/lwe_private_functional_packing_keyswitch.rs:8-89) with key `key_index` of the list over a batch:
+ * in batch x (kN+1), out_glwe batch x (k+1)N.  Bit-exact (tcgen05 kind::i8 GEMM over exactly split digits). */
+int b200tfhe_pfpks_batch_u64(b200tfhe_context *ctx, const b200tfhe_pfpksk *pf, uint32_t key_index, const uint64_t *in, uint64_t *out_glwe,
+                             uint32_t batch);
+/* circuit_bootstrap_boolean_vertical_packing_lwe_ciphertext_list_mem_optimized (lwe_wopbs.rs:651-704 ->
+ * fft64/crypto/wop_pbs/mod.rs:647-853) over a batch.  bits_in: batch x nbits x (n+1), the output of extract_bits (most
+ * significant bit first, each scaled by q/2); luts: n_luts x N, ONE polynomial per look-up table (nbits <= log2 N; the CMUX tree
+ * that multi-polynomial tables need, :468-592, is not built); out: batch x n_luts x (kN+1) under the big key, out[b][o] encrypts
+ * luts[o][index of the bits of b].  Per input: nbits * cbs_level bootstraps (homomorphic_shift_boolean :369-444),
+ * (k+1) private functional packing keyswitches each, Fourier conversion of the GGSWs, and n_luts blind rotations over the
+ * ciphertext's own GGSW list (:866-892) with sample extraction. */
+int b200tfhe_cbs_vertical_packing_batch_u64(b200tfhe_context *ctx, const b200tfhe_bsk *bsk, const b200tfhe_pfpksk *pf, const uint64_t *bits_in,
+                                            uint32_t nbits, const uint64_t *luts, uint32_t n_luts, uint32_t cbs_base_log, uint32_t cbs_level,
+                                            uint64_t *out, uint32_t batch);
 
 /* ---- device-resident waves over a ciphertext pool ---------------------------------------------
  * The reference evaluates a shortint / integer / Trivium circuit as rayon-parallel layers of

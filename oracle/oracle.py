@@ -35,6 +35,9 @@ PARAMS = {
     # multi-bit PBS sets (shortint/parameters/multi_bit.rs:115-132 group 2, :173-190 group 3) and toy versions
     "MULTI_BIT_2_2_GROUP_2": (818, 1, 2048, 22, 1, 5, 3, 64, 0.000002226459789930014, 0.0000000000000003152931493498455, 16, "ks_pbs"),
     "MULTI_BIT_2_2_GROUP_3": (888, 1, 2048, 21, 1, 7, 2, 64, 0.0000006125031601933181, 0.0000000000000003152931493498455, 16, "ks_pbs"),
+    # WOPBS_PARAM_MESSAGE_2_CARRY_2_KS_PBS (shortint/parameters/parameters_wopbs_message_carry.rs:432-451) and a toy of the same shape
+    "WOPBS_MESSAGE_2_CARRY_2": (769, 1, 2048, 15, 2, 6, 2, 64, 0.0000043131554647504185, 0.00000000000000029403601535432533, 16, "ks_pbs"),
+    "TOY_WOP": (12, 1, 2048, 15, 2, 6, 2, 64, 1e-9, 0.00000000000000029403601535432533, 16, "ks_pbs"),
     "TOY_MB_G2": (12, 1, 512, 12, 2, 4, 4, 64, 1e-9, 1e-15, 4, "ks_pbs"),
     "TOY_MB_G3": (12, 1, 512, 12, 2, 4, 4, 64, 1e-9, 1e-15, 4, "ks_pbs"),
     "TOY_MB22_G2": (12, 1, 2048, 22, 1, 5, 3, 64, 1e-9, 0.0000000000000003152931493498455, 16, "ks_pbs"),
@@ -50,6 +53,10 @@ PARAMS = {
 # LweBskGroupingFactor of the multi-bit sets (absent = classic bootstrap key)
 GROUPING = {"MULTI_BIT_2_2_GROUP_2": 2, "MULTI_BIT_2_2_GROUP_3": 3, "TOY_MB_G2": 2, "TOY_MB_G3": 3, "TOY_MB22_G2": 2, "TOY_MB22_G3": 3,
             "GOLD_MB": 2}
+
+
+# (pfks_base_log, pfks_level, cbs_base_log, cbs_level) of the WoP-PBS sets
+WOPBS = {"WOPBS_MESSAGE_2_CARRY_2": (15, 2, 5, 3), "TOY_WOP": (15, 2, 5, 3)}
 
 
 def build(force=False):
@@ -278,4 +285,37 @@ class Oracle:
         out = np.zeros((cts.shape[0], int(nbits), self.n + 1), np.uint64)
         for i in range(cts.shape[0]):
             lib().orc_extract_bits(C.byref(self.p), _p(self.ksk), _p(self.fbsk), _p(cts[i]), int(delta_log), int(nbits), _p(out[i]))
+        return out
+
+    # ---- circuit bootstrap + vertical packing (fft64/crypto/wop_pbs/mod.rs:243-853) ---------------------
+    def gen_cbs_pfpksk_list(self, pf_base_log, pf_level):
+        """k+1 private functional packing keyswitch keys, reference layout [k+1][kN+1][level 1..L][(k+1)N]."""
+        out = np.zeros((self.k + 1) * (self.big + 1) * int(pf_level) * self.glwe_len, np.uint64)
+        lib().orc_gen_cbs_pfpksk_list(C.byref(self.p), int(pf_base_log), int(pf_level), _p(self.glwe_key), C.c_uint64(self.seed + 5),
+                                      _p(out), self.nthreads)
+        return out
+
+    def pfpks(self, key, pf_base_log, pf_level, cts):
+        cts = u64(cts).reshape(-1, self.big + 1)
+        out = np.zeros((cts.shape[0], self.glwe_len), np.uint64)
+        for i in range(cts.shape[0]):
+            lib().orc_pfpks(C.byref(self.p), int(pf_base_log), int(pf_level), _p(key), _p(cts[i]), _p(out[i]))
+        return out
+
+    def circuit_bootstrap_boolean(self, pfpksk_list, wop, bit_ct, delta_log):
+        pb, pl, cb, cl = wop
+        out = np.zeros((cl, self.k + 1, self.glwe_len), np.uint64)
+        lib().orc_circuit_bootstrap_boolean(C.byref(self.p), _p(self.fbsk), _p(pfpksk_list), pb, pl, cb, cl, _p(u64(bit_ct)), int(delta_log), _p(out))
+        return out
+
+    def cbs_vertical_packing(self, pfpksk_list, wop, bits_in, luts):
+        """bits_in [B][nbits][n+1] (MSB first, q/2-scaled), luts [n_out][N] -> [B][n_out][kN+1]."""
+        pb, pl, cb, cl = wop
+        bits_in = u64(bits_in)
+        bits_in = bits_in.reshape(-1, bits_in.shape[-2], self.n + 1)
+        luts = u64(luts).reshape(-1, self.N)
+        out = np.zeros((bits_in.shape[0], luts.shape[0], self.big + 1), np.uint64)
+        for b in range(bits_in.shape[0]):
+            lib().orc_cbs_vertical_packing(C.byref(self.p), _p(self.fbsk), _p(pfpksk_list), pb, pl, cb, cl, _p(bits_in[b]),
+                                           bits_in.shape[1], _p(luts), luts.shape[0], _p(out[b]))
         return out

@@ -171,3 +171,34 @@ void orc_gen_pksk(const orc_params *p, const uint64_t *big_key, const uint64_t *
     pksk_ctx c = { p, big_key, glwe_key, seed, pksk };
     orc_parallel_for(pksk_one, &c, p->k * p->N, nthreads);
 }
+
+/* algorithms/lwe_wopbs.rs:80-160 (generate_circuit_bootstrap_lwe_pfpksk_list) over
+ * lwe_private_functional_packing_keyswitch_key_generation.rs:27-140: k+1 private functional packing keyswitch keys from the big
+ * LWE key (the flattened GLWE key) to the GLWE key, function x -> -x, polynomial = S_r for r < k and the constant -1 for r = k.
+ * Block (r, j) holds, for level 1..L, a GLWE encryption of  polynomial_r * (f(1) * bit_j) * 2^(bits - base_log*level),
+ * bit_j = big key bit j for j < kN and -1 for the body slot j = kN.  Layout [k+1][kN+1][level 1..L][(k+1)N]. */
+typedef struct { const orc_params *p; const uint64_t *glwe_key; uint64_t seed; uint64_t *out; int base_log, level; } pf_ctx;
+static void pfpksk_one(void *c, int idx) {
+    pf_ctx *x = (pf_ctx *)c; const orc_params *p = x->p;
+    int N = p->N, k = p->k, L = x->level, n_in = k * N + 1; size_t glwe = (size_t)(k + 1) * N; uint64_t m = maskw(p->bits);
+    int r = idx / n_in, j = idx % n_in;
+    rng_t rg; rng_seed(&rg, x->seed, 0x5000000ULL + (uint64_t)idx);
+    uint64_t *scratch = (uint64_t *)malloc(sizeof(uint64_t) * N);
+    uint64_t key_bit = j < k * N ? x->glwe_key[j] : m;                 /* last_key_iter_bit = Scalar::MAX (:84-90) */
+    uint64_t scalar = ((0 - 1ULL) * key_bit) & m;                      /* f(Scalar::ONE).wrapping_mul(input_key_bit) (:119) */
+    for (int level = 1; level <= L; level++) {
+        uint64_t *g = x->out + (((size_t)r * n_in + j) * L + (level - 1)) * glwe;
+        uint64_t *body = g + (size_t)k * N;
+        uint64_t summand = (scalar << (p->bits - x->base_log * level)) & m;   /* to_recomposition_summand */
+        memset(g, 0, sizeof(uint64_t) * glwe);
+        if (r < k) { for (int t = 0; t < N; t++) body[t] = (x->glwe_key[(size_t)r * N + t] * summand) & m; }
+        else body[0] = ((0 - summand)) & m;                           /* last polynomial = [Scalar::MAX, 0, ...] (lwe_wopbs.rs:128-136) */
+        glwe_encrypt_assign(p, x->glwe_key, g, &rg, scratch);
+    }
+    free(scratch);
+}
+void orc_gen_cbs_pfpksk_list(const orc_params *p, int base_log, int level, const uint64_t *glwe_key, uint64_t seed, uint64_t *out,
+                             int nthreads) {
+    pf_ctx c = { p, glwe_key, seed, out, base_log, level };
+    orc_parallel_for(pfpksk_one, &c, (p->k + 1) * (p->k * p->N + 1), nthreads);
+}

@@ -30,3 +30,80 @@ void orc_extract_bits(const orc_params *p, const uint64_t *ksk, const double *fb
     }
     free(buffer); free(shifted); free(ks); free(pbs); free(acc);
 }
+
+/* algorithms/lwe_private_functional_packing_keyswitch.rs:8-89.  key: one pfpksk [kN+1][level 1..L][(k+1)N]; in: [kN+1] (the
+ * body is decomposed like a mask element); out: GLWE [(k+1)N]. */
+void orc_pfpks(const orc_params *p, int base_log, int level, const uint64_t *key, const uint64_t *in, uint64_t *out) {
+    const uint64_t m = p->bits == 64 ? ~0ULL : ((1ULL << p->bits) - 1);
+    const int n_in = p->k * p->N + 1;
+    const size_t glwe = (size_t)(p->k + 1) * p->N;
+    uint64_t digits[64];
+    memset(out, 0, sizeof(uint64_t) * glwe);                                              /* :63 */
+    for (int j = 0; j < n_in; j++) {                                                      /* :71-88 */
+        orc_decompose(in[j], base_log, level, p->bits, digits);                           /* emits level L first */
+        for (int t = 0; t < level; t++) {
+            const uint64_t d = digits[t];
+            if (d == 0) continue;
+            const uint64_t *row = key + ((size_t)j * level + (level - 1 - t)) * glwe;    /* keyswitch_key_block.iter().rev() */
+            for (size_t c = 0; c < glwe; c++) out[c] -= d * row[c];
+        }
+    }
+    for (size_t c = 0; c < glwe; c++) out[c] &= m;
+}
+
+/* fft64/crypto/wop_pbs/mod.rs:243-344 (circuit_bootstrap_boolean) with :369-444 (homomorphic_shift_boolean):
+ * in: [n+1], one bit at position delta_log; ggsw_out: standard-domain GGSW [level 1..cbs_level][k+1 rows][(k+1)N]. */
+void orc_circuit_bootstrap_boolean(const orc_params *p, const double *fbsk, const uint64_t *pfpksk_list, int pf_base_log, int pf_level,
+                                   int cbs_base_log, int cbs_level, const uint64_t *in, int delta_log, uint64_t *ggsw_out) {
+    const int W = p->bits, N = p->N, k = p->k, k1 = k + 1, n_in = k * N + 1;
+    const uint64_t m = W == 64 ? ~0ULL : ((1ULL << W) - 1);
+    const size_t glwe = (size_t)k1 * N, key_len = (size_t)n_in * pf_level * glwe;
+    uint64_t *shifted = (uint64_t *)malloc(sizeof(uint64_t) * (p->n + 1)), *bs = (uint64_t *)malloc(sizeof(uint64_t) * n_in);
+    uint64_t *acc = (uint64_t *)calloc(glwe, sizeof(uint64_t));
+    for (int level = 1; level <= cbs_level; level++) {                                    /* :320-343 */
+        for (int c = 0; c <= p->n; c++) shifted[c] = (in[c] << (W - delta_log - 1)) & m;  /* cleartext mul (:398-402) */
+        shifted[p->n] = (shifted[p->n] + (1ULL << (W - 2))) & m;                          /* + q/4 (:405-407) */
+        const uint64_t alpha = 1ULL << (W - 1 - cbs_base_log * level);
+        for (int c = 0; c < N; c++) acc[(size_t)k * N + c] = (0 - alpha) & m;             /* :423-427 */
+        orc_pbs(p, fbsk, shifted, acc, bs);                                               /* :431-437 */
+        bs[n_in - 1] = (bs[n_in - 1] + alpha) & m;                                        /* :441-443 */
+        for (int r = 0; r < k1; r++)                                                      /* :333-342 */
+            orc_pfpks(p, pf_base_log, pf_level, pfpksk_list + (size_t)r * key_len, bs, ggsw_out + ((size_t)(level - 1) * k1 + r) * glwe);
+    }
+    free(shifted); free(bs); free(acc);
+}
+
+/* :647-746 (circuit_bootstrap_boolean_vertical_packing) for look-up tables of ONE polynomial each (log_lut_number = 0: no CMUX
+ * tree, :812-825), :866-892 (blind_rotate_assign over the GGSW list), ggsw.rs:766-777 (cmux), then sample extraction (:852).
+ * bits_in: [nbits][n+1] (most significant bit first, each scaled by q/2); luts: [n_out][N]; out: [n_out][kN+1]. */
+void orc_cbs_vertical_packing(const orc_params *p, const double *fbsk, const uint64_t *pfpksk_list, int pf_base_log, int pf_level,
+                              int cbs_base_log, int cbs_level, const uint64_t *bits_in, int nbits, const uint64_t *luts, int n_out,
+                              uint64_t *out) {
+    const int W = p->bits, N = p->N, k = p->k, k1 = k + 1;
+    const uint64_t m = W == 64 ? ~0ULL : ((1ULL << W) - 1);
+    const size_t glwe = (size_t)k1 * N, ggsw_len = (size_t)cbs_level * k1 * glwe;
+    uint64_t *ggsw_res = (uint64_t *)malloc(sizeof(uint64_t) * ggsw_len);
+    double *fggsw = (double *)malloc(sizeof(double) * ggsw_len * (size_t)nbits);
+    for (int i = 0; i < nbits; i++) {                                                     /* :721-733 */
+        orc_circuit_bootstrap_boolean(p, fbsk, pfpksk_list, pf_base_log, pf_level, cbs_base_log, cbs_level,
+                                      bits_in + (size_t)i * (p->n + 1), W - 1, ggsw_res);
+        for (size_t q = 0; q < ggsw_len / N; q++) orc_fft_forward_torus(N, ggsw_res + q * N, W, fggsw + (size_t)i * ggsw_len + q * N);
+    }
+    orc_params pc = *p;
+    pc.pbs_level = cbs_level;
+    pc.pbs_base_log = cbs_base_log;
+    uint64_t *acc = (uint64_t *)malloc(sizeof(uint64_t) * glwe), *ct1 = (uint64_t *)malloc(sizeof(uint64_t) * glwe);
+    for (int o = 0; o < n_out; o++) {                                                     /* :740-745 */
+        memset(acc, 0, sizeof(uint64_t) * glwe);
+        for (int c = 0; c < N; c++) acc[(size_t)k * N + c] = luts[(size_t)o * N + c] & m;
+        uint64_t deg = 1;
+        for (int i = nbits - 1; i >= 0; i--) {                                            /* ggsw_list.into_ggsw_iter().rev() (:874) */
+            for (int j = 0; j < k1; j++) orc_monomial_div(ct1 + (size_t)j * N, acc + (size_t)j * N, N, deg, W);
+            deg <<= 1;
+            for (size_t c = 0; c < glwe; c++) ct1[c] = (ct1[c] - acc[c]) & m;             /* cmux: ct1 -= ct0 */
+            orc_add_external_product(&pc, acc, fggsw + (size_t)i * ggsw_len, ct1);
+        }
+        orc_sample_extract0(out + (size_t)o * ((size_t)k * N + 1), acc, k, N, W);
+    }
+    free(ggsw_res); free(fggsw); free(acc); free(ct1);
+}

@@ -101,6 +101,19 @@ void orc_pack_into_accumulator(const orc_params *p, const uint64_t *pksk, const 
 void orc_extract_bits(const orc_params *p, const uint64_t *ksk, const double *fbsk, const uint64_t *in, int delta_log, int nbits,
                       uint64_t *out);
 
+/* private functional packing keyswitch, algorithms/lwe_private_functional_packing_keyswitch.rs:8-89 ; key [kN+1][level 1..L][(k+1)N] */
+void orc_pfpks(const orc_params *p, int base_log, int level, const uint64_t *key, const uint64_t *in, uint64_t *out_glwe);
+/* circuit_bootstrap_boolean, wop_pbs/mod.rs:243-344,369-444 ; ggsw_out [cbs_level][k+1][(k+1)N] */
+void orc_circuit_bootstrap_boolean(const orc_params *p, const double *fbsk, const uint64_t *pfpksk_list, int pf_base_log, int pf_level,
+                                   int cbs_base_log, int cbs_level, const uint64_t *in, int delta_log, uint64_t *ggsw_out);
+/* circuit_bootstrap_boolean_vertical_packing, :647-853, one-polynomial look-up tables ; out [n_out][kN+1] */
+void orc_cbs_vertical_packing(const orc_params *p, const double *fbsk, const uint64_t *pfpksk_list, int pf_base_log, int pf_level,
+                              int cbs_base_log, int cbs_level, const uint64_t *bits_in, int nbits, const uint64_t *luts, int n_out,
+                              uint64_t *out);
+/* generate_circuit_bootstrap_lwe_pfpksk_list, algorithms/lwe_wopbs.rs:80-160 ; out [k+1][kN+1][level 1..L][(k+1)N] */
+void orc_gen_cbs_pfpksk_list(const orc_params *p, int base_log, int level, const uint64_t *glwe_key, uint64_t seed, uint64_t *out,
+                             int nthreads);
+
 /* ---- LUTs and gate glue ---- */
 /* shortint/engine/mod.rs:72-128 ; f_table has p = msg_mod*carry_mod entries */
 void orc_fill_accumulator(const orc_params *p, const uint64_t *f_table, int pmod, uint64_t *glwe_out);

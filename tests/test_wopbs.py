@@ -137,3 +137,130 @@ def test_gpu_extract_bits_full_size_2_2(ctx):
     assert np.array_equal(got[:2, nbits - 1], ref[:, nbits - 1])
     _, ph_ref = _decrypt_bits(o, ref)
     assert np.abs((ph[:2] - ph_ref).astype(np.int64) / 2.0 ** 64).max() < _diff_bound(o, nbits) < 0.125
+
+
+# ---- circuit bootstrap + vertical packing (wop_pbs/mod.rs:243-853) ---------------------------------------------------------
+def _wop(name):
+    from oracle.oracle import WOPBS
+    return WOPBS[name]
+
+
+_PFPKSK = {}
+
+
+def _pfpksk(o, name):
+    if name not in _PFPKSK:
+        pb, pl, _, _ = _wop(name)
+        _PFPKSK[name] = o.gen_cbs_pfpksk_list(pb, pl)
+    return _PFPKSK[name]
+
+
+def _luts(o, nbits):
+    """two 4-bit -> 4-bit tables as polynomials: coefficient j holds f(j) * 2^60"""
+    lut = np.zeros((2, o.N), np.uint64)
+    for j in range(1 << nbits):
+        lut[0, j] = np.uint64(((j * j + 1) % 16) << 60)
+        lut[1, j] = np.uint64(((15 - j) % 16) << 60)
+    return lut
+
+
+def _decode4(o, cts):
+    ph = o.phase(cts.reshape(-1, o.big + 1)).reshape(cts.shape[:-1])
+    return ((ph.astype(np.uint64) + np.uint64(1 << 59)) >> np.uint64(60)).astype(int) & 15, ph
+
+
+def _sdiff(a, b):
+    """signed torus difference of two 64-bit values as a Python int"""
+    d = (int(a) - int(b)) % U64
+    return d - U64 if d >= U64 // 2 else d
+
+
+def test_oracle_pfpks_and_circuit_bootstrap():
+    """pfpks with key r decrypts to -phase * S_r (r < k) / +phase (r = k) (lwe_wopbs.rs:128-157); the GGSW of a circuit
+    bootstrap decrypts, level by level, to bit * 2^(64 - b*level) on the last row; vertical packing evaluates the tables."""
+    o = get_oracle("TOY_WOP")
+    wop = _wop("TOY_WOP")
+    pf = _pfpksk(o, "TOY_WOP")
+    key_len = (o.big + 1) * wop[1] * o.glwe_len
+    ct = o.encrypt(np.array([3 << 60], dtype=np.uint64), under="big", seed=61)
+    g = o.pfpks(pf[o.k * key_len:(o.k + 1) * key_len], wop[0], wop[1], ct)[0]
+    ph = o.glwe_phase(g)
+    assert abs(_sdiff(ph[0], 3 << 60)) < 2 ** 40 and np.abs(ph[1:].astype(np.int64)).max() < 2 ** 40
+    msgs = np.array([5, 10, 15, 0, 7], dtype=np.uint64)
+    bits = o.extract_bits(o.encrypt(msgs << np.uint64(60), under="big", seed=67), 60, 4)
+    ggsw = o.circuit_bootstrap_boolean(pf, wop, bits[0, 1], 63)               # bit 1 of 5 = 0b0101 (MSB first) is 1
+    for lvl in range(wop[3]):
+        ph = o.glwe_phase(ggsw[lvl, o.k])
+        assert abs(_sdiff(ph[0], 1 << (64 - wop[2] * (lvl + 1)))) < 2 ** 44
+    out = o.cbs_vertical_packing(pf, wop, bits, _luts(o, 4))
+    dec, ph = _decode4(o, out)
+    assert np.array_equal(dec[:, 0], (msgs * msgs + 1) % 16) and np.array_equal(dec[:, 1], 15 - msgs)
+    assert np.abs((ph - (dec.astype(np.uint64) << np.uint64(60))).astype(np.int64)).max() < 2.0 ** 64 / 256
+
+
+def _wop_keys(ctx, o, name):
+    import tfhe_rs_odd_b200 as t
+    t_, bsk, ksk = _keys(ctx, o)
+    wop = _wop(name)
+    pf = t.core_crypto.LwePrivateFunctionalPackingKeyswitchKeyList.upload(ctx, params_of(o), wop[0], wop[1], _pfpksk(o, name))
+    return t, bsk, ksk, pf, wop
+
+
+@pytest.mark.gpu
+def test_gpu_pfpks_bit_exact(ctx):
+    o = get_oracle("TOY_WOP")
+    t, bsk, ksk, pf, wop = _wop_keys(ctx, o, "TOY_WOP")
+    rng = np.random.default_rng(71)
+    B = 150
+    cts = rng.integers(0, U64, size=(B, o.big + 1), dtype=np.uint64)
+    cts[0, :] = 0
+    cts[1, :] = U64 - 1
+    cts[2, :] = 1 << 63
+    cts[3, :] = (1 << 63) - 1
+    cts[4, :] = np.uint64(1 << 33)                                            # exactly half of the last kept digit: rounding boundary
+    key_len = (o.big + 1) * wop[1] * o.glwe_len
+    host = _pfpksk(o, "TOY_WOP")
+    for r in range(o.k + 1):
+        got = t.core_crypto.private_functional_keyswitch_lwe_ciphertext_into_glwe_ciphertext(pf, r, cts)
+        ref = o.pfpks(host[r * key_len:(r + 1) * key_len], wop[0], wop[1], cts[:12])
+        assert np.array_equal(got[:12], ref)
+        one = t.core_crypto.private_functional_keyswitch_lwe_ciphertext_into_glwe_ciphertext(pf, r, cts[7])
+        assert np.array_equal(one, ref[7])
+        assert np.array_equal(t.core_crypto.private_functional_keyswitch_lwe_ciphertext_into_glwe_ciphertext(pf, r, cts[100:]), got[100:])
+    with pytest.raises(t.B200TfheError, match="out of range"):
+        t.core_crypto.private_functional_keyswitch_lwe_ciphertext_into_glwe_ciphertext(pf, o.k + 1, cts)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,B", [("TOY_WOP", 16), ("WOPBS_MESSAGE_2_CARRY_2", 8)])
+def test_gpu_wopbs_extract_then_circuit_bootstrap_vertical_packing(ctx, name, B):
+    """The whole WoP-PBS of a 4-bit message (shortint/wopbs/mod.rs:575-680): extract_bits, then circuit bootstrap + vertical
+    packing with two look-up tables.  Every message decrypts to table[message]; the oracle runs the first ciphertexts."""
+    o = get_oracle(name)
+    t, bsk, ksk, pf, wop = _wop_keys(ctx, o, name)
+    nbits = 4
+    msgs = (np.arange(B, dtype=np.uint64) * np.uint64(5) + np.uint64(1)) % np.uint64(16)
+    cts = o.encrypt(msgs << np.uint64(60), under="big", seed=73)
+    bits = t.core_crypto.extract_bits_from_lwe_ciphertext_mem_optimized(cts, bsk, ksk, 60, nbits)
+    b, _ = _decrypt_bits(o, bits)
+    assert np.array_equal(b, _bits_msb_first(msgs, nbits))
+    luts = _luts(o, nbits)
+    out = t.core_crypto.circuit_bootstrap_boolean_vertical_packing_lwe_ciphertext_list_mem_optimized(bits, luts, bsk, pf, wop[2], wop[3])
+    assert out.shape == (B, 2, o.big + 1)
+    dec, ph = _decode4(o, out)
+    assert np.array_equal(dec[:, 0], (msgs * msgs + 1) % 16) and np.array_equal(dec[:, 1], 15 - msgs)
+    err = np.abs((ph - (dec.astype(np.uint64) << np.uint64(60))).astype(np.int64)) / 2.0 ** 64
+    nref = 2
+    ref = o.cbs_vertical_packing(_pfpksk(o, name), wop, bits[:nref], luts)       # same extracted bits into the oracle
+    dref, phr = _decode4(o, ref)
+    assert np.array_equal(dref, dec[:nref])
+    eref = np.abs((phr - (dref.astype(np.uint64) << np.uint64(60))).astype(np.int64)) / 2.0 ** 64
+    assert err.max() < max(8 * eref.max(), 2.0 ** -9) < 1 / 64                   # same noise regime as the oracle's outputs
+    one = t.core_crypto.circuit_bootstrap_boolean_vertical_packing_lwe_ciphertext_list_mem_optimized(bits[3], luts[1], bsk, pf, wop[2], wop[3])
+    d1, _ = _decode4(o, one)
+    assert one.shape == (1, o.big + 1) and d1[0] == 15 - int(msgs[3])
+    with pytest.raises(t.B200TfheError, match="log2"):
+        big = np.zeros((1, 12, o.n + 1), np.uint64)
+        t.core_crypto.circuit_bootstrap_boolean_vertical_packing_lwe_ciphertext_list_mem_optimized(big, luts, bsk, pf, wop[2], wop[3])
+    with pytest.raises(t.B200TfheError, match="no blind-rotation instance"):
+        t.core_crypto.circuit_bootstrap_boolean_vertical_packing_lwe_ciphertext_list_mem_optimized(bits, luts, bsk, pf, 4, 3)

@@ -381,3 +381,72 @@ def extract_bits_from_lwe_ciphertext_mem_optimized(lwe_in, fourier_bsk, ksk, del
         np.copyto(lwe_list_out, res)
         return lwe_list_out
     return res
+
+
+# ---- circuit bootstrap + vertical packing (second half of the WoP-PBS) ---------------------------------------------------
+class LwePrivateFunctionalPackingKeyswitchKeyList:
+    """Device-resident key list of the circuit bootstrap (entities/lwe_private_functional_packing_keyswitch_key_list.rs,
+    generated by algorithms/lwe_wopbs.rs:80-160): [k+1][kN+1][level 1..L][(k+1)N]."""
+
+    def __init__(self, ctx, params, handle, decomp_base_log, decomp_level_count):
+        self.ctx, self.params, self._h = ctx, params, handle
+        self.decomp_base_log, self.decomp_level_count = decomp_base_log, decomp_level_count
+
+    @classmethod
+    def upload(cls, ctx, params, decomp_base_log, decomp_level_count, key_list):
+        a = np.ascontiguousarray(key_list, dtype=np.uint64).reshape(-1)
+        k, N = params.glwe_dimension, params.polynomial_size
+        expect = (k + 1) * (k * N + 1) * int(decomp_level_count) * (k + 1) * N
+        if a.size != expect:
+            raise B200TfheError(f"pfpksk list has {a.size} scalars, parameters imply {expect}")
+        h = C.c_void_p()
+        ctx.check(ctx._lib.b200tfhe_cbs_pfpksk_upload_u64(ctx._h, C.byref(params), int(decomp_base_log), int(decomp_level_count), _ptr(a), C.byref(h)))
+        return cls(ctx, params, h, int(decomp_base_log), int(decomp_level_count))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.ctx._lib.b200tfhe_cbs_pfpksk_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def private_functional_keyswitch_lwe_ciphertext_into_glwe_ciphertext(pfpksk_list, key_index, input_lwe):
+    """algorithms/lwe_private_functional_packing_keyswitch.rs:8-89 with key `key_index` of the list: [kN+1] or [B][kN+1] ->
+    GLWE [(k+1)N] per ciphertext.  Bit-exact."""
+    p, ctx = pfpksk_list.params, pfpksk_list.ctx
+    a, single = _as_list(input_lwe, p.glwe_dimension * p.polynomial_size + 1, 64, "pfpks input")
+    out = np.empty((a.shape[0], (p.glwe_dimension + 1) * p.polynomial_size), np.uint64)
+    ctx.check(ctx._lib.b200tfhe_pfpks_batch_u64(ctx._h, pfpksk_list._h, int(key_index), _ptr(a), _ptr(out), a.shape[0]))
+    return out[0] if single else out
+
+
+def circuit_bootstrap_boolean_vertical_packing_lwe_ciphertext_list_mem_optimized(lwe_list_in, big_lut_as_polynomial_list, fourier_bsk,
+                                                                                 pfpksk_list, base_log_cbs, level_cbs,
+                                                                                 number_of_luts=None, lwe_list_out=None):
+    """algorithms/lwe_wopbs.rs:651-704 -> fft64/crypto/wop_pbs/mod.rs:647-853.  lwe_list_in: [nbits][n+1] or [B][nbits][n+1]
+    (extract_bits output); big_lut_as_polynomial_list: [number_of_luts][N] (one polynomial per table; the reference deduces
+    number_of_luts from lwe_list_out, :736); result [number_of_luts][kN+1] per input."""
+    p, ctx = fourier_bsk.params, fourier_bsk.ctx
+    if p.torus_bits != 64:
+        raise B200TfheError("circuit bootstrap: 64-bit torus only")
+    a = np.ascontiguousarray(lwe_list_in, dtype=np.uint64)
+    if a.ndim not in (2, 3) or a.shape[-1] != p.lwe_dimension + 1:
+        raise B200TfheError(f"circuit bootstrap input: ciphertext length {a.shape[-1] if a.ndim else 0} != expected {p.lwe_dimension + 1}")
+    single = a.ndim == 2
+    a = a.reshape(-1, a.shape[-2], a.shape[-1])
+    luts = np.ascontiguousarray(big_lut_as_polynomial_list, dtype=np.uint64).reshape(-1, p.polynomial_size)
+    if number_of_luts is not None and luts.shape[0] != int(number_of_luts):
+        raise B200TfheError("circuit bootstrap: look-up tables of more than one polynomial need the CMUX tree, which is not built")
+    out = np.zeros((a.shape[0], luts.shape[0], p.glwe_dimension * p.polynomial_size + 1), np.uint64)
+    ctx.check(ctx._lib.b200tfhe_cbs_vertical_packing_batch_u64(ctx._h, fourier_bsk._h, pfpksk_list._h, _ptr(a), a.shape[1], _ptr(luts),
+                                                               luts.shape[0], int(base_log_cbs), int(level_cbs), _ptr(out), a.shape[0]))
+    res = out[0] if single else out
+    if lwe_list_out is not None:
+        np.copyto(lwe_list_out, res)
+        return lwe_list_out
+    return res

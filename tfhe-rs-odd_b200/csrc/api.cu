@@ -16,7 +16,7 @@ using namespace b200tfhe;
 static thread_local std::string g_global_err = "";
 
 struct Workspace {
-    enum { IN = 0, OUT, MID, LUTS, IDX, A, B, DIG, NSLOTS };
+    enum { IN = 0, OUT, MID, LUTS, IDX, A, B, DIG, C, D, NSLOTS };
     void *ptr[NSLOTS] = {};
     size_t cap[NSLOTS] = {};
     cudaError_t get(int slot, size_t bytes, void **out) {
@@ -906,6 +906,179 @@ int b200tfhe_extract_bits_batch_u64(b200tfhe_context *ctx, const b200tfhe_ksk *k
         if (br_dev_locked(ctx, bsk, d_ks, d_pbs, (const uint64_t *)d_lut + (size_t)r * glen, nullptr, batch, BR_MODE_LWE)) return 1;
     }
     CK(cudaMemcpyAsync(out, d_out, out_b, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+// ---- circuit bootstrap + vertical packing, the second half of the WoP-PBS ---------------------------------------------
+// LwePrivateFunctionalPackingKeyswitchKeyList of the circuit bootstrap (k+1 keys, algorithms/lwe_wopbs.rs:80-160) as k+1
+// byte-plane matrices for the tensor-core keyswitch: [kN+1 input elements incl. the body][level * sub rows] x (k+1)N columns.
+struct b200tfhe_pfpksk {
+    b200tfhe_context *ctx;
+    Params p;
+    int base_log, level, sub, sub_bits;
+    std::vector<KSTensorKey> keys;
+};
+
+int b200tfhe_cbs_pfpksk_upload_u64(b200tfhe_context *ctx, const b200tfhe_params *pp, uint32_t pfks_base_log, uint32_t pfks_level,
+                                   const uint64_t *list, b200tfhe_pfpksk **out) {
+    REQUIRE(ctx && pp && out && list, "cbs_pfpksk_upload: null argument");
+    *out = nullptr;
+    REQUIRE(pp->torus_bits == 64, "cbs_pfpksk_upload: 64-bit torus only");
+    REQUIRE(pp->glwe_dimension > 0 && is_pow2(pp->polynomial_size), "invalid dimensions");
+    REQUIRE(pfks_level >= 1 && pfks_base_log >= 1 && pfks_base_log <= 28 && pfks_level * pfks_base_log < 64, "invalid pfks decomposition");
+    Params p = to_params(pp);
+    const int sub = ((int)pfks_base_log + 6) / 7, sub_bits = ((int)pfks_base_log + sub - 1) / sub;
+    const int n_in = p.k * p.N + 1, n_out = (p.k + 1) * p.N - 1, rows_per = (int)pfks_level * sub;
+    REQUIRE(ks_tc_supported(64, n_in, n_out, rows_per, sub_bits + 1), "cbs_pfpksk_upload: the tensor-core keyswitch does not cover this set");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    const size_t width = (size_t)n_out + 1, key_words = (size_t)n_in * pfks_level * width;
+    void *d_raw = nullptr, *d_exp = nullptr;
+    CK(cudaMalloc(&d_raw, key_words * 8));
+    cudaError_t e = cudaMalloc(&d_exp, key_words * sub * 8);
+    if (e != cudaSuccess) { cudaFree(d_raw); return fail_cuda(ctx, "cudaMalloc(pfpksk)", e); }
+    b200tfhe_pfpksk *h = new b200tfhe_pfpksk{ctx, p, (int)pfks_base_log, (int)pfks_level, sub, sub_bits, {}};
+    h->keys.resize(p.k + 1);
+    int rc = 0;
+    for (int r = 0; r <= p.k && !rc; r++) {
+        void *planes = nullptr;
+        if (cudaMemcpy(d_raw, list + (size_t)r * key_words, key_words * 8, cudaMemcpyHostToDevice) != cudaSuccess) { rc = -10; break; }
+        if (cudaMalloc(&planes, ks_tc_key_bytes(64, n_in, n_out, rows_per)) != cudaSuccess) { rc = -11; break; }
+        h->keys[r].d_planes = planes;
+        // reference block order is level 1..L, consumed reversed (lwe_private_functional_packing_keyswitch.rs:81): rev = 1
+        rc = ks_expand_rows_launch(d_raw, d_exp, (size_t)n_in, (int)pfks_level, sub, sub_bits, 1, width, 64, ctx->stream);
+        if (!rc) rc = ks_tc_prepare_key(&h->keys[r], d_exp, planes, 64, n_in, n_out, rows_per, ctx->stream);
+        if (!rc && cudaStreamSynchronize(ctx->stream) != cudaSuccess) rc = -12;
+    }
+    cudaFree(d_raw);
+    cudaFree(d_exp);
+    if (rc) {
+        for (auto &k : h->keys) if (k.d_planes) cudaFree(k.d_planes);
+        delete h;
+        return fail(ctx, "cbs_pfpksk_upload failed: " + std::to_string(rc));
+    }
+    *out = h;
+    return 0;
+}
+int b200tfhe_cbs_pfpksk_destroy(b200tfhe_pfpksk *k) {
+    if (!k) return 0;
+    cudaSetDevice(k->ctx->device);
+    for (auto &t : k->keys) if (t.d_planes) cudaFree(t.d_planes);
+    delete k;
+    return 0;
+}
+
+// private_functional_keyswitch_lwe_ciphertext_into_glwe_ciphertext for key r over `entries` inputs (caller holds ctx->mu)
+static int pfpks_dev_locked(b200tfhe_context *ctx, const b200tfhe_pfpksk *pf, int r, const void *d_in, void *d_out, size_t out_stride,
+                            uint32_t entries) {
+    const Params &p = pf->p;
+    KSLaunch a{d_in, big_len(p), d_out, out_stride, nullptr, nullptr, p.k * p.N + 1, (p.k + 1) * p.N - 1, pf->level, pf->base_log, 64, (int)entries};
+    a.sub = pf->sub;
+    a.sub_bits = pf->sub_bits;
+    a.no_body = true;
+    void *digits = nullptr;
+    CK(ctx->ws.get(Workspace::DIG, (size_t)entries * pf->keys[r].kp, &digits));
+    int rc = ks_tc_launch(a, pf->keys[r], digits, ctx->stream);
+    ctx->launches += 2;
+    if (rc) return fail(ctx, "private functional packing keyswitch launch failed: " + std::to_string(rc));
+    return 0;
+}
+
+int b200tfhe_pfpks_batch_u64(b200tfhe_context *ctx, const b200tfhe_pfpksk *pf, uint32_t key_index, const uint64_t *in, uint64_t *out_glwe,
+                             uint32_t batch) {
+    REQUIRE(ctx && pf, "pfpks: null argument");
+    REQUIRE(pf->ctx == ctx, "key handle belongs to another context");
+    REQUIRE(key_index < pf->keys.size(), "pfpks: key index out of range");
+    if (batch == 0) return 0;
+    REQUIRE(in && out_glwe, "pfpks: null buffer");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    const Params &p = pf->p;
+    const size_t in_b = (size_t)batch * big_len(p) * 8, out_b = (size_t)batch * glwe_len(p) * 8;
+    void *d_in, *d_out;
+    CK(ctx->ws.get(Workspace::IN, in_b, &d_in));
+    CK(ctx->ws.get(Workspace::OUT, out_b, &d_out));
+    CK(cudaMemcpyAsync(d_in, in, in_b, cudaMemcpyHostToDevice, ctx->stream));
+    if (pfpks_dev_locked(ctx, pf, (int)key_index, d_in, d_out, glwe_len(p), batch)) return 1;
+    CK(cudaMemcpyAsync(out_glwe, d_out, out_b, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+// circuit_bootstrap_boolean_vertical_packing (wop_pbs/mod.rs:647-853) over a batch, look-up tables of one polynomial each.
+int b200tfhe_cbs_vertical_packing_batch_u64(b200tfhe_context *ctx, const b200tfhe_bsk *bsk, const b200tfhe_pfpksk *pf, const uint64_t *bits_in,
+                                            uint32_t nbits, const uint64_t *luts, uint32_t n_luts, uint32_t cbs_base_log, uint32_t cbs_level,
+                                            uint64_t *out, uint32_t batch) {
+    REQUIRE(ctx && bsk && pf, "cbs_vertical_packing: null argument");
+    REQUIRE(bsk->ctx == ctx && pf->ctx == ctx, "key handle belongs to another context");
+    const Params &p = bsk->p;
+    REQUIRE(p.bits == 64, "cbs_vertical_packing: 64-bit torus only");
+    // the reference's debug_asserts (:277-309): fpksk input key = bootstrap output key, same GLWE shape
+    REQUIRE(pf->p.k == p.k && pf->p.N == p.N, "cbs_vertical_packing: pfpksk and bootstrap key dimensions differ");
+    REQUIRE(cbs_level >= 1 && cbs_base_log >= 1 && cbs_level * cbs_base_log < 64, "cbs_vertical_packing: invalid cbs decomposition");
+    REQUIRE(nbits >= 1, "cbs_vertical_packing: empty lwe_list_in");   // :672-675
+    int log2N = 0;
+    while ((1 << log2N) < p.N) log2N++;
+    REQUIRE((int)nbits <= log2N, "cbs_vertical_packing: more input bits than log2(N); the CMUX tree for multi-polynomial tables is not built");
+    Params pc = p;
+    pc.pbs_level = (int)cbs_level;
+    pc.pbs_base_log = (int)cbs_base_log;
+    const int Rc = br_supported(pc);
+    REQUIRE(Rc != 0 && Rc != 256, "cbs_vertical_packing: no blind-rotation instance for (N, k, cbs_level, cbs_base_log)");
+    if (batch == 0 || n_luts == 0) return 0;
+    REQUIRE(bits_in && luts && out, "cbs_vertical_packing: null buffer");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    const size_t slen = small_len(p), blen = big_len(p), glen = glwe_len(p);
+    const size_t entries = (size_t)batch * nbits * cbs_level;             // bootstraps = GGSW level matrices
+    const size_t ggsw_words = (size_t)(p.k + 1) * glen;                   // one level matrix
+    const size_t n_vp = (size_t)batch * n_luts;
+    void *d_bits, *d_prep, *d_idx, *d_luts, *d_pbs, *d_ggsw, *d_fggsw, *d_out;
+    CK(ctx->ws.get(Workspace::IN, (size_t)batch * nbits * slen * 8, &d_bits));
+    CK(ctx->ws.get(Workspace::A, entries * slen * 8, &d_prep));
+    CK(ctx->ws.get(Workspace::IDX, (entries + n_vp) * 4, &d_idx));
+    CK(ctx->ws.get(Workspace::LUTS, ((size_t)cbs_level + n_luts) * glen * 8 + (nbits + 1) * 8, &d_luts));
+    CK(ctx->ws.get(Workspace::MID, entries * blen * 8, &d_pbs));
+    CK(ctx->ws.get(Workspace::B, entries * ggsw_words * 8, &d_ggsw));
+    CK(ctx->ws.get(Workspace::C, entries * ggsw_words * 8, &d_fggsw));
+    CK(ctx->ws.get(Workspace::OUT, n_vp * blen * 8, &d_out));
+    uint32_t *d_idx_vp = (uint32_t *)d_idx + entries;
+    uint64_t *d_luts_vp = (uint64_t *)d_luts + (size_t)cbs_level * glen, *d_fake = d_luts_vp + (size_t)n_luts * glen;
+    // host tables: accumulators -2^(63 - b*level) (:423-427), the tables as trivial GLWEs, and the rotation amounts of
+    // blind_rotate_assign (:872-890): step i divides by X^(2^i), i.e. a mask element whose modulus switch is 2N - 2^i, body 0
+    std::vector<uint64_t> h(((size_t)cbs_level + n_luts) * glen + nbits + 1, 0);
+    for (uint32_t l = 0; l < cbs_level; l++)
+        for (int c = 0; c < p.N; c++) h[(size_t)l * glen + (size_t)p.k * p.N + c] = 0 - (1ULL << (63 - cbs_base_log * (l + 1)));
+    for (uint32_t o = 0; o < n_luts; o++)
+        memcpy(&h[((size_t)cbs_level + o) * glen + (size_t)p.k * p.N], luts + (size_t)o * p.N, (size_t)p.N * 8);
+    for (uint32_t i = 0; i < nbits; i++) h[((size_t)cbs_level + n_luts) * glen + i] = (uint64_t)(2 * p.N - (1 << i)) << (64 - log2N - 1);
+    CK(cudaMemcpyAsync(d_luts, h.data(), h.size() * 8, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d_bits, bits_in, (size_t)batch * nbits * slen * 8, cudaMemcpyHostToDevice, ctx->stream));
+    int rc = cbs_prep_launch(d_bits, d_prep, (uint32_t *)d_idx, slen, (int)batch, (int)nbits, (int)cbs_level, 64, ctx->stream);
+    if (!rc) rc = mod_index_launch(d_idx_vp, n_vp, n_luts, ctx->stream);
+    ctx->launches += 2;
+    if (rc) return fail(ctx, "cbs prep launch failed: " + std::to_string(rc));
+    // homomorphic_shift_boolean for every (bit, level) in one bootstrap batch
+    if (br_dev_locked(ctx, bsk, d_prep, d_pbs, d_luts, (const uint32_t *)d_idx, (uint32_t)entries, BR_MODE_LWE)) return 1;
+    rc = cbs_post_launch(d_pbs, blen, entries, (int)cbs_level, (int)cbs_base_log, 64, ctx->stream);
+    ctx->launches++;
+    if (rc) return fail(ctx, "cbs post launch failed: " + std::to_string(rc));
+    // k+1 private functional packing keyswitches per bootstrap output: row r of the level matrix (:333-342)
+    for (int r = 0; r <= p.k; r++)
+        if (pfpks_dev_locked(ctx, pf, r, d_pbs, (uint64_t *)d_ggsw + (size_t)r * glen, ggsw_words, (uint32_t)entries)) return 1;
+    // fill_with_forward_fourier (:732): every polynomial of every GGSW, device layout of the blind-rotation kernels
+    rc = bsk_convert_polys_launch(Rc, 64, entries * (p.k + 1) * (p.k + 1), d_ggsw, d_fggsw, tw_fwd(ctx, Rc), ctx->stream);
+    ctx->launches++;
+    if (rc) return fail(ctx, "ggsw conversion launch failed: " + std::to_string(rc));
+    // vertical_packing with log_lut_number = 0 (:812-853): blind rotation over the ciphertext's own GGSW list + sample extraction
+    BRLaunch a{d_fake, 0, d_luts_vp, d_idx_vp, d_fggsw, d_out, blen, (int)nbits, (int)n_vp, BR_MODE_LWE, tw_fwd(ctx, Rc), tw_inv(ctx, Rc)};
+    a.bsk_ct_stride = (size_t)nbits * cbs_level * (p.k + 1) * (p.k + 1) * (p.N / 2);
+    a.bsk_ct_div = (int)n_luts;
+    rc = br_launch(pc, a, ctx->stream);
+    ctx->launches++;
+    if (rc) return fail(ctx, "vertical packing launch failed: " + std::to_string(rc));
+    CK(cudaMemcpyAsync(out, d_out, n_vp * blen * 8, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     return 0;
 }

@@ -39,7 +39,7 @@ __global__ void __launch_bounds__(CTS *(K + 1) * R)
 blind_rotate_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const T *__restrict__ luts,
                     const uint32_t *__restrict__ lut_idx, const cplx *__restrict__ bsk, T *__restrict__ out,
                     size_t out_stride, int n, int batch, int mode, const cplx *__restrict__ tw_fwd_,
-                    const cplx *__restrict__ tw_inv_) {
+                    const cplx *__restrict__ tw_inv_, size_t bsk_ct_stride, int bsk_ct_div) {
     typedef BRConfig<T, R, K, L, BL, CTS> CFG;
     typedef typename CFG::C C;
     constexpr int K1 = K + 1, N = C::N, REGION = C::REGION;
@@ -74,6 +74,7 @@ blind_rotate_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const T *__
 
     // ---- prologue: modulus switch of the whole input LWE (fft_impl/common.rs:26-43) --------------------
     const T *lwe = lwe_in + (size_t)ct * lwe_stride;
+    bsk += (size_t)(ct / bsk_ct_div) * bsk_ct_stride;   // per-ciphertext GGSW list (0: the shared bootstrap key)
     for (int i = r * R + lane; i <= n; i += K1 * R) ahat[i] = (uint16_t)(modswitch<T>(lwe[i], C::LOGN) & (2 * N - 1));
     __syncthreads();
     // acc <- LUT * X^{-b_hat}  (polynomial_algorithms.rs:315-354), as a rotation by 2N - b_hat
@@ -178,11 +179,15 @@ static int launch_br(const BRLaunch &a, cudaStream_t st) {
     int grid = (a.batch + CTS - 1) / CTS;
     kern<<<grid, CFG::THREADS, smem, st>>>((const T *)a.lwe_in, a.lwe_stride, (const T *)a.luts, a.lut_idx,
                                            (const cplx *)a.bsk, (T *)a.out, a.out_stride, a.n, a.batch, a.mode,
-                                           (const cplx *)a.tw_fwd, (const cplx *)a.tw_inv);
+                                           (const cplx *)a.tw_fwd, (const cplx *)a.tw_inv, a.bsk_ct_stride, a.bsk_ct_div);
     return (int)cudaGetLastError();
 }
 
+// last two: WOPBS_PARAM_MESSAGE_2_CARRY_2_KS_PBS (shortint/parameters/parameters_wopbs_message_carry.rs:432-451), its bootstrap
+// (level 2, base 2^15) and the GGSWs its circuit bootstrap produces (cbs level 3, base 2^5)
 #define BR_INSTANCES(X)              \
+    X(uint64_t, 32, 1, 2, 15, 2)     \
+    X(uint64_t, 32, 1, 3, 5, 1)      \
     X(uint64_t, 32, 1, 1, 23, 3)     \
     X(uint32_t, 16, 2, 3, 6, 2)      \
     X(uint64_t, 16, 3, 1, 18, 1)     \
@@ -210,7 +215,16 @@ int br_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
     // one-ciphertext-per-CTA latency kernel wins (148: 2.8 ms, 296: 5.6 ms); from there one wave of the TMEM kernel
     // (4 ciphertexts per CTA, 7.4 ms for anything up to 592) beats both it and the generic kernel.
     static const int lat_max = getenv("B200TFHE_LAT_MAX") ? atoi(getenv("B200TFHE_LAT_MAX")) : 2 * 148;
-    const bool lat = !force_tmem && a.batch <= lat_max && br_lat_supported(p);
+    const bool per_ct_key = a.bsk_ct_stride != 0;   // only the generic kernel indexes the key per ciphertext
+    const bool lat = !per_ct_key && !force_tmem && a.batch <= lat_max && br_lat_supported(p);
+    if (per_ct_key) {
+#define X(T, R, K, L, BL, CTS) \
+    if (p.bits == (int)sizeof(T) * 8 && p.N == 2 * R * R && p.k == K && p.pbs_level == L && p.pbs_base_log == BL) \
+        return launch_br<T, R, K, L, BL, CTS>(a, st);
+        BR_INSTANCES(X)
+#undef X
+        return -1;
+    }
     if (!lat && use_ws && br_ws_supported(p)) return br_ws_launch(p, a, st);
     if (!lat && !no_tmem && br_tmem_supported(p)) return br_tmem_launch(p, a, st);
     if (lat) return br_lat_launch(p, a, st);

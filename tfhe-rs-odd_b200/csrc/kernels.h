@@ -39,6 +39,10 @@ struct BRLaunch {
     size_t out_stride;
     int n, batch, mode;
     const void *tw_fwd, *tw_inv;
+    // per-ciphertext keys (vertical packing over circuit-bootstrapped GGSWs): ciphertext ct reads its n GGSWs at
+    // bsk + (ct / bsk_ct_div) * bsk_ct_stride (in complex values); 0 = one key shared by the batch
+    size_t bsk_ct_stride = 0;
+    int bsk_ct_div = 1;
 };
 
 // blind_rotate.cu
@@ -78,6 +82,11 @@ struct KSLaunch {
     int n_in, n_out, level, base_log, bits, batch;
     int body_col = -1;                     // output column that receives the input body; -1: the last one (n_out).  The packing
                                            // keyswitch (LWE -> GLWE) puts it on coefficient 0 of the body polynomial (k*N)
+    // tensor-core path only (private functional packing keyswitch, base_log up to 7 * sub): every reference digit is split
+    // EXACTLY into `sub` balanced sub-digits of sub_bits bits (most significant first) that meet key rows pre-shifted by
+    // 2^(sub_bits * (sub-1-s)), so sum_s d_s * (K << ...) == digit * K mod 2^W and the int8 GEMM stays bit-exact
+    int sub = 1, sub_bits = 0;
+    bool no_body = false;                  // the input body is an ordinary decomposed row (n_in counts it); nothing is added
 };
 int ks_launch(const KSLaunch &a, cudaStream_t st);
 int ks_colsum_launch(const void *ksk, void *colsum, int n_in, int n_out, int level, int base_log, int bits, cudaStream_t st);
@@ -92,6 +101,9 @@ int ks_tc_supported(int bits, int n_in, int n_out, int level, int base_log);
 size_t ks_tc_padded_k(int n_in, int level);
 size_t ks_tc_key_bytes(int bits, int n_in, int n_out, int level);
 int ks_tc_prepare_key(KSTensorKey *tk, const void *ksk, void *planes, int bits, int n_in, int n_out, int level, cudaStream_t st);
+// expanded[i][t*sub + s][j] = src[i][rev ? level-1-t : t][j] << (sub_bits * (sub-1-s)): the key rows the sub-digit split meets
+int ks_expand_rows_launch(const void *src, void *expanded, size_t n_in, int level, int sub, int sub_bits, int rev, size_t width, int bits,
+                          cudaStream_t st);
 int ks_tc_launch(const KSLaunch &a, const KSTensorKey &tk, void *digits, cudaStream_t st);   // digits: batch * kp bytes of scratch
 
 // wave_kernels.cu (device-resident waves over a ciphertext pool); WaveOp is layout-identical to b200tfhe_wave_op
@@ -119,6 +131,11 @@ int pack_rotate_sum_launch(const void *G, void *out, int p, int k, int N, int ba
 int eb_update_shift_launch(void *buffer, const void *pbs, void *shifted, size_t len, int batch, int sh, uint64_t alpha, int bits,
                            cudaStream_t st);
 int eb_store_launch(void *ks, void *out, size_t len, int batch, int nbits, int slot, int add_quarter, int bits, cudaStream_t st);
+// circuit bootstrap glue (wop_pbs/mod.rs:243-444): bootstrap batch [batch][nbits (reversed)][levels] with body + q/4 and the
+// accumulator index per entry; + alpha(level) on the bootstrap outputs; idx[e] = e % mod
+int cbs_prep_launch(const void *bits_in, void *out, uint32_t *lut_idx, size_t len, int batch, int nbits, int levels, int bits, cudaStream_t st);
+int cbs_post_launch(void *pbs, size_t len, size_t entries, int levels, int base_log, int bits, cudaStream_t st);
+int mod_index_launch(uint32_t *idx, size_t total, uint32_t mod, cudaStream_t st);
 
 // misc_kernels.cu
 int modswitch_launch(const void *in, uint32_t *out, size_t count, int log2N, int bits, cudaStream_t st);

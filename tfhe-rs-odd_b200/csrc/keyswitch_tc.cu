@@ -183,14 +183,42 @@ ks_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ 
 // digits[ct][i*level + t] = t-th digit the decomposition emits for input coefficient i (levels l_ks -> 1, the key's row order)
 template <typename T>
 __global__ void ks_digits_kernel(const T *__restrict__ in, size_t in_stride, int8_t *__restrict__ digits, size_t kp, int n_in,
-                                 int level, int base_log, int batch) {
+                                 int level, int base_log, int batch, int sub, int sub_bits) {
     const size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= (size_t)batch * n_in) return;
     const size_t ct = e / n_in;
     const int i = (int)(e % n_in);
     T state = decomp_init_state<T>(in[ct * in_stride + i], base_log, level);
-    int8_t *dst = digits + ct * kp + (size_t)i * level;
-    for (int t = 0; t < level; t++) dst[t] = (int8_t)decomp_next_digit<T>(state, base_log);
+    int8_t *dst = digits + ct * kp + (size_t)i * level * sub;
+    if (sub == 1) {
+        for (int t = 0; t < level; t++) dst[t] = (int8_t)decomp_next_digit<T>(state, base_log);
+        return;
+    }
+    // wide digits (|D| <= 2^(base_log-1), base_log <= 7*sub): D = sum_s d_s * 2^(sub_bits*(sub-1-s)) with the low sub-digits
+    // balanced in [-2^(sub_bits-1), 2^(sub_bits-1)) and the top one taking the rest (|d_0| <= 2^(base_log-1-sub_bits*(sub-1)) + 1)
+    const int half = 1 << (sub_bits - 1), mask = (1 << sub_bits) - 1;
+    for (int t = 0; t < level; t++) {
+        int D = (int)(typename TorusTraits<T>::Signed)decomp_next_digit<T>(state, base_log);
+        for (int s = sub - 1; s >= 1; s--) {
+            const int lo = ((D + half) & mask) - half;
+            dst[t * sub + s] = (int8_t)lo;
+            D = (D - lo) >> sub_bits;
+        }
+        dst[t * sub] = (int8_t)D;
+    }
+}
+
+template <typename T>
+__global__ void ks_expand_rows_kernel(const T *__restrict__ src, T *__restrict__ dst, size_t n_in, int level, int sub, int sub_bits, int rev,
+                                      size_t width) {
+    const size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t rows = n_in * (size_t)level * sub;
+    if (e >= rows * width) return;
+    const size_t row = e / width, j = e % width;
+    const size_t i = row / ((size_t)level * sub);
+    const int ts = (int)(row % ((size_t)level * sub)), t = ts / sub, s = ts % sub;
+    const T v = src[(i * level + (rev ? level - 1 - t : t)) * width + j];
+    dst[e] = (T)(v << (sub_bits * (sub - 1 - s)));
 }
 
 // planes[(j*PL + p)][r] = byte p of KSK[r][j]
@@ -265,9 +293,20 @@ int ks_tc_prepare_key(KSTensorKey *tk, const void *ksk, void *planes, int bits, 
     return make_map(reinterpret_cast<CUtensorMap *>(tk->map_b), planes, (size_t)width * (bits / 8), rows, kp, TC_BN);
 }
 
+int ks_expand_rows_launch(const void *src, void *expanded, size_t n_in, int level, int sub, int sub_bits, int rev, size_t width, int bits,
+                          cudaStream_t st) {
+    const size_t total = n_in * (size_t)level * sub * width;
+    if (total == 0) return 0;
+    const unsigned grid = (unsigned)((total + 255) / 256);
+    if (bits == 64) ks_expand_rows_kernel<uint64_t><<<grid, 256, 0, st>>>((const uint64_t *)src, (uint64_t *)expanded, n_in, level, sub, sub_bits, rev, width);
+    else ks_expand_rows_kernel<uint32_t><<<grid, 256, 0, st>>>((const uint32_t *)src, (uint32_t *)expanded, n_in, level, sub, sub_bits, rev, width);
+    return (int)cudaGetLastError();
+}
+
 int ks_tc_launch(const KSLaunch &a, const KSTensorKey &tk, void *digits, cudaStream_t st) {
     if (a.batch <= 0) return 0;
-    const size_t rows = (size_t)a.n_in * a.level, kp = tk.kp;
+    const size_t rows = (size_t)a.n_in * a.level * a.sub, kp = tk.kp;
+    const int body_col = a.no_body ? a.n_out + 1 : (a.body_col < 0 ? a.n_out : a.body_col);   // n_out + 1: no column matches
     alignas(64) CUtensorMap map_a;
     int rc = make_map(&map_a, digits, (size_t)a.batch, rows, kp, TC_BM);
     if (rc) return rc;
@@ -280,14 +319,14 @@ int ks_tc_launch(const KSLaunch &a, const KSTensorKey &tk, void *digits, cudaStr
     cudaError_t e;
     if (a.bits == 64) {
         if ((e = ensure_dynamic_smem((const void *)ks_tc_kernel<uint64_t>, TC_SMEM)) != cudaSuccess) return (int)e;
-        ks_digits_kernel<uint64_t><<<dgrid, 256, 0, st>>>((const uint64_t *)a.in, a.in_stride, (int8_t *)digits, kp, a.n_in, a.level, a.base_log, a.batch);
+        ks_digits_kernel<uint64_t><<<dgrid, 256, 0, st>>>((const uint64_t *)a.in, a.in_stride, (int8_t *)digits, kp, a.n_in, a.level, a.base_log, a.batch, a.sub, a.sub_bits);
         ks_tc_kernel<uint64_t><<<grid, TC_THREADS, TC_SMEM, st>>>(map_a, map_b, (const uint64_t *)a.in, a.in_stride, (uint64_t *)a.out,
-                                                                 a.out_stride, a.n_in, a.n_out, k_blocks, a.batch, a.body_col < 0 ? a.n_out : a.body_col);
+                                                                 a.out_stride, a.n_in, a.n_out, k_blocks, a.batch, body_col);
     } else {
         if ((e = ensure_dynamic_smem((const void *)ks_tc_kernel<uint32_t>, TC_SMEM)) != cudaSuccess) return (int)e;
-        ks_digits_kernel<uint32_t><<<dgrid, 256, 0, st>>>((const uint32_t *)a.in, a.in_stride, (int8_t *)digits, kp, a.n_in, a.level, a.base_log, a.batch);
+        ks_digits_kernel<uint32_t><<<dgrid, 256, 0, st>>>((const uint32_t *)a.in, a.in_stride, (int8_t *)digits, kp, a.n_in, a.level, a.base_log, a.batch, a.sub, a.sub_bits);
         ks_tc_kernel<uint32_t><<<grid, TC_THREADS, TC_SMEM, st>>>(map_a, map_b, (const uint32_t *)a.in, a.in_stride, (uint32_t *)a.out,
-                                                                 a.out_stride, a.n_in, a.n_out, k_blocks, a.batch, a.body_col < 0 ? a.n_out : a.body_col);
+                                                                 a.out_stride, a.n_in, a.n_out, k_blocks, a.batch, body_col);
     }
     return (int)cudaGetLastError();
 }
