@@ -234,7 +234,7 @@ def test_gpu_pfpks_bit_exact(ctx):
 @pytest.mark.gpu
 @pytest.mark.parametrize("name,B", [("TOY_WOP", 16), ("WOPBS_MESSAGE_2_CARRY_2", 8)])
 def test_gpu_wopbs_extract_then_circuit_bootstrap_vertical_packing(ctx, name, B):
-    """The whole WoP-PBS of a 4-bit message (shortint/wopbs/mod.rs:575-680): extract_bits, then circuit bootstrap + vertical
+    """The whole WoP-PBS of a 4-bit message (shortint/wopbs/mod.rs:547-830): extract_bits, then circuit bootstrap + vertical
     packing with two look-up tables.  Every message decrypts to table[message]; the oracle runs the first ciphertexts."""
     o = get_oracle(name)
     t, bsk, ksk, pf, wop = _wop_keys(ctx, o, name)

@@ -1,5 +1,5 @@
-// wopbs_kernels.cu -- the integer steps between the keyswitch and the bootstrap of every round of the bit extraction
-// (first half of the WoP-PBS).
+// wopbs_kernels.cu -- the element-wise integer steps of the WoP-PBS: between the keyswitch and the bootstrap of
+// every round of the bit extraction, and around the bootstraps of the circuit bootstrap (further down).
 //
 // Reference: extract_bits, tfhe/src/core_crypto/fft_impl/fft64/crypto/wop_pbs/mod.rs:66-225 (public wrapper
 // extract_bits_from_lwe_ciphertext_mem_optimized, core_crypto/algorithms/lwe_wopbs.rs:321-364).  Round `bit_idx` (from the
