@@ -234,14 +234,16 @@ int b200tfhe_pfpks_batch_u64(b200tfhe_context *ctx, const b200tfhe_pfpksk *pf, u
                              uint32_t batch);
 /* circuit_bootstrap_boolean_vertical_packing_lwe_ciphertext_list_mem_optimized (lwe_wopbs.rs:651-704 ->
  * fft64/crypto/wop_pbs/mod.rs:647-853) over a batch.  bits_in: batch x nbits x (n+1), the output of extract_bits (most
- * significant bit first, each scaled by q/2); luts: n_luts x N, ONE polynomial per look-up table (nbits <= log2 N; the CMUX tree
- * that multi-polynomial tables need, :468-592, is not built); out: batch x n_luts x (kN+1) under the big key, out[b][o] encrypts
- * luts[o][index of the bits of b].  Per input: nbits * cbs_level bootstraps (homomorphic_shift_boolean :369-444),
- * (k+1) private functional packing keyswitches each, Fourier conversion of the GGSWs, and n_luts blind rotations over the
- * ciphertext's own GGSW list (:866-892) with sample extraction. */
+ * significant bit first, each scaled by q/2); luts: n_luts x polys_per_lut x N (big_lut_as_polynomial_list; polys_per_lut = 2^t,
+ * t <= nbits, nbits - t <= log2 N); out: batch x n_luts x (kN+1) under the big key, out[b][o] encrypts coefficient `index` of
+ * table o, index = the nbits bits of b read as a number (polynomial index = its t most significant bits).
+ * Per input: nbits * cbs_level bootstraps (homomorphic_shift_boolean :369-444), (k+1) private functional packing
+ * keyswitches each, Fourier conversion of the GGSWs; per (input, table): the CMUX tree over the table's polynomials
+ * (cmux_tree_memory_optimized :468-592, one launch per layer) and a blind rotation over the input's own remaining GGSWs
+ * (:866-892) with sample extraction. */
 int b200tfhe_cbs_vertical_packing_batch_u64(b200tfhe_context *ctx, const b200tfhe_bsk *bsk, const b200tfhe_pfpksk *pf, const uint64_t *bits_in,
-                                            uint32_t nbits, const uint64_t *luts, uint32_t n_luts, uint32_t cbs_base_log, uint32_t cbs_level,
-                                            uint64_t *out, uint32_t batch);
+                                            uint32_t nbits, const uint64_t *luts, uint32_t n_luts, uint32_t polys_per_lut,
+                                            uint32_t cbs_base_log, uint32_t cbs_level, uint64_t *out, uint32_t batch);
 
 /* ---- device-resident waves over a ciphertext pool ---------------------------------------------
  * The reference evaluates a shortint / integer / Trivium circuit as rayon-parallel layers of

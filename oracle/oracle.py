@@ -308,14 +308,14 @@ class Oracle:
         lib().orc_circuit_bootstrap_boolean(C.byref(self.p), _p(self.fbsk), _p(pfpksk_list), pb, pl, cb, cl, _p(u64(bit_ct)), int(delta_log), _p(out))
         return out
 
-    def cbs_vertical_packing(self, pfpksk_list, wop, bits_in, luts):
-        """bits_in [B][nbits][n+1] (MSB first, q/2-scaled), luts [n_out][N] -> [B][n_out][kN+1]."""
+    def cbs_vertical_packing(self, pfpksk_list, wop, bits_in, luts, polys_per_lut=1):
+        """bits_in [B][nbits][n+1] (MSB first, q/2-scaled), luts [n_out][polys_per_lut][N] -> [B][n_out][kN+1]."""
         pb, pl, cb, cl = wop
         bits_in = u64(bits_in)
         bits_in = bits_in.reshape(-1, bits_in.shape[-2], self.n + 1)
-        luts = u64(luts).reshape(-1, self.N)
+        luts = u64(luts).reshape(-1, int(polys_per_lut), self.N)
         out = np.zeros((bits_in.shape[0], luts.shape[0], self.big + 1), np.uint64)
         for b in range(bits_in.shape[0]):
-            lib().orc_cbs_vertical_packing(C.byref(self.p), _p(self.fbsk), _p(pfpksk_list), pb, pl, cb, cl, _p(bits_in[b]),
-                                           bits_in.shape[1], _p(luts), luts.shape[0], _p(out[b]))
+            lib().orc_cbs_vertical_packing_tree(C.byref(self.p), _p(self.fbsk), _p(pfpksk_list), pb, pl, cb, cl, _p(bits_in[b]),
+                                                bits_in.shape[1], _p(luts), luts.shape[0], int(polys_per_lut), _p(out[b]))
         return out

@@ -73,14 +73,39 @@ void orc_circuit_bootstrap_boolean(const orc_params *p, const double *fbsk, cons
     free(shifted); free(bs); free(acc);
 }
 
-/* :647-746 (circuit_bootstrap_boolean_vertical_packing) for look-up tables of ONE polynomial each (log_lut_number = 0: no CMUX
- * tree, :812-825), :866-892 (blind_rotate_assign over the GGSW list), ggsw.rs:766-777 (cmux), then sample extraction (:852).
- * bits_in: [nbits][n+1] (most significant bit first, each scaled by q/2); luts: [n_out][N]; out: [n_out][kN+1]. */
-void orc_cbs_vertical_packing(const orc_params *p, const double *fbsk, const uint64_t *pfpksk_list, int pf_base_log, int pf_level,
-                              int cbs_base_log, int cbs_level, const uint64_t *bits_in, int nbits, const uint64_t *luts, int n_out,
-                              uint64_t *out) {
+/* :468-592 (cmux_tree_memory_optimized): binary tree of CMUXes over the 2^t polynomials of one look-up table.  The reference walks
+ * it depth-first with O(t) buffers; the operations and their operands are those of the plain layer-by-layer tree written here:
+ * layer j pairs consecutive nodes, node = t0 + ggsw (x) (t1 - t0) with the j-th GGSW from the END of the list (:541).
+ * fggsw: t Fourier GGSWs (most significant first); lut: [2^t][N]; out: GLWE. */
+static void cmux_tree(const orc_params *pc, const double *fggsw, size_t ggsw_len, int t, const uint64_t *lut, uint64_t *out) {
+    const int N = pc->N, k = pc->k;
+    const uint64_t m = pc->bits == 64 ? ~0ULL : ((1ULL << pc->bits) - 1);
+    const size_t glwe = (size_t)(k + 1) * N;
+    size_t count = (size_t)1 << t;
+    uint64_t *nodes = (uint64_t *)calloc(count * glwe, sizeof(uint64_t)), *diff = (uint64_t *)malloc(sizeof(uint64_t) * glwe);
+    for (size_t q = 0; q < count; q++) memcpy(nodes + q * glwe + (size_t)k * N, lut + q * N, sizeof(uint64_t) * N);   /* :531-537 */
+    for (int j = 0; j < t; j++) {
+        const double *g = fggsw + (size_t)(t - 1 - j) * ggsw_len;
+        for (size_t q = 0; q < count / 2; q++) {
+            uint64_t *t0 = nodes + 2 * q * glwe, *t1 = t0 + glwe;
+            for (size_t c = 0; c < glwe; c++) diff[c] = (t1[c] - t0[c]) & m;                                        /* :543-546 */
+            orc_add_external_product(pc, t0, g, diff);                                                               /* :566-567 */
+            if (q) memcpy(nodes + q * glwe, t0, sizeof(uint64_t) * glwe);
+        }
+        count /= 2;
+    }
+    memcpy(out, nodes, sizeof(uint64_t) * glwe);
+    free(nodes); free(diff);
+}
+
+/* :647-746 (circuit_bootstrap_boolean_vertical_packing), :785-853 (vertical_packing: CMUX tree over the polys_per_lut = 2^t
+ * polynomials of a table with the t most significant GGSWs, then blind rotation with the others),
+ * :866-892 (blind_rotate_assign over the GGSW list), ggsw.rs:766-777 (cmux), then sample extraction (:852).
+ * bits_in: [nbits][n+1] (most significant bit first, each scaled by q/2); luts: [n_out][polys_per_lut][N]; out: [n_out][kN+1]. */
+void orc_cbs_vertical_packing_tree(const orc_params *p, const double *fbsk, const uint64_t *pfpksk_list, int pf_base_log, int pf_level,
+                                   int cbs_base_log, int cbs_level, const uint64_t *bits_in, int nbits, const uint64_t *luts, int n_out,
+                                   int polys_per_lut, uint64_t *out) {
     const int W = p->bits, N = p->N, k = p->k, k1 = k + 1;
-    const uint64_t m = W == 64 ? ~0ULL : ((1ULL << W) - 1);
     const size_t glwe = (size_t)k1 * N, ggsw_len = (size_t)cbs_level * k1 * glwe;
     uint64_t *ggsw_res = (uint64_t *)malloc(sizeof(uint64_t) * ggsw_len);
     double *fggsw = (double *)malloc(sizeof(double) * ggsw_len * (size_t)nbits);
@@ -92,12 +117,15 @@ void orc_cbs_vertical_packing(const orc_params *p, const double *fbsk, const uin
     orc_params pc = *p;
     pc.pbs_level = cbs_level;
     pc.pbs_base_log = cbs_base_log;
+    int t = 0;                                                                            /* log_lut_number (:812-821) */
+    while ((1 << (t + 1)) <= polys_per_lut) t++;
+    if (t > nbits) t = 0;
+    const uint64_t m = W == 64 ? ~0ULL : ((1ULL << W) - 1);
     uint64_t *acc = (uint64_t *)malloc(sizeof(uint64_t) * glwe), *ct1 = (uint64_t *)malloc(sizeof(uint64_t) * glwe);
     for (int o = 0; o < n_out; o++) {                                                     /* :740-745 */
-        memset(acc, 0, sizeof(uint64_t) * glwe);
-        for (int c = 0; c < N; c++) acc[(size_t)k * N + c] = luts[(size_t)o * N + c] & m;
+        cmux_tree(&pc, fggsw, ggsw_len, t, luts + (size_t)o * polys_per_lut * N, acc);    /* :837-843 */
         uint64_t deg = 1;
-        for (int i = nbits - 1; i >= 0; i--) {                                            /* ggsw_list.into_ggsw_iter().rev() (:874) */
+        for (int i = nbits - 1; i >= t; i--) {                                            /* br_ggsw.into_ggsw_iter().rev() (:874) */
             for (int j = 0; j < k1; j++) orc_monomial_div(ct1 + (size_t)j * N, acc + (size_t)j * N, N, deg, W);
             deg <<= 1;
             for (size_t c = 0; c < glwe; c++) ct1[c] = (ct1[c] - acc[c]) & m;             /* cmux: ct1 -= ct0 */
@@ -106,4 +134,10 @@ void orc_cbs_vertical_packing(const orc_params *p, const double *fbsk, const uin
         orc_sample_extract0(out + (size_t)o * ((size_t)k * N + 1), acc, k, N, W);
     }
     free(ggsw_res); free(fggsw); free(acc); free(ct1);
+}
+
+void orc_cbs_vertical_packing(const orc_params *p, const double *fbsk, const uint64_t *pfpksk_list, int pf_base_log, int pf_level,
+                              int cbs_base_log, int cbs_level, const uint64_t *bits_in, int nbits, const uint64_t *luts, int n_out,
+                              uint64_t *out) {
+    orc_cbs_vertical_packing_tree(p, fbsk, pfpksk_list, pf_base_log, pf_level, cbs_base_log, cbs_level, bits_in, nbits, luts, n_out, 1, out);
 }

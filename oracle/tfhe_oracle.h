@@ -110,6 +110,10 @@ void orc_circuit_bootstrap_boolean(const orc_params *p, const double *fbsk, cons
 void orc_cbs_vertical_packing(const orc_params *p, const double *fbsk, const uint64_t *pfpksk_list, int pf_base_log, int pf_level,
                               int cbs_base_log, int cbs_level, const uint64_t *bits_in, int nbits, const uint64_t *luts, int n_out,
                               uint64_t *out);
+/* the same with tables of polys_per_lut = 2^t polynomials: CMUX tree (:468-592) over the t most significant bits first */
+void orc_cbs_vertical_packing_tree(const orc_params *p, const double *fbsk, const uint64_t *pfpksk_list, int pf_base_log, int pf_level,
+                                   int cbs_base_log, int cbs_level, const uint64_t *bits_in, int nbits, const uint64_t *luts, int n_out,
+                                   int polys_per_lut, uint64_t *out);
 /* generate_circuit_bootstrap_lwe_pfpksk_list, algorithms/lwe_wopbs.rs:80-160 ; out [k+1][kN+1][level 1..L][(k+1)N] */
 void orc_gen_cbs_pfpksk_list(const orc_params *p, int base_log, int level, const uint64_t *glwe_key, uint64_t seed, uint64_t *out,
                              int nthreads);

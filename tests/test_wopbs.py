@@ -259,8 +259,55 @@ def test_gpu_wopbs_extract_then_circuit_bootstrap_vertical_packing(ctx, name, B)
     one = t.core_crypto.circuit_bootstrap_boolean_vertical_packing_lwe_ciphertext_list_mem_optimized(bits[3], luts[1], bsk, pf, wop[2], wop[3])
     d1, _ = _decode4(o, one)
     assert one.shape == (1, o.big + 1) and d1[0] == 15 - int(msgs[3])
-    with pytest.raises(t.B200TfheError, match="log2"):
+    with pytest.raises(t.B200TfheError, match="too small"):
         big = np.zeros((1, 12, o.n + 1), np.uint64)
         t.core_crypto.circuit_bootstrap_boolean_vertical_packing_lwe_ciphertext_list_mem_optimized(big, luts, bsk, pf, wop[2], wop[3])
+    with pytest.raises(t.B200TfheError, match="power of two"):
+        t.core_crypto.circuit_bootstrap_boolean_vertical_packing_lwe_ciphertext_list_mem_optimized(
+            bits, np.zeros((3, o.N), np.uint64), bsk, pf, wop[2], wop[3], number_of_luts=1)
     with pytest.raises(t.B200TfheError, match="no blind-rotation instance"):
         t.core_crypto.circuit_bootstrap_boolean_vertical_packing_lwe_ciphertext_list_mem_optimized(bits, luts, bsk, pf, 4, 3)
+
+
+def test_oracle_cmux_tree_tables_of_several_polynomials():
+    """13 input bits, tables of 4 polynomials: 2 tree layers then 11 rotation steps (wop_pbs/mod.rs:812-853)."""
+    o = get_oracle("TOY_WOP")
+    wop = _wop("TOY_WOP")
+    nb = 13
+    msgs = np.array([5, 4097, 8191, 0, 6000], dtype=np.uint64)
+    bits = o.extract_bits(o.encrypt(msgs << np.uint64(64 - nb), under="big", seed=89), 64 - nb, nb)
+    idx = np.arange(1 << nb, dtype=np.uint64)
+    f = (idx * idx + idx // np.uint64(7) + np.uint64(3)) % np.uint64(16)
+    out = o.cbs_vertical_packing(_pfpksk(o, "TOY_WOP"), wop, bits, (f << np.uint64(60)).reshape(4, o.N), 4)
+    dec, _ = _decode4(o, out)
+    assert np.array_equal(dec[:, 0], f[msgs].astype(int))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nbits,polys", [(12, 2), (13, 4), (3, 4)])
+def test_gpu_vertical_packing_cmux_tree(ctx, nbits, polys):
+    """Tables of several polynomials: the CMUX tree (wop_pbs/mod.rs:468-592) over the most significant bits, then the blind
+    rotation over the others.  (3, 4): two tree layers and a single rotation step."""
+    o = get_oracle("TOY_WOP")
+    t, bsk, ksk, pf, wop = _wop_keys(ctx, o, "TOY_WOP")
+    rng = np.random.default_rng(79 + nbits)
+    msgs = rng.integers(0, 1 << nbits, 6, dtype=np.uint64)
+    msgs[0], msgs[1] = 0, (1 << nbits) - 1
+    cts = o.encrypt(msgs << np.uint64(64 - nbits), under="big", seed=83)
+    bits = t.core_crypto.extract_bits_from_lwe_ciphertext_mem_optimized(cts, bsk, ksk, 64 - nbits, nbits)
+    idx = np.arange(polys * o.N, dtype=np.uint64)
+    f = [(idx * idx + idx // np.uint64(7) + np.uint64(3)) % np.uint64(16), (idx ^ (idx >> np.uint64(3))) % np.uint64(16)]
+    luts = np.stack([(v << np.uint64(60)).astype(np.uint64) for v in f]).reshape(2 * polys, o.N)
+    out = t.core_crypto.circuit_bootstrap_boolean_vertical_packing_lwe_ciphertext_list_mem_optimized(bits, luts, bsk, pf, wop[2], wop[3], number_of_luts=2)
+    dec, ph = _decode4(o, out)
+    # the nbits input bits address coefficient `msg` of a table of 2^nbits entries laid out over polys * N coefficients:
+    # polynomial index = the log2(polys) most significant bits, rotation = the others
+    n_br = nbits - int(np.log2(polys))
+    pos = ((msgs >> np.uint64(n_br)) * np.uint64(o.N) + (msgs & np.uint64((1 << n_br) - 1))).astype(np.int64)
+    assert np.array_equal(dec[:, 0], f[0][pos].astype(int)) and np.array_equal(dec[:, 1], f[1][pos].astype(int))
+    ref = o.cbs_vertical_packing(_pfpksk(o, "TOY_WOP"), wop, bits[:2], luts, polys)
+    dref, phr = _decode4(o, ref)
+    assert np.array_equal(dref, dec[:2])
+    err = np.abs((ph - (dec.astype(np.uint64) << np.uint64(60))).astype(np.int64)) / 2.0 ** 64
+    eref = np.abs((phr - (dref.astype(np.uint64) << np.uint64(60))).astype(np.int64)) / 2.0 ** 64
+    assert err.max() < max(8 * eref.max(), 2.0 ** -9) < 1 / 64

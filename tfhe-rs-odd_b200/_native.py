@@ -71,7 +71,7 @@ _PROTOS = {
     "b200tfhe_cbs_pfpksk_upload_u64": [_VP, C.POINTER(Params), _U32, _U32, _VP, _PP],
     "b200tfhe_cbs_pfpksk_destroy": [_VP],
     "b200tfhe_pfpks_batch_u64": [_VP, _VP, _U32, _VP, _VP, _U32],
-    "b200tfhe_cbs_vertical_packing_batch_u64": [_VP, _VP, _VP, _VP, _U32, _VP, _U32, _U32, _U32, _VP, _U32],
+    "b200tfhe_cbs_vertical_packing_batch_u64": [_VP, _VP, _VP, _VP, _U32, _VP, _U32, _U32, _U32, _U32, _VP, _U32],
     "b200tfhe_wave_run": [_VP, _VP, _VP, _VP, _VP, _U32, _U32],
 }
 for _s in ("u64", "u32"):

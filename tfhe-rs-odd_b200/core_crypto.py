@@ -429,8 +429,9 @@ def circuit_bootstrap_boolean_vertical_packing_lwe_ciphertext_list_mem_optimized
                                                                                  pfpksk_list, base_log_cbs, level_cbs,
                                                                                  number_of_luts=None, lwe_list_out=None):
     """algorithms/lwe_wopbs.rs:651-704 -> fft64/crypto/wop_pbs/mod.rs:647-853.  lwe_list_in: [nbits][n+1] or [B][nbits][n+1]
-    (extract_bits output); big_lut_as_polynomial_list: [number_of_luts][N] (one polynomial per table; the reference deduces
-    number_of_luts from lwe_list_out, :736); result [number_of_luts][kN+1] per input."""
+    (extract_bits output); big_lut_as_polynomial_list: [number_of_luts * polys_per_lut][N]; the reference deduces
+    number_of_luts from lwe_list_out (:736) -- here it is an argument (default: one polynomial per table); result
+    [number_of_luts][kN+1] per input."""
     p, ctx = fourier_bsk.params, fourier_bsk.ctx
     if p.torus_bits != 64:
         raise B200TfheError("circuit bootstrap: 64-bit torus only")
@@ -440,11 +441,12 @@ def circuit_bootstrap_boolean_vertical_packing_lwe_ciphertext_list_mem_optimized
     single = a.ndim == 2
     a = a.reshape(-1, a.shape[-2], a.shape[-1])
     luts = np.ascontiguousarray(big_lut_as_polynomial_list, dtype=np.uint64).reshape(-1, p.polynomial_size)
-    if number_of_luts is not None and luts.shape[0] != int(number_of_luts):
-        raise B200TfheError("circuit bootstrap: look-up tables of more than one polynomial need the CMUX tree, which is not built")
-    out = np.zeros((a.shape[0], luts.shape[0], p.glwe_dimension * p.polynomial_size + 1), np.uint64)
-    ctx.check(ctx._lib.b200tfhe_cbs_vertical_packing_batch_u64(ctx._h, fourier_bsk._h, pfpksk_list._h, _ptr(a), a.shape[1], _ptr(luts),
-                                                               luts.shape[0], int(base_log_cbs), int(level_cbs), _ptr(out), a.shape[0]))
+    n_luts = luts.shape[0] if number_of_luts is None else int(number_of_luts)
+    if n_luts < 1 or luts.shape[0] % n_luts:
+        raise B200TfheError("circuit bootstrap: the polynomial list does not split into number_of_luts tables")   # chunks_exact (:741)
+    out = np.zeros((a.shape[0], n_luts, p.glwe_dimension * p.polynomial_size + 1), np.uint64)
+    ctx.check(ctx._lib.b200tfhe_cbs_vertical_packing_batch_u64(ctx._h, fourier_bsk._h, pfpksk_list._h, _ptr(a), a.shape[1], _ptr(luts), n_luts,
+                                                               luts.shape[0] // n_luts, int(base_log_cbs), int(level_cbs), _ptr(out), a.shape[0]))
     res = out[0] if single else out
     if lwe_list_out is not None:
         np.copyto(lwe_list_out, res)

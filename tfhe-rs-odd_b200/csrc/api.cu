@@ -1006,10 +1006,10 @@ int b200tfhe_pfpks_batch_u64(b200tfhe_context *ctx, const b200tfhe_pfpksk *pf, u
     return 0;
 }
 
-// circuit_bootstrap_boolean_vertical_packing (wop_pbs/mod.rs:647-853) over a batch, look-up tables of one polynomial each.
+// circuit_bootstrap_boolean_vertical_packing (wop_pbs/mod.rs:647-853) over a batch.
 int b200tfhe_cbs_vertical_packing_batch_u64(b200tfhe_context *ctx, const b200tfhe_bsk *bsk, const b200tfhe_pfpksk *pf, const uint64_t *bits_in,
-                                            uint32_t nbits, const uint64_t *luts, uint32_t n_luts, uint32_t cbs_base_log, uint32_t cbs_level,
-                                            uint64_t *out, uint32_t batch) {
+                                            uint32_t nbits, const uint64_t *luts, uint32_t n_luts, uint32_t polys_per_lut,
+                                            uint32_t cbs_base_log, uint32_t cbs_level, uint64_t *out, uint32_t batch) {
     REQUIRE(ctx && bsk && pf, "cbs_vertical_packing: null argument");
     REQUIRE(bsk->ctx == ctx && pf->ctx == ctx, "key handle belongs to another context");
     const Params &p = bsk->p;
@@ -1020,12 +1020,20 @@ int b200tfhe_cbs_vertical_packing_batch_u64(b200tfhe_context *ctx, const b200tfh
     REQUIRE(nbits >= 1, "cbs_vertical_packing: empty lwe_list_in");   // :672-675
     int log2N = 0;
     while ((1 << log2N) < p.N) log2N++;
-    REQUIRE((int)nbits <= log2N, "cbs_vertical_packing: more input bits than log2(N); the CMUX tree for multi-polynomial tables is not built");
+    // cmux_tree_memory_optimized asserts polynomial_count == 2^(number of its GGSWs) (:475); vertical_packing gives it the
+    // log2(polynomial_count) most significant bits and the blind rotation the others (:812-825)
+    REQUIRE(polys_per_lut >= 1 && (polys_per_lut & (polys_per_lut - 1)) == 0, "cbs_vertical_packing: polynomials per table must be a power of two");
+    int tree = 0;
+    while ((1u << tree) < polys_per_lut) tree++;
+    REQUIRE(tree <= (int)nbits, "cbs_vertical_packing: more table polynomials than 2^nbits");
+    const int n_br = (int)nbits - tree;
+    REQUIRE(n_br <= log2N, "cbs_vertical_packing: the table is too small for the input bits (nbits - log2(polynomials per table) > log2 N)");
     Params pc = p;
     pc.pbs_level = (int)cbs_level;
     pc.pbs_base_log = (int)cbs_base_log;
     const int Rc = br_supported(pc);
     REQUIRE(Rc != 0 && Rc != 256, "cbs_vertical_packing: no blind-rotation instance for (N, k, cbs_level, cbs_base_log)");
+    REQUIRE(tree == 0 || cmux_layer_supported(pc), "cbs_vertical_packing: no CMUX-tree instance for (N, k, cbs_level, cbs_base_log)");
     if (batch == 0 || n_luts == 0) return 0;
     REQUIRE(bits_in && luts && out, "cbs_vertical_packing: null buffer");
     std::lock_guard<std::mutex> g(ctx->mu);
@@ -1038,25 +1046,36 @@ int b200tfhe_cbs_vertical_packing_batch_u64(b200tfhe_context *ctx, const b200tfh
     CK(ctx->ws.get(Workspace::IN, (size_t)batch * nbits * slen * 8, &d_bits));
     CK(ctx->ws.get(Workspace::A, entries * slen * 8, &d_prep));
     CK(ctx->ws.get(Workspace::IDX, (entries + n_vp) * 4, &d_idx));
-    CK(ctx->ws.get(Workspace::LUTS, ((size_t)cbs_level + n_luts) * glen * 8 + (nbits + 1) * 8, &d_luts));
+    const size_t n_direct = tree ? 0 : n_luts;                            // tables handed to the blind rotation as they are
+    CK(ctx->ws.get(Workspace::LUTS, ((size_t)cbs_level + n_direct) * glen * 8 + (nbits + 1) * 8, &d_luts));
     CK(ctx->ws.get(Workspace::MID, entries * blen * 8, &d_pbs));
     CK(ctx->ws.get(Workspace::B, entries * ggsw_words * 8, &d_ggsw));
     CK(ctx->ws.get(Workspace::C, entries * ggsw_words * 8, &d_fggsw));
     CK(ctx->ws.get(Workspace::OUT, n_vp * blen * 8, &d_out));
     uint32_t *d_idx_vp = (uint32_t *)d_idx + entries;
-    uint64_t *d_luts_vp = (uint64_t *)d_luts + (size_t)cbs_level * glen, *d_fake = d_luts_vp + (size_t)n_luts * glen;
+    uint64_t *d_luts_vp = (uint64_t *)d_luts + (size_t)cbs_level * glen, *d_fake = d_luts_vp + n_direct * glen;
     // host tables: accumulators -2^(63 - b*level) (:423-427), the tables as trivial GLWEs, and the rotation amounts of
     // blind_rotate_assign (:872-890): step i divides by X^(2^i), i.e. a mask element whose modulus switch is 2N - 2^i, body 0
-    std::vector<uint64_t> h(((size_t)cbs_level + n_luts) * glen + nbits + 1, 0);
+    std::vector<uint64_t> h(((size_t)cbs_level + n_direct) * glen + nbits + 1, 0);
     for (uint32_t l = 0; l < cbs_level; l++)
         for (int c = 0; c < p.N; c++) h[(size_t)l * glen + (size_t)p.k * p.N + c] = 0 - (1ULL << (63 - cbs_base_log * (l + 1)));
-    for (uint32_t o = 0; o < n_luts; o++)
-        memcpy(&h[((size_t)cbs_level + o) * glen + (size_t)p.k * p.N], luts + (size_t)o * p.N, (size_t)p.N * 8);
-    for (uint32_t i = 0; i < nbits; i++) h[((size_t)cbs_level + n_luts) * glen + i] = (uint64_t)(2 * p.N - (1 << i)) << (64 - log2N - 1);
+    for (size_t o = 0; o < n_direct; o++)
+        memcpy(&h[((size_t)cbs_level + o) * glen + (size_t)p.k * p.N], luts + o * p.N, (size_t)p.N * 8);
+    for (int i = 0; i < n_br; i++) h[((size_t)cbs_level + n_direct) * glen + i] = (uint64_t)(2 * p.N - (1 << i)) << (64 - log2N - 1);
     CK(cudaMemcpyAsync(d_luts, h.data(), h.size() * 8, cudaMemcpyHostToDevice, ctx->stream));
+    std::vector<uint64_t> h_tab;                                          // CMUX tree leaves: every table polynomial as a trivial GLWE
+    void *d_tab = nullptr;
+    if (tree) {
+        const size_t n_poly = (size_t)n_luts * polys_per_lut;
+        h_tab.assign(n_poly * glen, 0);
+        for (size_t q = 0; q < n_poly; q++) memcpy(&h_tab[q * glen + (size_t)p.k * p.N], luts + q * p.N, (size_t)p.N * 8);
+        CK(ctx->ws.get(Workspace::D, h_tab.size() * 8, &d_tab));
+        CK(cudaMemcpyAsync(d_tab, h_tab.data(), h_tab.size() * 8, cudaMemcpyHostToDevice, ctx->stream));
+    }
     CK(cudaMemcpyAsync(d_bits, bits_in, (size_t)batch * nbits * slen * 8, cudaMemcpyHostToDevice, ctx->stream));
     int rc = cbs_prep_launch(d_bits, d_prep, (uint32_t *)d_idx, slen, (int)batch, (int)nbits, (int)cbs_level, 64, ctx->stream);
-    if (!rc) rc = mod_index_launch(d_idx_vp, n_vp, n_luts, ctx->stream);
+    // accumulator of rotation e: table e % n_luts as it is, or node e of the last tree layer
+    if (!rc) rc = mod_index_launch(d_idx_vp, n_vp, tree ? (uint32_t)n_vp : n_luts, ctx->stream);
     ctx->launches += 2;
     if (rc) return fail(ctx, "cbs prep launch failed: " + std::to_string(rc));
     // homomorphic_shift_boolean for every (bit, level) in one bootstrap batch
@@ -1071,9 +1090,30 @@ int b200tfhe_cbs_vertical_packing_batch_u64(b200tfhe_context *ctx, const b200tfh
     rc = bsk_convert_polys_launch(Rc, 64, entries * (p.k + 1) * (p.k + 1), d_ggsw, d_fggsw, tw_fwd(ctx, Rc), ctx->stream);
     ctx->launches++;
     if (rc) return fail(ctx, "ggsw conversion launch failed: " + std::to_string(rc));
-    // vertical_packing with log_lut_number = 0 (:812-853): blind rotation over the ciphertext's own GGSW list + sample extraction
-    BRLaunch a{d_fake, 0, d_luts_vp, d_idx_vp, d_fggsw, d_out, blen, (int)nbits, (int)n_vp, BR_MODE_LWE, tw_fwd(ctx, Rc), tw_inv(ctx, Rc)};
-    a.bsk_ct_stride = (size_t)nbits * cbs_level * (p.k + 1) * (p.k + 1) * (p.N / 2);
+    const size_t ggsw_cplx = (size_t)cbs_level * (p.k + 1) * (p.k + 1) * (p.N / 2), key_stride = (size_t)nbits * ggsw_cplx;
+    // cmux_tree_memory_optimized (:468-592), a layer per launch: layer j pairs consecutive nodes with the j-th GGSW from the end of
+    // the tree's sub-list = entry n_br + j of the reversed list built in step 1
+    const void *d_acc = d_luts_vp;
+    if (tree) {
+        // the conversion above was the last reader of the standard-domain GGSWs and of the bootstrap inputs: their slots ping-pong
+        void *d_layer[2];
+        const size_t layer_bytes = n_vp * (polys_per_lut / 2) * glen * 8;
+        CK(ctx->ws.get(Workspace::A, layer_bytes, &d_layer[0]));
+        CK(ctx->ws.get(Workspace::B, layer_bytes, &d_layer[1]));
+        const void *src = d_tab;
+        for (int j = 0; j < tree; j++) {
+            const int pairs = (int)(polys_per_lut >> (j + 1));
+            rc = cmux_layer_launch(pc, src, j ? (size_t)n_luts * pairs * 2 : 0, d_layer[j & 1], (const cplx *)d_fggsw + (size_t)(n_br + j) * ggsw_cplx,
+                                   key_stride, (int)n_luts, pairs, n_vp * pairs, tw_fwd(ctx, Rc), tw_inv(ctx, Rc), ctx->stream);
+            ctx->launches++;
+            if (rc) return fail(ctx, "cmux tree launch failed: " + std::to_string(rc));
+            src = d_layer[j & 1];
+        }
+        d_acc = src;
+    }
+    // vertical_packing (:812-853): blind rotation over the ciphertext's own remaining GGSWs + sample extraction
+    BRLaunch a{d_fake, 0, d_acc, d_idx_vp, d_fggsw, d_out, blen, n_br, (int)n_vp, BR_MODE_LWE, tw_fwd(ctx, Rc), tw_inv(ctx, Rc)};
+    a.bsk_ct_stride = key_stride;
     a.bsk_ct_div = (int)n_luts;
     rc = br_launch(pc, a, ctx->stream);
     ctx->launches++;

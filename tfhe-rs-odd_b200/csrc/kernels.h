@@ -137,6 +137,11 @@ int cbs_prep_launch(const void *bits_in, void *out, uint32_t *lut_idx, size_t le
 int cbs_post_launch(void *pbs, size_t len, size_t entries, int levels, int base_log, int bits, cudaStream_t st);
 int mod_index_launch(uint32_t *idx, size_t total, uint32_t mod, cudaStream_t st);
 
+// cmux_tree.cu (one layer of the vertical packing's CMUX tree: wop_pbs/mod.rs:468-592); pc carries (cbs_level, cbs_base_log)
+int cmux_layer_supported(const Params &pc);
+int cmux_layer_launch(const Params &pc, const void *in, size_t ct_in_stride, void *out, const void *ggsw, size_t key_stride, int n_luts,
+                      int pairs, size_t n_cmux, const void *tw_fwd, const void *tw_inv, cudaStream_t st);
+
 // misc_kernels.cu
 int modswitch_launch(const void *in, uint32_t *out, size_t count, int log2N, int bits, cudaStream_t st);
 int sample_extract_launch(const void *glwe, void *lwe, int k, int N, int batch, int bits, cudaStream_t st);
