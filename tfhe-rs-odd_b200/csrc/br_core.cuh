@@ -59,12 +59,14 @@ template <typename T, int R, int K, int L, int BASE_LOG> struct BRCore {
             // several levels: the decomposition states of this lane's 2R coefficients stay in registers and ONE rolled loop
             // emits a level's digits and transforms them, so the instruction stream holds a single copy of the radix-R FFT
             // (the unrolled form missed the instruction cache: profiles/r01_ncu_other_kernels.json, boolean: no_instruction 1.5/issue)
-            T s0[R], s1[R];
+            // a state holds L*BASE_LOG bits (+ a carry): 32-bit registers whenever that fits, whatever the torus width
+            typedef typename StateWord<T, L * BASE_LOG>::type S;
+            S s0[R], s1[R];
             static_for<0, R>([&](auto p) {
                 constexpr int m = brev(decltype(p)::value, FFT::LOGR);
                 const int c = lane + R * m;
-                s0[decltype(p)::value] = decomp_init_state<T>(rot_read<T, N>(acc_r, c, a) - acc_r[c], BASE_LOG, L);
-                s1[decltype(p)::value] = decomp_init_state<T>(rot_read<T, N>(acc_r, c + M, a) - acc_r[c + M], BASE_LOG, L);
+                s0[decltype(p)::value] = (S)decomp_init_state<T>(rot_read<T, N>(acc_r, c, a) - acc_r[c], BASE_LOG, L);
+                s1[decltype(p)::value] = (S)decomp_init_state<T>(rot_read<T, N>(acc_r, c + M, a) - acc_r[c + M], BASE_LOG, L);
             });
 #if defined(__CUDA_ARCH__)
 #pragma unroll 1
@@ -72,8 +74,8 @@ template <typename T, int R, int K, int L, int BASE_LOG> struct BRCore {
             for (int t = 0; t < L; t++) {
                 cplx x[R];
                 static_for<0, R>([&](auto p) {
-                    x[decltype(p)::value] = cplx{int_to_double((int32_t)decomp_next_digit<T>(s0[decltype(p)::value], BASE_LOG)),
-                                                 int_to_double((int32_t)decomp_next_digit<T>(s1[decltype(p)::value], BASE_LOG))};
+                    x[decltype(p)::value] = cplx{int_to_double((int32_t)decomp_next_digit<S>(s0[decltype(p)::value], BASE_LOG)),
+                                                 int_to_double((int32_t)decomp_next_digit<S>(s1[decltype(p)::value], BASE_LOG))};
                 });
                 FFT::fwd_pass1(lane, x, fbuf_r + t * REGION, twf);
             }

@@ -66,6 +66,11 @@ template <typename T> HD typename TorusTraits<T>::Signed decomp_next_digit(T &st
     return (typename TorusTraits<T>::Signed)(res - (carry << base_log));
 }
 
+// register type of a decomposition state of STATE_BITS = level * base_log bits: the recurrence never leaves
+// [0, 2^STATE_BITS] (masked at init, + one carry), so 32 bits do whenever STATE_BITS <= 31
+template <typename T, int STATE_BITS, bool NARROW = (STATE_BITS <= 31)> struct StateWord { typedef T type; };
+template <typename T, int STATE_BITS> struct StateWord<T, STATE_BITS, true> { typedef uint32_t type; };
+
 HD int ilog2(int x) { int l = 0; while ((1 << l) < x) l++; return l; }
 
 }  // namespace b200tfhe
