@@ -40,11 +40,12 @@ template <typename T, int K, int L, int BASE_LOG> struct BigCore {
             const int c = tid + TH * m;
             T d0 = rot_read<T, N>(acc_r, c, a) - acc_r[c];
             T d1 = rot_read<T, N>(acc_r, c + M, a) - acc_r[c + M];
-            T s0 = decomp_init_state<T>(d0, BASE_LOG, L), s1 = decomp_init_state<T>(d1, BASE_LOG, L);
+            typedef typename StateWord<T, L * BASE_LOG>::type S;   // 32-bit recurrence when the state fits
+            S s0 = (S)decomp_init_state<T>(d0, BASE_LOG, L), s1 = (S)decomp_init_state<T>(d1, BASE_LOG, L);
             int32_t g0 = 0, g1 = 0;
             static_for<0, TL + 1>([&](auto) {
-                g0 = (int32_t)decomp_next_digit<T>(s0, BASE_LOG);
-                g1 = (int32_t)decomp_next_digit<T>(s1, BASE_LOG);
+                g0 = (int32_t)decomp_next_digit<S>(s0, BASE_LOG);
+                g1 = (int32_t)decomp_next_digit<S>(s1, BASE_LOG);
             });
             x[decltype(p)::value] = cplx{int_to_double_scaled<12>(g0), int_to_double_scaled<12>(g1)};   // digits / M
         });
@@ -56,10 +57,11 @@ template <typename T, int K, int L, int BASE_LOG> struct BigCore {
             const int c = tid + TH * m;
             T d0 = rot_read<T, N>(acc_r, c, a) - acc_r[c];
             T d1 = rot_read<T, N>(acc_r, c + M, a) - acc_r[c + M];
-            T s0 = decomp_init_state<T>(d0, BASE_LOG, L), s1 = decomp_init_state<T>(d1, BASE_LOG, L);
+            typedef typename StateWord<T, L * BASE_LOG>::type S;
+            S s0 = (S)decomp_init_state<T>(d0, BASE_LOG, L), s1 = (S)decomp_init_state<T>(d1, BASE_LOG, L);
             int32_t g0 = 0, g1 = 0;
             static_for<0, L>([&](auto e) {    // every level's digit is a few integer instructions: compute all, select one
-                const int32_t e0 = (int32_t)decomp_next_digit<T>(s0, BASE_LOG), e1 = (int32_t)decomp_next_digit<T>(s1, BASE_LOG);
+                const int32_t e0 = (int32_t)decomp_next_digit<S>(s0, BASE_LOG), e1 = (int32_t)decomp_next_digit<S>(s1, BASE_LOG);
                 if (tl == decltype(e)::value) { g0 = e0; g1 = e1; }
             });
             x[decltype(p)::value] = cplx{int_to_double_scaled<12>(g0), int_to_double_scaled<12>(g1)};   // digits / M
