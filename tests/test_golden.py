@@ -176,3 +176,49 @@ def test_cuda_path_matches_golden_gadget_integer_ops(ctx, zn):
     bs = gadget.Bootstrapper(k, None, pksk)
     assert np.array_equal(bs.pack_into_new_accumulator(lwes[2:4], 3), zn["GOLD_PK.packed_p3_count2"])
     assert np.array_equal(bs.pack_into_new_accumulator(lwes[:5], 5), zn["GOLD_PK.packed_p5_count5"])
+
+
+# ---- WoP-PBS row: private functional packing keyswitch with the circuit-bootstrap key list (tests/golden/wopbs_golden.npz) ----
+GOLD_WOP = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "wopbs_golden.npz")
+
+
+@pytest.fixture(scope="module")
+def zw():
+    return np.load(GOLD_WOP)
+
+
+def test_oracle_reproduces_golden_pfpks(zw):
+    from oracle.oracle import Oracle
+    o = Oracle("GOLD_PK")
+    o.glwe_key = zw["GOLD_PK.glwe_key"].astype(np.uint64)
+    pb, pl = int(zw["pf_base_log"]), int(zw["pf_level"])
+    pf, lwes = zw["GOLD_PK.pfpksk_list"], zw["GOLD_PK.lwes"]
+    key_len = (o.big + 1) * pl * o.glwe_len
+    assert pf.size == (o.k + 1) * key_len
+    for r in range(o.k + 1):
+        assert np.array_equal(o.pfpks(pf[r * key_len:(r + 1) * key_len], pb, pl, lwes), zw["GOLD_PK.pfpks_out"][r])
+    # meaning of the stored vectors (lwe_wopbs.rs:128-157): an encryption of 5 * 2^60 goes to -m * S_r for r < k and to +m for r = k
+    m, S = 5 << 60, o.glwe_key.reshape(o.k, o.N)
+    ph = zw["GOLD_PK.enc5_phases"]
+    for r in range(o.k + 1):
+        want = np.zeros(o.N, dtype=object)
+        if r < o.k:
+            want[:] = [(-m * int(s)) % (1 << 64) for s in S[r]]
+        else:
+            want[0] = m
+        d = np.array([((int(a) - int(b) + (1 << 63)) % (1 << 64)) - (1 << 63) for a, b in zip(ph[r], want)], dtype=np.float64)
+        assert np.abs(d).max() < 2.0 ** 50
+
+
+@pytest.mark.gpu
+def test_cuda_path_matches_golden_pfpks(ctx, zw):
+    """Bit for bit: the tensor-core GEMM over exactly split base-2^15 digits against the stored outputs of the reference loop."""
+    import tfhe_rs_odd_b200 as t
+    from oracle.oracle import Oracle
+    o = Oracle("GOLD_PK")
+    p = params_of(o)
+    pf = t.core_crypto.LwePrivateFunctionalPackingKeyswitchKeyList.upload(ctx, p, int(zw["pf_base_log"]), int(zw["pf_level"]),
+                                                                         zw["GOLD_PK.pfpksk_list"])
+    for r in range(o.k + 1):
+        got = t.core_crypto.private_functional_keyswitch_lwe_ciphertext_into_glwe_ciphertext(pf, r, zw["GOLD_PK.lwes"])
+        assert np.array_equal(got, zw["GOLD_PK.pfpks_out"][r])
