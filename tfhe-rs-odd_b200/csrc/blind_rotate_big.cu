@@ -6,6 +6,22 @@
 
 namespace b200tfhe {
 
+#if defined(__CUDA_ARCH__)
+DEV void tmem_st16(uint32_t taddr, const uint32_t (&v)[16]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+                 "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]), "r"(v[10]),
+                 "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+                 : "memory");
+}
+DEV void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+                   "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                 : "r"(taddr)
+                 : "memory");
+}
+#endif
+
 template <typename T, int K, int L, int BL>
 __global__ void __launch_bounds__(256, 1)
 blind_rotate_big_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const T *__restrict__ luts,
@@ -24,8 +40,8 @@ blind_rotate_big_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const T
     const int tid = threadIdx.x;
     const int ct = blockIdx.x;
     if (ct >= batch) return;
-    if (tid < 32) {   // 256 tensor-memory columns: the Fourier accumulators of the 8 warps
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(&tmem_base_smem)), "n"(256));
+    if (tid < 32) {   // tensor-memory columns [0,256): the Fourier accumulators of the 8 warps; [256,320): second-level digits
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(&tmem_base_smem)), "n"(512));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
     tmem_fence_before();
@@ -52,6 +68,9 @@ blind_rotate_big_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const T
     // profiles/r01_ncu_other_kernels.json) is covered by the transform.
     const int warp = tid >> 5;
     const uint32_t t_f = tmem_base_smem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((warp >> 2) * 128);
+    // L = 2: the decomposition of a row runs ONCE per iteration; the level-(L-1) digits wait in tensor memory (16 packed words per
+    // thread and row) for their own step, which keeps the reference's summation order (level-major) at half the integer work
+    const uint32_t t_dig = tmem_base_smem + ((uint32_t)((warp & 3) * 32) << 16) + 256u + (uint32_t)((warp >> 2) * (16 * K1));
 
     for (int i = 0; i < n; i++) {
         const int a = ahat[i];
@@ -67,7 +86,19 @@ blind_rotate_big_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const T
             cplx gv[P];
             static_for<0, P>([&](auto p) { gv[decltype(p)::value] = ldg_stream(gbase + decltype(p)::value * 256); });
             cplx x[P];
-            C::digits_rt(tid, acc + (size_t)r * N, a, t, x);
+            if constexpr (L == 2) {
+                uint32_t packed[P];
+                if (t == 0) {
+                    C::digits_both(tid, acc + (size_t)r * N, a, x, packed);
+                    tmem_st16(t_dig + (uint32_t)(r * 16), packed);     // completed by the tmem_wait_st at the end of the step
+                } else {
+                    tmem_ld16(t_dig + (uint32_t)(r * 16), packed);
+                    tmem_wait_ld();
+                    C::digits_unpack(packed, x);
+                }
+            } else {
+                C::digits_rt(tid, acc + (size_t)r * N, a, t, x);
+            }
             __syncthreads();               // previous user of S1 is done
             C::fwdA(tid, x, S1, ta, tq);
             __syncthreads();
@@ -130,7 +161,7 @@ blind_rotate_big_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const T
 
     tmem_fence_before();
     __syncthreads();
-    if (tid < 32) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base_smem), "n"(256));
+    if (tid < 32) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base_smem), "n"(512));
     T *o = out + (size_t)ct * out_stride;
     if (mode == BR_MODE_GLWE) {
         for (int c = tid; c < K1 * N; c += 256) o[c] = acc[c];

@@ -67,6 +67,29 @@ template <typename T, int K, int L, int BASE_LOG> struct BigCore {
             x[decltype(p)::value] = cplx{int_to_double_scaled<12>(g0), int_to_double_scaled<12>(g1)};   // digits / M
         });
     }
+    // L = 2: both levels' digits from ONE pass over the coefficients; the first (level L) goes to x, the second is packed
+    // (two 16-bit digits, |digit| <= 2^(BASE_LOG-1) <= 2^15 - 1 requires BASE_LOG <= 15) for the step that transforms it later
+    HD static void digits_both(int tid, const T *acc_r, int a, cplx (&x)[P], uint32_t (&packed)[P]) {
+        static_assert(L != 2 || BASE_LOG <= 15, "packed second-level digits are 16 bits wide");
+        static_for<0, P>([&](auto p) {
+            constexpr int m = brev(decltype(p)::value, LOGP);
+            const int c = tid + TH * m;
+            T d0 = rot_read<T, N>(acc_r, c, a) - acc_r[c];
+            T d1 = rot_read<T, N>(acc_r, c + M, a) - acc_r[c + M];
+            typedef typename StateWord<T, L * BASE_LOG>::type S;
+            S s0 = (S)decomp_init_state<T>(d0, BASE_LOG, L), s1 = (S)decomp_init_state<T>(d1, BASE_LOG, L);
+            const int32_t g0 = (int32_t)decomp_next_digit<S>(s0, BASE_LOG), g1 = (int32_t)decomp_next_digit<S>(s1, BASE_LOG);
+            const int32_t h0 = (int32_t)decomp_next_digit<S>(s0, BASE_LOG), h1 = (int32_t)decomp_next_digit<S>(s1, BASE_LOG);
+            x[decltype(p)::value] = cplx{int_to_double_scaled<12>(g0), int_to_double_scaled<12>(g1)};
+            packed[decltype(p)::value] = ((uint32_t)h0 & 0xFFFFu) | ((uint32_t)h1 << 16);
+        });
+    }
+    HD static void digits_unpack(const uint32_t (&packed)[P], cplx (&x)[P]) {
+        static_for<0, P>([&](auto p) {
+            const uint32_t w = packed[decltype(p)::value];
+            x[decltype(p)::value] = cplx{int_to_double_scaled<12>((int32_t)(int16_t)(w & 0xFFFFu)), int_to_double_scaled<12>((int32_t)w >> 16)};
+        });
+    }
     HD static void key_input(int tid, const T *poly, cplx (&x)[P]) {
         static_for<0, P>([&](auto p) {
             constexpr int m = brev(decltype(p)::value, LOGP);
