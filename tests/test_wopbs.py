@@ -311,3 +311,28 @@ def test_gpu_vertical_packing_cmux_tree(ctx, nbits, polys):
     err = np.abs((ph - (dec.astype(np.uint64) << np.uint64(60))).astype(np.int64)) / 2.0 ** 64
     eref = np.abs((phr - (dref.astype(np.uint64) << np.uint64(60))).astype(np.int64)) / 2.0 ** 64
     assert err.max() < max(8 * eref.max(), 2.0 ** -9) < 1 / 64
+
+
+@pytest.mark.gpu
+def test_gpu_wop_bootstrap_set_large_ragged_batch(ctx):
+    """The bootstrap of the WoP-PBS set (N 2048, level 2, base 2^15) on a batch of several waves that is not a multiple of the
+    ciphertexts per CTA (ghost ciphertext), two tables selected per ciphertext, against the oracle; GLWE and LWE epilogues agree."""
+    import tfhe_rs_odd_b200 as t
+    o = get_oracle("TOY_WOP")
+    _, bsk, ksk = _keys(ctx, o)
+    B = 3 * 148 + 157
+    msgs = (np.arange(B) * 7 + 3) % o.pmod
+    cts = o.encrypt(o.encode(msgs), under="small", seed=97)
+    luts = np.stack([o.lut(lambda x: x), o.lut(lambda x: (5 * x + 2) % o.pmod)])
+    idx = (np.arange(B) % 2).astype(np.uint32)
+    want = np.where(idx == 0, msgs, (5 * msgs + 2) % o.pmod).astype(np.uint64)
+    out = t.programmable_bootstrap_lwe_ciphertext(cts, luts, bsk, lut_idx=idx)
+    ph = o.phase(out)
+    assert np.array_equal(o.decode(ph) % o.pmod, want)
+    nref = 16
+    ref = o.pbs(cts[:nref], luts, idx[:nref])
+    d = (ph[:nref] - o.phase(ref)).astype(np.int64) / 2.0 ** 64
+    assert np.abs(d).max() < phase_bound(o)
+    glwe = t.core_crypto.programmable_bootstrap_lwe_ciphertext_without_sample_extract(cts, luts, bsk, lut_idx=idx)
+    ext = t.core_crypto.extract_lwe_sample_from_glwe_ciphertext(ctx, glwe, o.k, o.N, 64)
+    assert np.array_equal(ext, out)                                                              # same kernel, other epilogue
