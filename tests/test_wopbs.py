@@ -336,3 +336,50 @@ def test_gpu_wop_bootstrap_set_large_ragged_batch(ctx):
     glwe = t.core_crypto.programmable_bootstrap_lwe_ciphertext_without_sample_extract(cts, luts, bsk, lut_idx=idx)
     ext = t.core_crypto.extract_lwe_sample_from_glwe_ciphertext(ctx, glwe, o.k, o.N, 64)
     assert np.array_equal(ext, out)                                                              # same kernel, other epilogue
+
+
+# ---- host mirror of shortint::wopbs::WopbsKey (tfhe-rs-odd_b200/wopbs.py) ---------------------------------------------------
+def test_wopbs_lut_tables_match_reference_formulas():
+    """generate_lut (wopbs/mod.rs:282-295) and generate_lut_without_padding (:320-333), computed without a device."""
+    import tfhe_rs_odd_b200 as t  # noqa: F401
+    from tfhe_rs_odd_b200 import wopbs
+
+    class _P:
+        polynomial_size = 2048
+
+    class _SK:
+        params = _P()
+
+    class _PF:
+        decomp_level_count, decomp_base_log = 2, 15
+    key = wopbs.WopbsKey(_SK(), _PF(), wopbs.WopbsParameters(2, 15, 3, 5, 4, 4))
+    lut = key.generate_lut(lambda x: x * x % 4)
+    assert lut.values.shape == (1, 2048) and lut.output_ciphertext_count == 1
+    assert [int(v) >> 59 for v in lut.values[0, :16]] == [(i % 4) ** 2 % 4 for i in range(16)] and not lut.values[0, 16:].any()
+    lut2 = key.generate_lut_without_padding(lambda x: 3 - x)
+    assert [int(v) >> 60 for v in lut2.values[0, :16]] == [3 - i % 4 for i in range(16)]
+    with pytest.raises(t.B200TfheError, match="does not match"):
+        wopbs.WopbsKey(_SK(), _PF(), wopbs.WopbsParameters(3, 15, 3, 5, 4, 4))
+
+
+@pytest.mark.gpu
+def test_gpu_wopbs_key_applies_lut_to_every_message(ctx):
+    """WopbsKey.wopbs (wopbs/mod.rs:434-451) and programmable_bootstrapping_without_padding (:472-495) over all 16 values of a
+    2_2 block, as the reference's doc-tests do for one value."""
+    import tfhe_rs_odd_b200 as t
+    from tfhe_rs_odd_b200 import shortint, wopbs
+    name = "TOY_WOP"
+    o = get_oracle(name)
+    _, bsk, ksk, pf, wop = _wop_keys(ctx, o, name)
+    key = wopbs.WopbsKey(shortint.ServerKey(ksk, bsk, 4, 4), pf, wopbs.WopbsParameters(wop[1], wop[0], wop[3], wop[2], 4, 4))
+    msgs = np.arange(16, dtype=np.uint64)
+    f = lambda x: (x * x + 1) % 4                                                    # noqa: E731
+    cts = shortint.CiphertextList(o.encrypt(msgs << np.uint64(59), under="big", seed=101), degree=15, noise_level=shortint.NOISE_NOMINAL)
+    out = key.wopbs(cts, key.generate_lut(f))
+    ph = o.phase(out.data)
+    dec = ((ph.astype(np.uint64) + np.uint64(1 << 58)) >> np.uint64(59)).astype(int) & 31
+    assert np.array_equal(dec, [f(int(m) % 4) for m in msgs]) and (out.degree == 3).all() and (out.noise_level == shortint.NOISE_NOMINAL).all()
+    cts2 = shortint.CiphertextList(o.encrypt(msgs << np.uint64(60), under="big", seed=103), degree=15, noise_level=shortint.NOISE_NOMINAL)
+    out2 = key.programmable_bootstrapping_without_padding(cts2, key.generate_lut_without_padding(f))
+    dec2, _ = _decode4(o, out2.data)
+    assert np.array_equal(dec2, [f(int(m) % 4) for m in msgs])
