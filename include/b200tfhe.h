@@ -240,7 +240,7 @@ int b200tfhe_pfpks_batch_u64(b200tfhe_context *ctx, const b200tfhe_pfpksk *pf, u
  * Per input: nbits * cbs_level bootstraps (homomorphic_shift_boolean :369-444), (k+1) private functional packing
  * keyswitches each, Fourier conversion of the GGSWs; per (input, table): the CMUX tree over the table's polynomials
  * (cmux_tree_memory_optimized :468-592, one launch per layer) and a blind rotation over the input's own remaining GGSWs
- * (:866-892) with sample extraction. */
+ * (:866-892) with sample extraction.  Batches above 1024 inputs are processed in slices (bounded device workspace). */
 int b200tfhe_cbs_vertical_packing_batch_u64(b200tfhe_context *ctx, const b200tfhe_bsk *bsk, const b200tfhe_pfpksk *pf, const uint64_t *bits_in,
                                             uint32_t nbits, const uint64_t *luts, uint32_t n_luts, uint32_t polys_per_lut,
                                             uint32_t cbs_base_log, uint32_t cbs_level, uint64_t *out, uint32_t batch);

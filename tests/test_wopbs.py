@@ -383,3 +383,23 @@ def test_gpu_wopbs_key_applies_lut_to_every_message(ctx):
     out2 = key.programmable_bootstrapping_without_padding(cts2, key.generate_lut_without_padding(f))
     dec2, _ = _decode4(o, out2.data)
     assert np.array_equal(dec2, [f(int(m) % 4) for m in msgs])
+
+
+@pytest.mark.gpu
+def test_gpu_cbs_vertical_packing_batch_slices(ctx):
+    """Batches above 1024 inputs go through the device in slices (bounded workspace): same bits out as the slices run separately,
+    every 2-bit input decrypts to its table entry."""
+    o = get_oracle("TOY_WOP")
+    t, bsk, ksk, pf, wop = _wop_keys(ctx, o, "TOY_WOP")
+    B, nbits = 1024 + 77, 2
+    msgs = (np.arange(B) * 3 + 1) % 4
+    bitvals = _bits_msb_first(msgs, nbits).astype(np.uint64)
+    bits = o.encrypt((bitvals.reshape(-1) << np.uint64(63)), under="small", seed=107).reshape(B, nbits, o.n + 1)
+    lut = np.zeros((1, o.N), np.uint64)
+    lut[0, :4] = (np.array([2, 0, 3, 1], dtype=np.uint64) << np.uint64(60))
+    f = t.core_crypto.circuit_bootstrap_boolean_vertical_packing_lwe_ciphertext_list_mem_optimized
+    out = f(bits, lut, bsk, pf, wop[2], wop[3])
+    dec, _ = _decode4(o, out)
+    assert np.array_equal(dec[:, 0], np.array([2, 0, 3, 1])[msgs])
+    assert np.array_equal(out[1024:], f(bits[1024:], lut, bsk, pf, wop[2], wop[3]))
+    assert np.array_equal(out[:8], f(bits[:8], lut, bsk, pf, wop[2], wop[3]))

@@ -1036,6 +1036,18 @@ int b200tfhe_cbs_vertical_packing_batch_u64(b200tfhe_context *ctx, const b200tfh
     REQUIRE(tree == 0 || cmux_layer_supported(pc), "cbs_vertical_packing: no CMUX-tree instance for (N, k, cbs_level, cbs_base_log)");
     if (batch == 0 || n_luts == 0) return 0;
     REQUIRE(bits_in && luts && out, "cbs_vertical_packing: null buffer");
+    // device scratch per input: nbits * cbs_level GGSW level matrices twice (standard + Fourier domain), 2 * 12 * 64 KB at the 2_2
+    // WoP-PBS set; larger batches go through in slices so that the workspace stays around 2 GB
+    constexpr uint32_t CBS_CHUNK = 1024;
+    if (batch > CBS_CHUNK) {
+        for (uint32_t b0 = 0; b0 < batch; b0 += CBS_CHUNK) {
+            const uint32_t nb = batch - b0 < CBS_CHUNK ? batch - b0 : CBS_CHUNK;
+            if (b200tfhe_cbs_vertical_packing_batch_u64(ctx, bsk, pf, bits_in + (size_t)b0 * nbits * small_len(p), nbits, luts, n_luts, polys_per_lut,
+                                                        cbs_base_log, cbs_level, out + (size_t)b0 * n_luts * big_len(p), nb))
+                return 1;
+        }
+        return 0;
+    }
     std::lock_guard<std::mutex> g(ctx->mu);
     CK(cudaSetDevice(ctx->device));
     const size_t slen = small_len(p), blen = big_len(p), glen = glwe_len(p);
