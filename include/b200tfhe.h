@@ -46,7 +46,7 @@ typedef struct {
     int32_t polynomial_size;  /* N   */
     int32_t pbs_base_log;
     int32_t pbs_level;
-    int32_t ks_base_log;
+    int32_t ks_base_log;      /* 1 .. 28 (above 7: exact digit split on the tensor-core keyswitch) */
     int32_t ks_level;
     int32_t torus_bits;       /* 64 or 32 */
 } b200tfhe_params;

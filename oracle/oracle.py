@@ -38,6 +38,10 @@ PARAMS = {
     # WOPBS_PARAM_MESSAGE_2_CARRY_2_KS_PBS (shortint/parameters/parameters_wopbs_message_carry.rs:432-451) and a toy of the same shape
     "WOPBS_MESSAGE_2_CARRY_2": (769, 1, 2048, 15, 2, 6, 2, 64, 0.0000043131554647504185, 0.00000000000000029403601535432533, 16, "ks_pbs"),
     "TOY_WOP": (12, 1, 2048, 15, 2, 6, 2, 64, 1e-9, 0.00000000000000029403601535432533, 16, "ks_pbs"),
+    # keyswitch bases wider than an int8 digit: 2^10 x 1 level (WOPBS_PARAM_MESSAGE_3_CARRY_3_KS_PBS), 2^15 x 2, and 2^12 x 2 on the 2^32 torus
+    "TOY_KSW10": (12, 1, 2048, 23, 1, 10, 1, 64, 1e-9, 0.00000000000000029403601535432533, 16, "ks_pbs"),
+    "TOY_KSW15": (20, 1, 512, 12, 2, 15, 2, 64, 1e-9, 1e-15, 4, "ks_pbs"),
+    "TOY_KSW12_U32": (20, 2, 512, 6, 3, 12, 2, 32, 1e-7, 1e-8, 0, "pbs_ks"),
     "TOY_MB_G2": (12, 1, 512, 12, 2, 4, 4, 64, 1e-9, 1e-15, 4, "ks_pbs"),
     "TOY_MB_G3": (12, 1, 512, 12, 2, 4, 4, 64, 1e-9, 1e-15, 4, "ks_pbs"),
     "TOY_MB22_G2": (12, 1, 2048, 22, 1, 5, 3, 64, 1e-9, 0.0000000000000003152931493498455, 16, "ks_pbs"),

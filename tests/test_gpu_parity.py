@@ -49,6 +49,30 @@ def test_keyswitch_bit_exact(ctx, name):
     assert t.keyswitch_lwe_ciphertext(ksk, np.zeros((0, o.big + 1), _dt(o))).shape == (0, o.n + 1)
 
 
+@pytest.mark.parametrize("name", ["TOY_KSW10", "TOY_KSW15", "TOY_KSW12_U32"])
+def test_keyswitch_wide_base_bit_exact(ctx, name):
+    """Keyswitch bases above 2^7 (the 3_3 / 4_4 WoP-PBS sets use 2^10 / 2^11): every reference digit is split exactly into int8
+    sub-digits that meet pre-shifted key rows, so the tensor-core GEMM stays bit-identical to the reference loop
+    (lwe_keyswitch.rs:143-169) -- rounding-boundary rows included."""
+    import tfhe_rs_odd_b200 as t
+    o = get_oracle(name)
+    p = params_of(o)
+    ksk = t.LweKeyswitchKey.upload(ctx, p, o.ksk.astype(_dt(o)))
+    rng = np.random.default_rng(13)
+    B = 150
+    cts = rng.integers(0, 2 ** o.bits, size=(B, o.big + 1), dtype=np.uint64)
+    cts[0, :] = 0
+    cts[1, :] = (1 << o.bits) - 1
+    cts[2, :] = 1 << (o.bits - 1)
+    cts[3, :] = (1 << (o.bits - 1)) - 1
+    cts[4, :] = 1 << (o.bits - o.b_ks * o.l_ks - 1)          # half of the last kept digit: the rounding boundary
+    cts[5, :] = (1 << (o.bits - o.b_ks * o.l_ks - 1)) - 1
+    ref = o.keyswitch(cts)
+    got = t.keyswitch_lwe_ciphertext(ksk, cts.astype(_dt(o)))
+    assert np.array_equal(got.astype(np.uint64), ref)
+    assert np.array_equal(t.keyswitch_lwe_ciphertext(ksk, cts[9].astype(_dt(o))).astype(np.uint64), ref[9])   # batch of one: same path
+
+
 @pytest.mark.parametrize("name", ["TOY_U64", "TOY_U32", "TOY_1_1", "TOY_3_3", "MESSAGE_2_CARRY_2", "BOOLEAN_DEFAULT"])
 def test_keyswitch_tensor_core_path_bit_exact(ctx, name):
     """The tcgen05 kind::i8 keyswitch (digits x byte planes of the key): same bits as the oracle on a batch that is ragged

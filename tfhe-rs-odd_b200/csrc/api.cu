@@ -70,6 +70,7 @@ struct b200tfhe_ksk {
     bool finalized;
     KSTensorKey tk;      // byte-plane copy of the key for the tensor-core path (d_planes == nullptr: not available)
     int body_col = -1;   // output column receiving the input body (-1: the last one); k*N for a packing keyswitch key
+    int sub = 1, sub_bits = 0;   // base_log > 7: every digit split exactly into `sub` int8 sub-digits (KSLaunch::sub), tensor-core path only
 };
 // LwePackingKeyswitchKey: the same integer GEMM with (k+1)N output columns and the body on coefficient 0 of the body polynomial
 struct b200tfhe_pksk {
@@ -202,8 +203,9 @@ static int check_pbs_params(b200tfhe_context *ctx, const Params &p) {
 static int check_ks_params(b200tfhe_context *ctx, const Params &p) {
     REQUIRE(p.bits == 64 || p.bits == 32, "only native 2^64 / 2^32 ciphertext moduli are supported");
     REQUIRE(p.n > 0 && p.k > 0 && p.N > 0, "invalid dimensions");
-    REQUIRE(p.ks_level > 0 && p.ks_base_log > 0 && p.ks_base_log <= 7 && p.ks_level * p.ks_base_log < p.bits,
-            "invalid keyswitch decomposition (base_log must be <= 7)");
+    // base_log <= 7: int8 digits as they are; up to 28: digits split exactly into int8 sub-digits for the tensor-core GEMM
+    REQUIRE(p.ks_level > 0 && p.ks_base_log > 0 && p.ks_base_log <= 28 && p.ks_level * p.ks_base_log < p.bits,
+            "invalid keyswitch decomposition (base_log must be <= 28)");
     return 0;
 }
 // number of GGSW ciphertexts of a bootstrap key: n (classic) or n/G * 2^G (entities/lwe_multi_bit_bootstrap_key.rs)
@@ -360,10 +362,32 @@ int b200tfhe_ksk_finalize(b200tfhe_context *ctx, b200tfhe_ksk *k) {
     REQUIRE(ctx && k, "ksk_finalize: null argument");
     std::lock_guard<std::mutex> g(ctx->mu);
     CK(cudaSetDevice(ctx->device));
-    int rc = ks_colsum_launch(k->d_ksk, k->d_colsum, k->p.k * k->p.N, k->p.n, k->p.ks_level, k->p.ks_base_log, k->p.bits, ctx->stream);
+    const int n_in = k->p.k * k->p.N;
+    int rc;
+    if (k->p.ks_base_log > 7) {
+        // wide base (e.g. 2^10 / 2^11 of the 3_3 / 4_4 WoP-PBS sets): key rows replicated with shifts for the exact digit split
+        const int bl = k->p.ks_base_log, sub = (bl + 5) / 6, sub_bits = (bl + sub - 1) / sub, rows_per = k->p.ks_level * sub;   // sub-digits of <= 6 bits (+ carry) fit int8
+        REQUIRE(ks_tc_supported(k->p.bits, n_in, k->p.n, rows_per, sub_bits + 1), "keyswitch base_log > 7 needs the tensor-core path, which does not cover this set");
+        const size_t width = (size_t)k->p.n + 1;
+        void *d_exp = nullptr, *planes = nullptr;
+        CK(cudaMalloc(&d_exp, (size_t)n_in * rows_per * width * sz(k->p)));
+        cudaError_t e = cudaMalloc(&planes, ks_tc_key_bytes(k->p.bits, n_in, k->p.n, rows_per));
+        if (e != cudaSuccess) { cudaFree(d_exp); return fail_cuda(ctx, "cudaMalloc(ksk planes)", e); }
+        if (k->tk.d_planes) { cudaFree(k->tk.d_planes); k->tk.d_planes = nullptr; }
+        rc = ks_expand_rows_launch(k->d_ksk, d_exp, (size_t)n_in, k->p.ks_level, sub, sub_bits, 0, width, k->p.bits, ctx->stream);
+        if (!rc) rc = ks_tc_prepare_key(&k->tk, d_exp, planes, k->p.bits, n_in, k->p.n, rows_per, ctx->stream);
+        ctx->launches += 2;
+        cudaError_t es = cudaStreamSynchronize(ctx->stream);
+        cudaFree(d_exp);
+        if (rc || es != cudaSuccess) { cudaFree(planes); k->tk.d_planes = nullptr; return fail(ctx, "wide keyswitch key preparation failed: " + std::to_string(rc)); }
+        k->sub = sub;
+        k->sub_bits = sub_bits;
+        k->finalized = true;
+        return 0;
+    }
+    rc = ks_colsum_launch(k->d_ksk, k->d_colsum, k->p.k * k->p.N, k->p.n, k->p.ks_level, k->p.ks_base_log, k->p.bits, ctx->stream);
     ctx->launches++;
     if (rc) return fail(ctx, "ks_colsum launch failed: " + std::to_string(rc));
-    const int n_in = k->p.k * k->p.N;
     if (!getenv("B200TFHE_NO_KS_TC") && ks_tc_supported(k->p.bits, n_in, k->p.n, k->p.ks_level, k->p.ks_base_log)) {
         if (k->tk.d_planes) { cudaFree(k->tk.d_planes); k->tk.d_planes = nullptr; }
         void *planes = nullptr;
@@ -412,9 +436,11 @@ static int ks_dev_locked(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const v
     const Params &p = ksk->p;
     KSLaunch a{d_in, big_len(p), d_out, small_len(p), ksk->d_ksk, ksk->d_colsum, p.k * p.N, p.n, p.ks_level, p.ks_base_log, p.bits, (int)batch};
     a.body_col = ksk->body_col;
+    a.sub = ksk->sub;
+    a.sub_bits = ksk->sub_bits;
     static const int tc_min = getenv("B200TFHE_KS_TC_MIN") ? atoi(getenv("B200TFHE_KS_TC_MIN")) : 1;
     int rc;
-    if (ksk->tk.d_planes && (int)batch >= tc_min) {
+    if (ksk->tk.d_planes && ((int)batch >= tc_min || ksk->sub > 1)) {
         void *digits = nullptr;
         CK(ctx->ws.get(Workspace::DIG, (size_t)batch * ksk->tk.kp, &digits));
         rc = ks_tc_launch(a, ksk->tk, digits, ctx->stream);
@@ -928,7 +954,7 @@ int b200tfhe_cbs_pfpksk_upload_u64(b200tfhe_context *ctx, const b200tfhe_params 
     REQUIRE(pp->glwe_dimension > 0 && is_pow2(pp->polynomial_size), "invalid dimensions");
     REQUIRE(pfks_level >= 1 && pfks_base_log >= 1 && pfks_base_log <= 28 && pfks_level * pfks_base_log < 64, "invalid pfks decomposition");
     Params p = to_params(pp);
-    const int sub = ((int)pfks_base_log + 6) / 7, sub_bits = ((int)pfks_base_log + sub - 1) / sub;
+    const int sub = ((int)pfks_base_log + 5) / 6, sub_bits = ((int)pfks_base_log + sub - 1) / sub;   // sub-digits of <= 6 bits (+ carry) fit int8
     const int n_in = p.k * p.N + 1, n_out = (p.k + 1) * p.N - 1, rows_per = (int)pfks_level * sub;
     REQUIRE(ks_tc_supported(64, n_in, n_out, rows_per, sub_bits + 1), "cbs_pfpksk_upload: the tensor-core keyswitch does not cover this set");
     std::lock_guard<std::mutex> g(ctx->mu);
