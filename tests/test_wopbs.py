@@ -403,3 +403,42 @@ def test_gpu_cbs_vertical_packing_batch_slices(ctx):
     assert np.array_equal(dec[:, 0], np.array([2, 0, 3, 1])[msgs])
     assert np.array_equal(out[1024:], f(bits[1024:], lut, bsk, pf, wop[2], wop[3]))
     assert np.array_equal(out[:8], f(bits[:8], lut, bsk, pf, wop[2], wop[3]))
+
+
+@pytest.mark.gpu
+def test_gpu_wopbs_k3_n512_family(ctx):
+    """The (k 3, N 512) WoP-PBS family (WOPBS_PARAM_MESSAGE_2_CARRY_1_KS_PBS / 4_CARRY_0: pbs 12/2, ks 2/4, pfks 12/2, cbs 3/4) at a toy n:
+    R = 16 instances of the bootstrap, of the per-ciphertext-GGSW blind rotation and of the CMUX layer; pfpks with a 2^12 base
+    (two 6-bit sub-digits).  Every 3-bit message through one table, then 10 bits through a 2-polynomial table (one tree layer)."""
+    name = "TOY_WOP_K3"
+    o = get_oracle(name)
+    t, bsk, ksk, pf, wop = _wop_keys(ctx, o, name)
+    host = _pfpksk(o, name)
+    rng = np.random.default_rng(109)
+    rnd = rng.integers(0, U64, size=(9, o.big + 1), dtype=np.uint64)
+    key_len = (o.big + 1) * wop[1] * o.glwe_len
+    for r in (0, o.k):
+        got = t.core_crypto.private_functional_keyswitch_lwe_ciphertext_into_glwe_ciphertext(pf, r, rnd)
+        assert np.array_equal(got, o.pfpks(host[r * key_len:(r + 1) * key_len], wop[0], wop[1], rnd))
+    f = t.core_crypto.circuit_bootstrap_boolean_vertical_packing_lwe_ciphertext_list_mem_optimized
+    msgs = np.arange(8, dtype=np.uint64)
+    bits = t.core_crypto.extract_bits_from_lwe_ciphertext_mem_optimized(o.encrypt(msgs << np.uint64(61), under="big", seed=113), bsk, ksk, 61, 3)
+    lut = np.zeros((1, o.N), np.uint64)
+    lut[0, :8] = ((msgs * np.uint64(3) + np.uint64(1)) % np.uint64(8)) << np.uint64(61)
+    out = f(bits, lut, bsk, pf, wop[2], wop[3])
+    ph = o.phase(out.reshape(-1, o.big + 1))
+    dec = ((ph.astype(np.uint64) + np.uint64(1 << 60)) >> np.uint64(61)).astype(int) & 7
+    assert np.array_equal(dec, ((msgs * 3 + 1) % 8).astype(int))
+    ref = o.cbs_vertical_packing(host, wop, bits[:2], lut)
+    assert np.array_equal(((o.phase(ref.reshape(-1, o.big + 1)).astype(np.uint64) + np.uint64(1 << 60)) >> np.uint64(61)).astype(int) & 7, dec[:2])
+    nb = 10                                                          # 2 polynomials of 512 entries: one CMUX layer + 9 rotation steps
+    m10 = np.array([0, 1023, 512, 511, 700], dtype=np.uint64)
+    bits10 = t.core_crypto.extract_bits_from_lwe_ciphertext_mem_optimized(o.encrypt(m10 << np.uint64(54), under="big", seed=127), bsk, ksk, 54, nb)
+    b10, _ = _decrypt_bits(o, bits10)
+    assert np.array_equal(b10, _bits_msb_first(m10, nb))
+    idx = np.arange(2 * o.N, dtype=np.uint64)
+    tab = (idx * np.uint64(5) + idx // np.uint64(9)) % np.uint64(8)
+    out10 = f(bits10, (tab << np.uint64(61)).reshape(2, o.N), bsk, pf, wop[2], wop[3], number_of_luts=1)
+    ph10 = o.phase(out10.reshape(-1, o.big + 1))
+    dec10 = ((ph10.astype(np.uint64) + np.uint64(1 << 60)) >> np.uint64(61)).astype(int) & 7
+    assert np.array_equal(dec10, tab[m10.astype(np.int64)].astype(int))
