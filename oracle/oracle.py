@@ -40,6 +40,8 @@ PARAMS = {
     "TOY_WOP": (12, 1, 2048, 15, 2, 6, 2, 64, 1e-9, 0.00000000000000029403601535432533, 16, "ks_pbs"),
     # shape of WOPBS_PARAM_MESSAGE_2_CARRY_1_KS_PBS (:n 487, k 3, N 512, pbs 12/2, ks 2/4, pfks 12/2, cbs 3/4) with a toy n
     "TOY_WOP_K3": (12, 3, 512, 12, 2, 2, 4, 64, 1e-9, 1e-15, 8, "ks_pbs"),
+    # shape of WOPBS_PARAM_MESSAGE_3_CARRY_1_KS_PBS (k 3, N 512, pbs 9/3, ks 2/4, pfks 9/3, cbs 3/5) with a toy n
+    "TOY_WOP_K3B": (12, 3, 512, 9, 3, 2, 4, 64, 1e-9, 1e-15, 8, "ks_pbs"),
     # keyswitch bases wider than an int8 digit: 2^10 x 1 level (WOPBS_PARAM_MESSAGE_3_CARRY_3_KS_PBS), 2^15 x 2, and 2^12 x 2 on the 2^32 torus
     "TOY_KSW10": (12, 1, 2048, 23, 1, 10, 1, 64, 1e-9, 0.00000000000000029403601535432533, 16, "ks_pbs"),
     "TOY_KSW15": (20, 1, 512, 12, 2, 15, 2, 64, 1e-9, 1e-15, 4, "ks_pbs"),
@@ -62,7 +64,7 @@ GROUPING = {"MULTI_BIT_2_2_GROUP_2": 2, "MULTI_BIT_2_2_GROUP_3": 3, "TOY_MB_G2":
 
 
 # (pfks_base_log, pfks_level, cbs_base_log, cbs_level) of the WoP-PBS sets
-WOPBS = {"WOPBS_MESSAGE_2_CARRY_2": (15, 2, 5, 3), "TOY_WOP": (15, 2, 5, 3), "TOY_WOP_K3": (12, 2, 3, 4)}
+WOPBS = {"WOPBS_MESSAGE_2_CARRY_2": (15, 2, 5, 3), "TOY_WOP": (15, 2, 5, 3), "TOY_WOP_K3": (12, 2, 3, 4), "TOY_WOP_K3B": (9, 3, 3, 5)}
 
 
 def build(force=False):

@@ -406,11 +406,12 @@ def test_gpu_cbs_vertical_packing_batch_slices(ctx):
 
 
 @pytest.mark.gpu
-def test_gpu_wopbs_k3_n512_family(ctx):
-    """The (k 3, N 512) WoP-PBS family (WOPBS_PARAM_MESSAGE_2_CARRY_1_KS_PBS / 4_CARRY_0: pbs 12/2, ks 2/4, pfks 12/2, cbs 3/4) at a toy n:
+@pytest.mark.parametrize("name", ["TOY_WOP_K3", "TOY_WOP_K3B"])
+def test_gpu_wopbs_k3_n512_family(ctx, name):
+    """The (k 3, N 512) WoP-PBS families (WOPBS_PARAM_MESSAGE_2_CARRY_1_KS_PBS / 4_CARRY_0: pbs 12/2, ks 2/4, pfks 12/2, cbs 3/4, and
+    1_CARRY_2 / 3_CARRY_1 / 4_CARRY_1 / 6_CARRY_0: pbs 9/3, pfks 9/3, cbs 3/5) at a toy n:
     R = 16 instances of the bootstrap, of the per-ciphertext-GGSW blind rotation and of the CMUX layer; pfpks with a 2^12 base
     (two 6-bit sub-digits).  Every 3-bit message through one table, then 10 bits through a 2-polynomial table (one tree layer)."""
-    name = "TOY_WOP_K3"
     o = get_oracle(name)
     t, bsk, ksk, pf, wop = _wop_keys(ctx, o, name)
     host = _pfpksk(o, name)

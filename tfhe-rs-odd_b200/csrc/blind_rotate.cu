@@ -185,12 +185,15 @@ static int launch_br(const BRLaunch &a, cudaStream_t st) {
 
 // first two: WOPBS_PARAM_MESSAGE_2_CARRY_2_KS_PBS (shortint/parameters/parameters_wopbs_message_carry.rs:432-451; also 1_CARRY_1), its
 // bootstrap (level 2, base 2^15) and the GGSWs its circuit bootstrap produces (cbs level 3, base 2^5); next two: the same pair for
-// the (k 3, N 512) sets WOPBS_PARAM_MESSAGE_2_CARRY_1 / 4_CARRY_0 (pbs level 2 base 2^12, cbs level 4 base 2^3)
+// the (k 3, N 512) sets WOPBS_PARAM_MESSAGE_2_CARRY_1 / 4_CARRY_0 (pbs level 2 base 2^12, cbs level 4 base 2^3);
+// last two: 1_CARRY_2 / 3_CARRY_1 / 4_CARRY_1 / 6_CARRY_0 (pbs level 3 base 2^9, cbs level 5 base 2^3)
 #define BR_INSTANCES(X)              \
     X(uint64_t, 32, 1, 2, 15, 2)     \
     X(uint64_t, 32, 1, 3, 5, 1)      \
     X(uint64_t, 16, 3, 2, 12, 1)     \
     X(uint64_t, 16, 3, 4, 3, 1)      \
+    X(uint64_t, 16, 3, 3, 9, 1)      \
+    X(uint64_t, 16, 3, 5, 3, 1)      \
     X(uint64_t, 32, 1, 1, 23, 3)     \
     X(uint32_t, 16, 2, 3, 6, 2)      \
     X(uint64_t, 16, 3, 1, 18, 1)     \

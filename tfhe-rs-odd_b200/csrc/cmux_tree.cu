@@ -115,7 +115,8 @@ cmux_layer_kernel(const T *__restrict__ in, size_t ct_in_stride, T *__restrict__
 
 // (T, R, K, L, BASE_LOG) of the circuit-bootstrapped GGSWs: WOPBS_PARAM_MESSAGE_2_CARRY_2_KS_PBS (cbs level 3, base 2^5)
 //                                                        WOPBS_PARAM_MESSAGE_2_CARRY_1_KS_PBS / 4_CARRY_0 (k 3, N 512; cbs level 4, base 2^3)
-#define CMUX_INSTANCES(X) X(uint64_t, 32, 1, 3, 5) X(uint64_t, 16, 3, 4, 3)
+//                                                        1_CARRY_2 / 3_CARRY_1 / 4_CARRY_1 / 6_CARRY_0 (cbs level 5, base 2^3)
+#define CMUX_INSTANCES(X) X(uint64_t, 32, 1, 3, 5) X(uint64_t, 16, 3, 4, 3) X(uint64_t, 16, 3, 5, 3)
 
 int cmux_layer_supported(const Params &pc) {
 #define X(T, R, K, L, BL) \
