@@ -183,6 +183,18 @@ int b200tfhe_ks_pbs_batch_dev(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, co
 int b200tfhe_pbs_ks_batch_dev(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, const void *d_in,
                               void *d_out, const void *d_luts, const uint32_t *d_lut_idx, uint32_t batch);
 
+/* Allocation-free variant of b200tfhe_keyswitch_batch_dev.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same inputs, outputs and result bits as b200tfhe_keyswitch_batch_dev (tensor-core keyswitch), but the
+ * int8 digit scratch is a fixed file-scope __device__ array of B200TFHE_NOALLOC_KS_SCRATCH_BYTES (held by every GPU that
+ * loads the library until the process exits) instead of the context's growable workspace: the call performs no cudaMalloc /
+ * cudaFree.  batch * padded(k*N*ks_level*sub) must fit the array (409 ciphertexts at PARAM_MESSAGE_2_CARRY_2), larger
+ * batches are rejected with an error; the key must have tensor-core byte planes (every parameter set of the reference has).
+ * Every call on a device shares the one array, which keeps the previous call's contents (nothing in it has to start at zero:
+ * each call rewrites all it reads): calls that OVERLAP on the GPU -- two contexts / streams on one device -- race on it. */
+#define B200TFHE_NOALLOC_KS_SCRATCH_BYTES (4u << 20)
+int b200tfhe_keyswitch_batch_noalloc_dev(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const void *d_in, void *d_out, uint32_t batch);
+
 /* ---- gadget extras of the fork (tfhe/src/gadget/engine/bootstrapping.rs), 64-bit torus ---------------------
  * LwePackingKeyswitchKey (core_crypto/entities/lwe_packing_keyswitch_key.rs; generation
  * algorithms/lwe_packing_keyswitch_key_generation.rs:60-150): [kN][l_ks (level l_ks first)][(k+1)N], input key = the big LWE

@@ -49,6 +49,7 @@ _PROTOS = {
     "b200tfhe_ksk_destroy": [_VP],
     "b200tfhe_gate_batch_u32": [_VP, _VP, _VP, _I, _I, _VP, _VP, _VP, _U32],
     "b200tfhe_keyswitch_batch_dev": [_VP, _VP, _VP, _VP, _U32],
+    "b200tfhe_keyswitch_batch_noalloc_dev": [_VP, _VP, _VP, _VP, _U32],
     "b200tfhe_pbs_batch_dev": [_VP, _VP, _VP, _VP, _VP, _VP, _U32],
     "b200tfhe_blind_rotate_batch_dev": [_VP, _VP, _VP, _VP, _VP, _VP, _U32],
     "b200tfhe_ks_pbs_batch_dev": [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _U32],

@@ -481,6 +481,35 @@ int b200tfhe_keyswitch_batch_dev(b200tfhe_context *ctx, const b200tfhe_ksk *ksk,
     CK(cudaSetDevice(ctx->device));
     return ks_dev_locked(ctx, ksk, d_in, d_out, batch);
 }
+// Allocation-free variant of keyswitch_batch_dev (no counterpart in the reference; see noalloc.cu): the digit scratch of the
+// tensor-core keyswitch is a fixed __device__ array instead of the context's growable workspace.
+static_assert(NOALLOC_KS_SCRATCH_BYTES == B200TFHE_NOALLOC_KS_SCRATCH_BYTES, "scratch size: kernels.h vs b200tfhe.h");
+int b200tfhe_keyswitch_batch_noalloc_dev(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const void *d_in, void *d_out, uint32_t batch) {
+    REQUIRE(ctx && ksk && (batch == 0 || (d_in && d_out)), "keyswitch_batch_noalloc_dev: null argument");
+    REQUIRE(ksk->ctx == ctx, "key handle belongs to another context");
+    REQUIRE(ksk->finalized, "keyswitch: key not finalized (call b200tfhe_ksk_finalize after filling the device buffer)");
+    REQUIRE(ksk->tk.d_planes, "keyswitch_batch_noalloc_dev: this key has no tensor-core byte planes; b200tfhe_keyswitch_batch_dev "
+                              "runs the CUDA-core kernel for it, which needs no scratch");
+    const Params &p = ksk->p;
+    const size_t max_batch = NOALLOC_KS_SCRATCH_BYTES / ksk->tk.kp;
+    REQUIRE((size_t)batch <= max_batch,
+            "keyswitch_batch_noalloc_dev: batch " + std::to_string(batch) + " needs " + std::to_string((size_t)batch * ksk->tk.kp) +
+                " bytes of digit scratch, the fixed device array holds " + std::to_string((size_t)NOALLOC_KS_SCRATCH_BYTES) +
+                " (at most " + std::to_string(max_batch) + " ciphertexts per call for this key)");
+    if (batch == 0) return 0;
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    KSLaunch a{d_in, big_len(p), d_out, small_len(p), ksk->d_ksk, ksk->d_colsum, p.k * p.N, p.n, p.ks_level, p.ks_base_log, p.bits, (int)batch};
+    a.body_col = ksk->body_col;
+    a.sub = ksk->sub;
+    a.sub_bits = ksk->sub_bits;
+    cudaError_t ce = cudaSuccess;
+    const int rc = ks_tc_noalloc_launch(a, ksk->tk, ctx->device, ctx->stream, &ce);
+    if (rc == -12) return fail_cuda(ctx, "cudaGetSymbolAddress(noalloc keyswitch scratch)", ce);
+    if (rc) return fail(ctx, "keyswitch (noalloc) launch failed: " + std::to_string(rc));
+    ctx->launches += 2;
+    return 0;
+}
 int b200tfhe_pbs_batch_dev(b200tfhe_context *ctx, const b200tfhe_bsk *bsk, const void *d_in, void *d_out, const void *d_luts,
                            const uint32_t *d_idx, uint32_t batch) {
     REQUIRE(ctx && bsk && (batch == 0 || (d_in && d_out && d_luts)), "pbs_batch_dev: null argument");

@@ -106,6 +106,10 @@ int ks_expand_rows_launch(const void *src, void *expanded, size_t n_in, int leve
                           cudaStream_t st);
 int ks_tc_launch(const KSLaunch &a, const KSTensorKey &tk, void *digits, cudaStream_t st);   // digits: batch * kp bytes of scratch
 
+// noalloc.cu: the same two launches with the digit scratch in a file-scope __device__ array (no cudaMalloc anywhere on the path)
+constexpr size_t NOALLOC_KS_SCRATCH_BYTES = (size_t)4 << 20;   // == B200TFHE_NOALLOC_KS_SCRATCH_BYTES of the public header
+int ks_tc_noalloc_launch(const KSLaunch &a, const KSTensorKey &tk, int device, cudaStream_t st, cudaError_t *cuda_err);
+
 // wave_kernels.cu (device-resident waves over a ciphertext pool); WaveOp is layout-identical to b200tfhe_wave_op
 struct WaveOp {
     uint32_t dst;
