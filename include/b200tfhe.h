@@ -65,6 +65,17 @@ int b200tfhe_synchronize(b200tfhe_context *ctx);
 const char *b200tfhe_last_error(const b200tfhe_context *ctx);
 /* the context's CUDA stream as a cudaStream_t cast to void* (for callers that interleave their own work) */
 void *b200tfhe_context_stream(b200tfhe_context *ctx);
+/* Tuning / test knobs of one context (they replace the environment switches of earlier builds; production needs none):
+ *   "br_kernel"       0 auto (default) | 1 generic multi-ciphertext kernel | 2 tensor-memory kernel (N 2048, k 1, l 1) |
+ *                     3 one-ciphertext-per-SM latency kernel | 4 generic kernel, one ciphertext per CTA | 5 warp-specialised
+ *                     experiment (only in a `make WS=1` build).  A kernel that is not built for the key's parameter set makes
+ *                     the blind rotation fail with an error -- the parity tests run every kernel on the same inputs this way.
+ *   "lat_max"         largest batch that runs on the latency kernel in auto mode (default 296 = 2 x 148 SMs; 0 = never)
+ *   "ks_tensor_core"  0: use the CUDA-core keyswitch even where the tensor-core key planes exist (default 1)
+ *   "ks_tc_min"       smallest batch on the tensor-core keyswitch (default 1)
+ *   "chunk_min"       minimum chunk (ciphertexts) of the H2D / compute / D2H pipeline of host-pointer calls (default 3552; 0 = off)
+ * Unknown keys and out-of-range values are errors. */
+int b200tfhe_context_set_option(b200tfhe_context *ctx, const char *key, int64_t value);
 /* 1 if blind rotation is implemented for this parameter set on this build, else 0 */
 int b200tfhe_params_supported(const b200tfhe_params *p);
 
@@ -154,6 +165,25 @@ int b200tfhe_pbs_ks_batch_u64(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, co
                               uint64_t *out, const uint64_t *luts, uint32_t n_luts, const uint32_t *lut_idx, uint32_t batch);
 int b200tfhe_pbs_ks_batch_u32(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, const uint32_t *in,
                               uint32_t *out, const uint32_t *luts, uint32_t n_luts, const uint32_t *lut_idx, uint32_t batch);
+
+/* add_external_product_assign(_mem_optimized) (algorithms/lwe_programmable_bootstrapping.rs:309-475 ->
+ * fft_impl/fft64/crypto/ggsw.rs:477-598) over a list:  out[b] <- out[b] + ggsw[ggsw_idx[b]] (x) glwe[b].
+ * The FourierGgswCiphertext list is a bootstrap-key handle (a classic LweBootstrapKey IS a list of lwe_dimension GGSW
+ * ciphertexts, entities/lwe_bootstrap_key.rs:99-106): upload stand-alone GGSWs with b200tfhe_bsk_upload_* and
+ * p->lwe_dimension = their count.  ggsw_idx[b] < lwe_dimension selects ciphertext b's GGSW (NULL: all use GGSW 0).
+ * out (read and written) and glwe: batch x (k+1)N.  This is one blind-rotation iteration without the rotate-and-subtract;
+ * the result differs from the reference's f64 path only by FFT rounding (per-CMUX bound). */
+int b200tfhe_external_product_batch_u64(b200tfhe_context *ctx, const b200tfhe_bsk *ggsw, const uint32_t *ggsw_idx, uint64_t *out,
+                                        const uint64_t *glwe, uint32_t batch);
+int b200tfhe_external_product_batch_u32(b200tfhe_context *ctx, const b200tfhe_bsk *ggsw, const uint32_t *ggsw_idx, uint32_t *out,
+                                        const uint32_t *glwe, uint32_t batch);
+/* cmux_assign(_mem_optimized) (lwe_programmable_bootstrapping.rs:552-765 -> ggsw.rs:766-777) over a list, both operands
+ * updated exactly as the reference updates them:  ct1[b] <- ct1[b] - ct0[b];  ct0[b] <- ct0[b] + ggsw[ggsw_idx[b]] (x) ct1[b]
+ * (ct0 then encrypts ct1's old message where the GGSW encrypts 1, its own where it encrypts 0). */
+int b200tfhe_cmux_batch_u64(b200tfhe_context *ctx, const b200tfhe_bsk *ggsw, const uint32_t *ggsw_idx, uint64_t *ct0, uint64_t *ct1,
+                            uint32_t batch);
+int b200tfhe_cmux_batch_u32(b200tfhe_context *ctx, const b200tfhe_bsk *ggsw, const uint32_t *ggsw_idx, uint32_t *ct0, uint32_t *ct1,
+                            uint32_t batch);
 
 /* boolean binary gate over a list (boolean/engine/mod.rs:607-798 + Bootstrapper::apply_bootstrapping_pattern,
  * engine/bootstrapping.rs:392-401): linear combination, then PBS->KS (pbs_first != 0, DEFAULT_PARAMETERS) or

@@ -250,6 +250,72 @@ class Oracle:
         return self._batch(lambda *a: L.orc_pbs_batch(C.byref(self.p), _p(self.fbsk), *a, 1 if sample_extract else 0),
                            cts, luts, lut_idx, self.n + 1, od)
 
+    def blind_rotate(self, cts, luts, lut_idx=None):
+        """blind_rotate_assign over a list: the rotated GLWE accumulators (no sample extraction)."""
+        return self.pbs(cts, luts, lut_idx, sample_extract=False)
+
+    def ggsw_fourier(self, index):
+        """Fourier GGSW `index` of the bootstrap key, [l][k+1][k+1][N doubles]."""
+        sz = self.l * (self.k + 1) ** 2 * self.N
+        return self.fbsk[index * sz:(index + 1) * sz]
+
+    def add_external_product(self, out, ggsw_index, glwe):
+        """add_external_product_assign (fft64/crypto/ggsw.rs:477-598): returns out + ggsw[ggsw_index] (x) glwe, one GGSW index per ciphertext."""
+        out, glwe = u64(out).reshape(-1, self.glwe_len).copy(), u64(glwe).reshape(-1, self.glwe_len)
+        idx = np.broadcast_to(np.asarray(ggsw_index, dtype=np.int64), (out.shape[0],))
+        for b in range(out.shape[0]):
+            g = np.ascontiguousarray(self.ggsw_fourier(int(idx[b])))
+            lib().orc_add_external_product(C.byref(self.p), _p(out[b]), _p(g), _p(np.ascontiguousarray(glwe[b])))
+        return out
+
+    def cmux(self, ct0, ct1, ggsw_index):
+        """cmux_assign (ggsw.rs:766-777): ct1 -= ct0; ct0 += ggsw (x) ct1.  Returns the new (ct0, ct1)."""
+        ct0, ct1 = u64(ct0).reshape(-1, self.glwe_len), u64(ct1).reshape(-1, self.glwe_len)
+        d = ct1 - ct0
+        if self.bits == 32:
+            d &= np.uint64(0xFFFFFFFF)
+        return self.add_external_product(ct0, ggsw_index, d), d
+
+    def decompose_all(self, x):
+        """Signed decomposition of every element (commons/math/decomposition/decomposer.rs:99-119, iter.rs:120-127), vectorised:
+        returns [l][...] wrapping digits, index 0 = level l (the first the iterator emits)."""
+        x = u64(x)
+        m = np.uint64((1 << self.bits) - 1 if self.bits < 64 else 0xFFFFFFFFFFFFFFFF)
+        b, L = self.b, self.l
+        shift = np.uint64(self.bits - b * L)
+        one = np.uint64(1)
+        # closest_representable: round to the top b*l bits
+        st = ((((x >> (shift - one)) + one) >> one) << shift) & m
+        st = st >> shift
+        out = []
+        mb = np.uint64((1 << b) - 1)
+        for _ in range(L):
+            res = st & mb
+            st = st >> np.uint64(b)
+            carry = ((((res - one) & m) | st) & res) >> np.uint64(b - 1)
+            st = (st + carry) & m
+            out.append((res - (carry << np.uint64(b))) & m)
+        return np.stack(out)
+
+    def exact_external_product(self, out, ggsw_index, glwe):
+        """out + ggsw (x) glwe in EXACT integer arithmetic mod 2^bits: digits x the STANDARD-domain key, schoolbook negacyclic
+        products (the helper of the reference's own FFT test, fft/tests.rs:83-100) -- no FFT anywhere."""
+        k1, N, L = self.k + 1, self.N, self.l
+        out = u64(out).reshape(k1, N).copy()
+        glwe = u64(glwe).reshape(k1, N)
+        g = self.bsk.reshape(-1, L, k1, k1, N)[ggsw_index]
+        digs = self.decompose_all(glwe)                      # [l][k1][N], index 0 = level l
+        m = np.uint64((1 << self.bits) - 1 if self.bits < 64 else 0xFFFFFFFFFFFFFFFF)
+        tmp = np.zeros(N, np.uint64)
+        for t in range(L):
+            lvl = L - 1 - t                                   # key levels stored 1..l
+            for r in range(k1):
+                d = np.ascontiguousarray(digs[t, r])
+                for j in range(k1):
+                    lib().orc_negacyclic_schoolbook(N, _p(d), _p(np.ascontiguousarray(g[lvl, r, j])), _p(tmp), self.bits)
+                    out[j] = (out[j] + tmp) & m
+        return out.reshape(-1)
+
     def gate_prologue(self, gate, a, b):
         a, b = u64(a).reshape(-1, self.n + 1), u64(b).reshape(-1, self.n + 1)
         out = np.zeros_like(a)

@@ -48,3 +48,14 @@ def phase_bound(o):
     # n (not n/2): upper bound over the secret key's Hamming weight, which matters for the toy sets with n ~ 10
     var = o.n * (1.0 + o.k * o.N / 2.0) * 2.0 ** (-2 * o.b * o.l) / 12.0
     return 8.0 * (2.0 * var) ** 0.5
+
+
+def fft_bound(o):
+    """Per-coefficient bound, in units of the torus LSB, on the difference of two f64 evaluations (different operation order) of ONE
+    external product: |digit| <= B/2 times key values in [-1/2, 1/2), a random walk over the (k+1) l N terms, relative error 2^-53
+    per operation; 16x head-room for the ~log2(N) butterfly levels and the maximum over all coefficients.  That is 2^-22 of the
+    torus (2^42 LSBs) at PARAM_MESSAGE_2_CARRY_2 -- measured maximum 2^-24.4 -- and at least one LSB.  The reference's own
+    acceptance threshold for one FFT product (fft/tests.rs:166-167: 2^(BITS - (52 - magnitude - log2 N))) is 2^46 there."""
+    terms = (o.k + 1) * o.l * o.N
+    est = 2.0 ** (o.b - 1) * 0.5 * terms ** 0.5 * 2.0 ** -53
+    return max(1.0, 16.0 * est * 2.0 ** o.bits)

@@ -131,3 +131,35 @@ def test_boolean_truth_tables():
     for gate, want in truth.items():
         out = o.pbs_ks(o.gate_prologue(gate, ca, cb), o.boolean_lut())
         assert np.array_equal(o.decode_bool(o.phase(out, "small")), want), gate
+
+
+@pytest.mark.parametrize("name", ["TOY_2_2", "TOY_U64", "TOY_U32", "TOY_1_1"])
+def test_oracle_external_product_vs_exact_integer_product(name):
+    """The oracle's add_external_product (f64 FFT, the reference's operation order) against the EXACT result: digits x the
+    standard-domain key by schoolbook negacyclic products in wrapping integer arithmetic, no FFT (the reference's own
+    convolution_naive, fft/tests.rs:83-100).  Threshold: the reference's (fft/tests.rs:166-167) summed over the (k+1) l products,
+    and the tighter per-CMUX bound the GPU tests use (conftest.fft_bound)."""
+    from conftest import fft_bound, get_oracle
+    o = get_oracle(name)
+    rng = np.random.default_rng(0xE1)
+    for gi in (0, o.n - 1):
+        acc = rng.integers(0, 2 ** o.bits, size=o.glwe_len, dtype=np.uint64)
+        glwe = rng.integers(0, 2 ** o.bits, size=o.glwe_len, dtype=np.uint64)
+        got = o.add_external_product(acc, gi, glwe)[0]
+        exact = o.exact_external_product(acc, gi, glwe)
+        d = (got - exact)
+        if o.bits == 32:
+            d = (d & np.uint64(0xFFFFFFFF)).astype(np.uint32).astype(np.int32).astype(np.int64)
+        else:
+            d = d.astype(np.int64)
+        log2n = o.N.bit_length() - 1
+        ref_threshold = (o.k + 1) * o.l * 2.0 ** max(0, o.bits - (52 - o.b - log2n))
+        assert np.abs(d).max() <= ref_threshold
+        assert np.abs(d).max() <= fft_bound(o), (np.abs(d).max(), fft_bound(o))
+    # the vectorised decomposition used above is the KAT-pinned one
+    x = rng.integers(0, 2 ** o.bits, size=64, dtype=np.uint64)
+    digs = o.decompose_all(x)
+    for i, v in enumerate(x):
+        out = np.zeros(o.l, np.uint64)
+        lib().orc_decompose(C.c_uint64(int(v)), o.b, o.l, o.bits, _p(out))
+        assert np.array_equal(digs[:, i], out)

@@ -28,6 +28,7 @@ _PROTOS = {
     "b200tfhe_synchronize": [_VP],
     "b200tfhe_last_error": [_VP],
     "b200tfhe_context_stream": [_VP],
+    "b200tfhe_context_set_option": [_VP, C.c_char_p, C.c_int64],
     "b200tfhe_params_supported": [C.POINTER(Params)],
     "b200tfhe_bsk_upload_u64": [_VP, C.POINTER(Params), _VP, _PP],
     "b200tfhe_bsk_upload_u32": [_VP, C.POINTER(Params), _VP, _PP],
@@ -81,6 +82,8 @@ for _s in ("u64", "u32"):
     _PROTOS[f"b200tfhe_blind_rotate_batch_{_s}"] = [_VP, _VP, _VP, _VP, _VP, _U32, _VP, _U32]
     _PROTOS[f"b200tfhe_ks_pbs_batch_{_s}"] = [_VP, _VP, _VP, _VP, _VP, _VP, _U32, _VP, _U32]
     _PROTOS[f"b200tfhe_pbs_ks_batch_{_s}"] = [_VP, _VP, _VP, _VP, _VP, _VP, _U32, _VP, _U32]
+    _PROTOS[f"b200tfhe_external_product_batch_{_s}"] = [_VP, _VP, _VP, _VP, _VP, _U32]
+    _PROTOS[f"b200tfhe_cmux_batch_{_s}"] = [_VP, _VP, _VP, _VP, _VP, _U32]
     _PROTOS[f"b200tfhe_modulus_switch_{_s}"] = [_VP, _VP, _VP, _SZ, _U32]
     _PROTOS[f"b200tfhe_sample_extract_batch_{_s}"] = [_VP, _VP, _VP, _U32, _U32, _U32]
 _RESTYPES = {"b200tfhe_last_error": C.c_char_p, "b200tfhe_context_stream": C.c_void_p, "b200tfhe_launch_count": C.c_uint64,

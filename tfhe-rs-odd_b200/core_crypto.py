@@ -53,6 +53,10 @@ class Context:
     def synchronize(self):
         self.check(self._lib.b200tfhe_synchronize(self._h))
 
+    def set_option(self, key, value):
+        """Tuning / test knob of this context (b200tfhe_context_set_option): "br_kernel", "lat_max", "ks_tensor_core", "ks_tc_min", "chunk_min"."""
+        self.check(self._lib.b200tfhe_context_set_option(self._h, key.encode(), int(value)))
+
     @property
     def stream(self):
         return self._lib.b200tfhe_context_stream(self._h)
@@ -298,6 +302,48 @@ def blind_rotate_assign(input_lwe, accumulator_glwe, fourier_bsk):
     res = programmable_bootstrap_lwe_ciphertext_without_sample_extract(a, luts, fourier_bsk, np.arange(a.shape[0], dtype=np.uint32))
     acc[...] = res.reshape(acc.shape)
     return acc
+
+
+def _ggsw_idx(ggsw_idx, batch):
+    if ggsw_idx is None:
+        return None
+    return np.ascontiguousarray(np.broadcast_to(np.asarray(ggsw_idx, dtype=np.uint32), (batch,)))
+
+
+def add_external_product_assign(out, ggsw, glwe, ggsw_idx=None):
+    """out <- out + ggsw (x) glwe (algorithms/lwe_programmable_bootstrapping.rs:309-475), in place over a list.
+
+    ggsw: a FourierLweBootstrapKey used as a list of lwe_dimension Fourier GGSW ciphertexts; ggsw_idx selects one per
+    ciphertext (scalar or array; None = GGSW 0)."""
+    p, ctx = ggsw.params, ggsw.ctx
+    w = (p.glwe_dimension + 1) * p.polynomial_size
+    dt = _dtype(p.torus_bits)
+    if not (isinstance(out, np.ndarray) and out.dtype == dt and out.flags.c_contiguous and out.size % w == 0):
+        raise B200TfheError(f"external product output must be a contiguous {dt.__name__} array of whole GLWE ciphertexts")
+    g, _ = _as_list(glwe, w, p.torus_bits, "external-product input")
+    batch = out.size // w
+    if g.shape[0] != batch:
+        raise B200TfheError("external product: out and glwe hold different numbers of ciphertexts")
+    fn = getattr(ctx._lib, f"b200tfhe_external_product_batch_{_suf(p.torus_bits)}")
+    ctx.check(fn(ctx._h, ggsw._h, _ptr(_ggsw_idx(ggsw_idx, batch)), _ptr(out), _ptr(g), batch))
+    return out
+
+
+def cmux_assign(ct0, ct1, ggsw, ggsw_idx=None):
+    """cmux_assign (lwe_programmable_bootstrapping.rs:552-765 -> ggsw.rs:766-777), in place over a list, both operands updated as
+    the reference updates them: ct1 <- ct1 - ct0, ct0 <- ct0 + ggsw (x) ct1."""
+    p, ctx = ggsw.params, ggsw.ctx
+    w = (p.glwe_dimension + 1) * p.polynomial_size
+    dt = _dtype(p.torus_bits)
+    for a in (ct0, ct1):
+        if not (isinstance(a, np.ndarray) and a.dtype == dt and a.flags.c_contiguous and a.size % w == 0):
+            raise B200TfheError(f"cmux operands must be contiguous {dt.__name__} arrays of whole GLWE ciphertexts")
+    if ct0.size != ct1.size:
+        raise B200TfheError("cmux: ct0 and ct1 hold different numbers of ciphertexts")
+    batch = ct0.size // w
+    fn = getattr(ctx._lib, f"b200tfhe_cmux_batch_{_suf(p.torus_bits)}")
+    ctx.check(fn(ctx._h, ggsw._h, _ptr(_ggsw_idx(ggsw_idx, batch)), _ptr(ct0), _ptr(ct1), batch))
+    return ct0, ct1
 
 
 def keyswitch_programmable_bootstrap(ksk, fourier_bsk, input_lwe, accumulator, lut_idx=None):

@@ -54,6 +54,12 @@ struct b200tfhe_context {
     enum { MAX_CHUNKS = 8 };
     cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
     cudaEvent_t ev_in[MAX_CHUNKS] = {}, ev_done[MAX_CHUNKS] = {}, ev_start = nullptr;
+    // tuning / test knobs (b200tfhe_context_set_option); the defaults are what production uses
+    int opt_br_kernel = BR_AUTO;     // which blind-rotation kernel (kernels.h: BR_AUTO .. BR_WS)
+    int opt_lat_max = 2 * 148;       // largest batch on the one-ciphertext-per-SM latency kernel
+    int opt_ks_tensor_core = 1;      // 0: CUDA-core keyswitch even where the tensor-core planes exist
+    int opt_ks_tc_min = 1;           // smallest batch on the tensor-core keyswitch
+    uint32_t opt_chunk_min = 6 * 592;   // minimum chunk of the H2D / compute / D2H pipeline of host-pointer calls (0: off)
 };
 struct b200tfhe_bsk {
     b200tfhe_context *ctx;
@@ -61,6 +67,7 @@ struct b200tfhe_bsk {
     void *d_fourier;
     size_t bytes;
     int grouping = 0;    // 0: classic key (one GGSW per mask element); G >= 2: multi-bit key, 2^G GGSWs per G elements
+    int device = 0;      // copied from the context: *_destroy must not dereference a context that may already be gone
 };
 struct b200tfhe_ksk {
     b200tfhe_context *ctx;
@@ -71,6 +78,7 @@ struct b200tfhe_ksk {
     KSTensorKey tk;      // byte-plane copy of the key for the tensor-core path (d_planes == nullptr: not available)
     int body_col = -1;   // output column receiving the input body (-1: the last one); k*N for a packing keyswitch key
     int sub = 1, sub_bits = 0;   // base_log > 7: every digit split exactly into `sub` int8 sub-digits (KSLaunch::sub), tensor-core path only
+    int device = 0;
 };
 // LwePackingKeyswitchKey: the same integer GEMM with (k+1)N output columns and the body on coefficient 0 of the body polynomial
 struct b200tfhe_pksk {
@@ -187,6 +195,30 @@ int b200tfhe_synchronize(b200tfhe_context *ctx) {
 void *b200tfhe_context_stream(b200tfhe_context *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
 uint64_t b200tfhe_launch_count(const b200tfhe_context *ctx) { return ctx ? ctx->launches : 0; }
 
+int b200tfhe_context_set_option(b200tfhe_context *ctx, const char *key, int64_t value) {
+    REQUIRE(ctx && key, "context_set_option: null argument");
+    std::lock_guard<std::mutex> g(ctx->mu);
+    const std::string k(key);
+    if (k == "br_kernel") {
+        REQUIRE(value >= BR_AUTO && value <= BR_WS, "context_set_option: br_kernel must be 0 (auto) .. 5");
+        ctx->opt_br_kernel = (int)value;
+    } else if (k == "lat_max") {
+        REQUIRE(value >= 0 && value <= (1 << 20), "context_set_option: lat_max out of range");
+        ctx->opt_lat_max = (int)value;
+    } else if (k == "ks_tensor_core") {
+        ctx->opt_ks_tensor_core = value != 0;
+    } else if (k == "ks_tc_min") {
+        REQUIRE(value >= 0, "context_set_option: ks_tc_min must be >= 0");
+        ctx->opt_ks_tc_min = (int)value;
+    } else if (k == "chunk_min") {
+        REQUIRE(value >= 0 && value <= 0xFFFFFFFFll, "context_set_option: chunk_min out of range");
+        ctx->opt_chunk_min = (uint32_t)value;
+    } else {
+        return fail(ctx, "context_set_option: unknown option \"" + k + "\"");
+    }
+    return 0;
+}
+
 int b200tfhe_params_supported(const b200tfhe_params *p) {
     if (!p) return 0;
     return br_supported(to_params(p)) != 0;
@@ -233,6 +265,7 @@ static int bsk_alloc(b200tfhe_context *ctx, const b200tfhe_params *pp, int group
     std::lock_guard<std::mutex> g(ctx->mu);
     CK(cudaSetDevice(ctx->device));
     b200tfhe_bsk *k = new b200tfhe_bsk{ctx, p, nullptr, bsk_polys(p, grouping) * (p.N / 2) * sizeof(cplx), grouping};
+    k->device = ctx->device;
     cudaError_t e = cudaMalloc(&k->d_fourier, k->bytes);
     if (e != cudaSuccess) { delete k; return fail_cuda(ctx, "cudaMalloc(bsk)", e); }
     *out = k;
@@ -337,7 +370,7 @@ int b200tfhe_bsk_device_buffer(const b200tfhe_bsk *bsk, void **d_ptr, size_t *by
 }
 int b200tfhe_bsk_destroy(b200tfhe_bsk *bsk) {
     if (!bsk) return 0;
-    cudaSetDevice(bsk->ctx->device);
+    cudaSetDevice(bsk->device);
     cudaFree(bsk->d_fourier);
     delete bsk;
     return 0;
@@ -352,6 +385,7 @@ int b200tfhe_ksk_alloc(b200tfhe_context *ctx, const b200tfhe_params *pp, b200tfh
     CK(cudaSetDevice(ctx->device));
     size_t bytes = (size_t)p.k * p.N * p.ks_level * small_len(p) * sz(p);
     b200tfhe_ksk *k = new b200tfhe_ksk{ctx, p, nullptr, nullptr, bytes, false, {}};
+    k->device = ctx->device;
     cudaError_t e = cudaMalloc(&k->d_ksk, bytes);
     if (e == cudaSuccess) e = cudaMalloc(&k->d_colsum, small_len(p) * sz(p));
     if (e != cudaSuccess) { cudaFree(k->d_ksk); delete k; return fail_cuda(ctx, "cudaMalloc(ksk)", e); }
@@ -388,7 +422,7 @@ int b200tfhe_ksk_finalize(b200tfhe_context *ctx, b200tfhe_ksk *k) {
     rc = ks_colsum_launch(k->d_ksk, k->d_colsum, k->p.k * k->p.N, k->p.n, k->p.ks_level, k->p.ks_base_log, k->p.bits, ctx->stream);
     ctx->launches++;
     if (rc) return fail(ctx, "ks_colsum launch failed: " + std::to_string(rc));
-    if (!getenv("B200TFHE_NO_KS_TC") && ks_tc_supported(k->p.bits, n_in, k->p.n, k->p.ks_level, k->p.ks_base_log)) {
+    if (ks_tc_supported(k->p.bits, n_in, k->p.n, k->p.ks_level, k->p.ks_base_log)) {
         if (k->tk.d_planes) { cudaFree(k->tk.d_planes); k->tk.d_planes = nullptr; }
         void *planes = nullptr;
         CK(cudaMalloc(&planes, ks_tc_key_bytes(k->p.bits, n_in, k->p.n, k->p.ks_level)));
@@ -420,7 +454,7 @@ int b200tfhe_ksk_device_buffer(const b200tfhe_ksk *ksk, void **d_ptr, size_t *by
 }
 int b200tfhe_ksk_destroy(b200tfhe_ksk *ksk) {
     if (!ksk) return 0;
-    cudaSetDevice(ksk->ctx->device);
+    cudaSetDevice(ksk->device);
     cudaFree(ksk->d_ksk);
     cudaFree(ksk->d_colsum);
     if (ksk->tk.d_planes) cudaFree(ksk->tk.d_planes);
@@ -438,9 +472,8 @@ static int ks_dev_locked(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const v
     a.body_col = ksk->body_col;
     a.sub = ksk->sub;
     a.sub_bits = ksk->sub_bits;
-    static const int tc_min = getenv("B200TFHE_KS_TC_MIN") ? atoi(getenv("B200TFHE_KS_TC_MIN")) : 1;
     int rc;
-    if (ksk->tk.d_planes && ((int)batch >= tc_min || ksk->sub > 1)) {
+    if (ksk->tk.d_planes && (((int)batch >= ctx->opt_ks_tc_min && ctx->opt_ks_tensor_core) || ksk->sub > 1)) {
         void *digits = nullptr;
         CK(ctx->ws.get(Workspace::DIG, (size_t)batch * ksk->tk.kp, &digits));
         rc = ks_tc_launch(a, ksk->tk, digits, ctx->stream);
@@ -458,8 +491,11 @@ static int br_dev_locked(b200tfhe_context *ctx, const b200tfhe_bsk *bsk, const v
     int R = bsk_radix(p, bsk->grouping);
     BRLaunch a{d_in, small_len(p), d_luts, d_idx, bsk->d_fourier, d_out, mode == BR_MODE_GLWE ? glwe_len(p) : big_len(p),
                p.n, (int)batch, mode, tw_fwd(ctx, R), tw_inv(ctx, R)};
+    a.force = ctx->opt_br_kernel;
+    a.lat_max = ctx->opt_lat_max;
     int rc = bsk->grouping ? br_mb_launch(p, bsk->grouping, a, ctx->stream) : br_launch(p, a, ctx->stream);
     ctx->launches++;
+    if (rc == -2) return fail(ctx, "blind_rotate: the kernel selected with option \"br_kernel\" is not built for this parameter set");
     if (rc) return fail(ctx, "blind_rotate launch failed: " + std::to_string(rc));
     return 0;
 }
@@ -613,7 +649,7 @@ static int host_op(b200tfhe_context *ctx, Op op, const b200tfhe_ksk *ksk, const 
     if (op == OP_PBS_KS) CK(ctx->ws.get(Workspace::MID, batch * big_len(p) * s, &d_mid));
 
     // chunking: only when every chunk still fills the GPU for several waves (unit = 4 ciphertexts x 148 SMs)
-    static const uint32_t min_chunk = getenv("B200TFHE_CHUNK_MIN") ? (uint32_t)atoi(getenv("B200TFHE_CHUNK_MIN")) : 6 * 592;
+    const uint32_t min_chunk = ctx->opt_chunk_min;
     uint32_t n_chunks = 1, chunk = batch;
     if (batch >= 2 * min_chunk && min_chunk > 0) {
         n_chunks = batch / min_chunk;
@@ -691,6 +727,60 @@ extern "C" {
 HOST_OPS(u64, uint64_t, 64)
 HOST_OPS(u32, uint32_t, 32)
 #undef HOST_OPS
+
+// add_external_product_assign / cmux_assign over a list (a10): host buffers staged through the workspace, one CTA per ciphertext
+static int external_product_host(b200tfhe_context *ctx, const b200tfhe_bsk *ggsw, const uint32_t *idx, void *out, void *src, uint32_t batch,
+                                 int cmux, int bits) {
+    REQUIRE(ctx && ggsw, "external_product: null argument");
+    REQUIRE(ggsw->ctx == ctx, "key handle belongs to another context");
+    REQUIRE(ggsw->grouping == 0, "external_product: a multi-bit bootstrap key is not a GGSW list");
+    const Params &p = ggsw->p;
+    REQUIRE(p.bits == bits, "torus width of the GGSW list does not match the entry point");
+    const int R = external_product_supported(p);
+    REQUIRE(R != 0, "external product is not built for this (N, k, level, base_log, bits) set");
+    if (batch == 0) return 0;
+    REQUIRE(out && src, "null ciphertext buffer");
+    if (idx)
+        for (uint32_t i = 0; i < batch; i++) REQUIRE(idx[i] < (uint32_t)p.n, "ggsw_idx out of range");
+    const size_t bytes = (size_t)batch * glwe_len(p) * sz(p);
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    void *d_out, *d_src, *d_idx = nullptr;
+    CK(ctx->ws.get(Workspace::OUT, bytes, &d_out));
+    CK(ctx->ws.get(Workspace::IN, bytes, &d_src));
+    CK(cudaMemcpyAsync(d_out, out, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d_src, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    if (idx) {
+        CK(ctx->ws.get(Workspace::IDX, (size_t)batch * 4, &d_idx));
+        CK(cudaMemcpyAsync(d_idx, idx, (size_t)batch * 4, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    const int rc = external_product_launch(p, d_out, d_src, ggsw->d_fourier, (const uint32_t *)d_idx, cmux, (int)batch, tw_fwd(ctx, R),
+                                           tw_inv(ctx, R), ctx->stream);
+    ctx->launches++;
+    if (rc) {
+        cudaStreamSynchronize(ctx->stream);
+        return fail(ctx, "external_product launch failed: " + std::to_string(rc));
+    }
+    cudaError_t e = cudaMemcpyAsync(out, d_out, bytes, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess && cmux) e = cudaMemcpyAsync(src, d_src, bytes, cudaMemcpyDeviceToHost, ctx->stream);
+    cudaError_t es = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess || es != cudaSuccess) return fail_cuda(ctx, "external_product", e != cudaSuccess ? e : es);
+    return 0;
+}
+int b200tfhe_external_product_batch_u64(b200tfhe_context *ctx, const b200tfhe_bsk *g, const uint32_t *idx, uint64_t *out, const uint64_t *glwe,
+                                        uint32_t batch) {
+    return external_product_host(ctx, g, idx, out, const_cast<uint64_t *>(glwe), batch, 0, 64);
+}
+int b200tfhe_external_product_batch_u32(b200tfhe_context *ctx, const b200tfhe_bsk *g, const uint32_t *idx, uint32_t *out, const uint32_t *glwe,
+                                        uint32_t batch) {
+    return external_product_host(ctx, g, idx, out, const_cast<uint32_t *>(glwe), batch, 0, 32);
+}
+int b200tfhe_cmux_batch_u64(b200tfhe_context *ctx, const b200tfhe_bsk *g, const uint32_t *idx, uint64_t *ct0, uint64_t *ct1, uint32_t batch) {
+    return external_product_host(ctx, g, idx, ct0, ct1, batch, 1, 64);
+}
+int b200tfhe_cmux_batch_u32(b200tfhe_context *ctx, const b200tfhe_bsk *g, const uint32_t *idx, uint32_t *ct0, uint32_t *ct1, uint32_t batch) {
+    return external_product_host(ctx, g, idx, ct0, ct1, batch, 1, 32);
+}
 
 int b200tfhe_gate_batch_u32(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, int gate, int pbs_first,
                             const uint32_t *a, const uint32_t *b, uint32_t *out, uint32_t batch) {
@@ -973,6 +1063,7 @@ struct b200tfhe_pfpksk {
     Params p;
     int base_log, level, sub, sub_bits;
     std::vector<KSTensorKey> keys;
+    int device = 0;
 };
 
 int b200tfhe_cbs_pfpksk_upload_u64(b200tfhe_context *ctx, const b200tfhe_params *pp, uint32_t pfks_base_log, uint32_t pfks_level,
@@ -994,6 +1085,7 @@ int b200tfhe_cbs_pfpksk_upload_u64(b200tfhe_context *ctx, const b200tfhe_params 
     cudaError_t e = cudaMalloc(&d_exp, key_words * sub * 8);
     if (e != cudaSuccess) { cudaFree(d_raw); return fail_cuda(ctx, "cudaMalloc(pfpksk)", e); }
     b200tfhe_pfpksk *h = new b200tfhe_pfpksk{ctx, p, (int)pfks_base_log, (int)pfks_level, sub, sub_bits, {}};
+    h->device = ctx->device;
     h->keys.resize(p.k + 1);
     int rc = 0;
     for (int r = 0; r <= p.k && !rc; r++) {
@@ -1018,7 +1110,7 @@ int b200tfhe_cbs_pfpksk_upload_u64(b200tfhe_context *ctx, const b200tfhe_params 
 }
 int b200tfhe_cbs_pfpksk_destroy(b200tfhe_pfpksk *k) {
     if (!k) return 0;
-    cudaSetDevice(k->ctx->device);
+    cudaSetDevice(k->device);
     for (auto &t : k->keys) if (t.d_planes) cudaFree(t.d_planes);
     delete k;
     return 0;
@@ -1201,6 +1293,7 @@ struct b200tfhe_pool {
     void *d_slots = nullptr, *d_luts = nullptr, *d_ops = nullptr, *d_staging = nullptr, *d_mid = nullptr, *d_out = nullptr;
     uint32_t *d_idx = nullptr;
     uint32_t n_luts = 0, ops_cap = 0;
+    int device = 0;
 };
 
 int b200tfhe_pool_create(b200tfhe_context *ctx, const b200tfhe_params *pp, int big, uint32_t capacity, b200tfhe_pool **out) {
@@ -1212,6 +1305,7 @@ int b200tfhe_pool_create(b200tfhe_context *ctx, const b200tfhe_params *pp, int b
     std::lock_guard<std::mutex> g(ctx->mu);
     CK(cudaSetDevice(ctx->device));
     b200tfhe_pool *pl = new b200tfhe_pool{ctx, p, big != 0, capacity, big ? big_len(p) : small_len(p)};
+    pl->device = ctx->device;
     cudaError_t e = cudaMalloc(&pl->d_slots, (size_t)capacity * pl->len * sz(p));
     if (e != cudaSuccess) { delete pl; return fail_cuda(ctx, "cudaMalloc(pool)", e); }
     cudaMemsetAsync(pl->d_slots, 0, (size_t)capacity * pl->len * sz(p), ctx->stream);
@@ -1220,8 +1314,8 @@ int b200tfhe_pool_create(b200tfhe_context *ctx, const b200tfhe_params *pp, int b
 }
 int b200tfhe_pool_destroy(b200tfhe_pool *pl) {
     if (!pl) return 0;
-    cudaSetDevice(pl->ctx->device);
-    cudaStreamSynchronize(pl->ctx->stream);
+    cudaSetDevice(pl->device);
+    cudaDeviceSynchronize();     // not the context's stream: the context may already be destroyed
     for (void *q : {pl->d_slots, pl->d_luts, pl->d_ops, pl->d_staging, pl->d_mid, pl->d_out, (void *)pl->d_idx})
         if (q) cudaFree(q);
     delete pl;

@@ -214,27 +214,31 @@ int br_supported(const Params &p) {
 
 int br_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
     if (a.batch <= 0) return 0;
-    static const bool no_tmem = getenv("B200TFHE_NO_TMEM") != nullptr;   // A/B switch for profiling
-    static const bool force_tmem = getenv("B200TFHE_FORCE_TMEM") != nullptr;   // tests: exercise the TMEM kernel on small batches
-    static const bool use_ws = getenv("B200TFHE_WS") != nullptr;               // warp-specialised variant (experimental)
     // Measured on one B200 at PARAM_MESSAGE_2_CARRY_2 (tools/sweep_small_batches.sh): up to two ciphertexts per SM the
     // one-ciphertext-per-CTA latency kernel wins (148: 2.8 ms, 296: 5.6 ms); from there one wave of the TMEM kernel
     // (4 ciphertexts per CTA, 7.4 ms for anything up to 592) beats both it and the generic kernel.
-    static const int lat_max = getenv("B200TFHE_LAT_MAX") ? atoi(getenv("B200TFHE_LAT_MAX")) : 2 * 148;
     const bool per_ct_key = a.bsk_ct_stride != 0;   // only the generic kernel indexes the key per ciphertext
-    const bool lat = !per_ct_key && !force_tmem && a.batch <= lat_max && br_lat_supported(p);
-    if (per_ct_key) {
+    if (per_ct_key || a.force == BR_GENERIC) {
 #define X(T, R, K, L, BL, CTS) \
     if (p.bits == (int)sizeof(T) * 8 && p.N == 2 * R * R && p.k == K && p.pbs_level == L && p.pbs_base_log == BL) \
         return launch_br<T, R, K, L, BL, CTS>(a, st);
         BR_INSTANCES(X)
 #undef X
-        return -1;
+        return per_ct_key ? -1 : br_big_launch(p, a, st);
     }
-    if (!lat && use_ws && br_ws_supported(p)) return br_ws_launch(p, a, st);
-    if (!lat && !no_tmem && br_tmem_supported(p)) return br_tmem_launch(p, a, st);
-    if (lat) return br_lat_launch(p, a, st);
-    if (a.batch < 3 * 148) {
+    // explicit choices (context option "br_kernel": parity tests exercise every kernel on the same inputs); -2: not built for this set
+    if (a.force == BR_TMEM) return br_tmem_supported(p) ? br_tmem_launch(p, a, st) : -2;
+    if (a.force == BR_LAT) return br_lat_supported(p) ? br_lat_launch(p, a, st) : -2;
+#ifdef B200TFHE_BUILD_WS
+    if (a.force == BR_WS) return br_ws_supported(p) ? br_ws_launch(p, a, st) : -2;
+#else
+    if (a.force == BR_WS) return -2;
+#endif
+    if (a.force == BR_AUTO) {
+        if (a.batch <= a.lat_max && br_lat_supported(p)) return br_lat_launch(p, a, st);
+        if (br_tmem_supported(p)) return br_tmem_launch(p, a, st);
+    }
+    if (a.batch < 3 * 148 || a.force == BR_GENERIC_1CT) {
 #define X(T, R, K, L, BL, CTS) \
     if (p.bits == (int)sizeof(T) * 8 && p.N == 2 * R * R && p.k == K && p.pbs_level == L && p.pbs_base_log == BL) \
         return launch_br<T, R, K, L, BL, CTS>(a, st);

@@ -67,6 +67,21 @@ template <typename T, int K, int L, int BASE_LOG> struct BigCore {
             x[decltype(p)::value] = cplx{int_to_double_scaled<12>(g0), int_to_double_scaled<12>(g1)};   // digits / M
         });
     }
+    // digits of level index tl of the polynomial src_r as it is (stand-alone external product / CMUX: no rotate-and-subtract)
+    HD static void digits_plain_rt(int tid, const T *src_r, int tl, cplx (&x)[P]) {
+        static_for<0, P>([&](auto p) {
+            constexpr int m = brev(decltype(p)::value, LOGP);
+            const int c = tid + TH * m;
+            typedef typename StateWord<T, L * BASE_LOG>::type S;
+            S s0 = (S)decomp_init_state<T>(src_r[c], BASE_LOG, L), s1 = (S)decomp_init_state<T>(src_r[c + M], BASE_LOG, L);
+            int32_t g0 = 0, g1 = 0;
+            static_for<0, L>([&](auto e) {
+                const int32_t e0 = (int32_t)decomp_next_digit<S>(s0, BASE_LOG), e1 = (int32_t)decomp_next_digit<S>(s1, BASE_LOG);
+                if (tl == decltype(e)::value) { g0 = e0; g1 = e1; }
+            });
+            x[decltype(p)::value] = cplx{int_to_double_scaled<12>(g0), int_to_double_scaled<12>(g1)};   // digits / M
+        });
+    }
     // L = 2: both levels' digits from ONE pass over the coefficients; the first (level L) goes to x, the second is packed
     // (two 16-bit digits, |digit| <= 2^(BASE_LOG-1) <= 2^15 - 1 requires BASE_LOG <= 15) for the step that transforms it later
     HD static void digits_both(int tid, const T *acc_r, int a, cplx (&x)[P], uint32_t (&packed)[P]) {

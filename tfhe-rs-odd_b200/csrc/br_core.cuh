@@ -259,4 +259,31 @@ template <typename T, int R, int K, int L, int BASE_LOG> struct BRCore {
     }
 };
 
+// signed decomposition of the polynomial d_r as it is (no rotate-and-subtract) + first forward pass, level by level with the
+// decomposition states of this lane's 2R coefficients in registers (the rolled form of BRCore::digits_fwd_pass1)
+template <typename T, int R, int K, int L, int BL>
+HD void plain_digits_fwd_pass1(int lane, const T *d_r, cplx *fbuf_r, const cplx (*twf)[R]) {
+    typedef BRCore<T, R, K, L, BL> C;
+    typedef typename C::FFT FFT;
+    typedef typename StateWord<T, L * BL>::type S;
+    S s0[R], s1[R];
+    static_for<0, R>([&](auto p) {
+        constexpr int m = brev(decltype(p)::value, FFT::LOGR);
+        const int c = lane + R * m;
+        s0[decltype(p)::value] = (S)decomp_init_state<T>(d_r[c], BL, L);
+        s1[decltype(p)::value] = (S)decomp_init_state<T>(d_r[c + C::M], BL, L);
+    });
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
+    for (int t = 0; t < L; t++) {
+        cplx x[R];
+        static_for<0, R>([&](auto p) {
+            x[decltype(p)::value] = cplx{int_to_double((int32_t)decomp_next_digit<S>(s0[decltype(p)::value], BL)),
+                                         int_to_double((int32_t)decomp_next_digit<S>(s1[decltype(p)::value], BL))};
+        });
+        FFT::fwd_pass1(lane, x, fbuf_r + t * C::REGION, twf);
+    }
+}
+
 }  // namespace b200tfhe

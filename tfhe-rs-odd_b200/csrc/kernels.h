@@ -43,7 +43,11 @@ struct BRLaunch {
     // bsk + (ct / bsk_ct_div) * bsk_ct_stride (in complex values); 0 = one key shared by the batch
     size_t bsk_ct_stride = 0;
     int bsk_ct_div = 1;
+    // kernel choice (b200tfhe_context_set_option "br_kernel" / "lat_max"): BR_AUTO picks by parameter set and batch size
+    int force = 0;
+    int lat_max = 2 * 148;
 };
+enum { BR_AUTO = 0, BR_GENERIC = 1, BR_TMEM = 2, BR_LAT = 3, BR_GENERIC_1CT = 4, BR_WS = 5 };
 
 // blind_rotate.cu
 int br_supported(const Params &p);  // returns team radix R (16/32) or 0
@@ -59,9 +63,12 @@ int bsk_convert_big_launch(const Params &p, const void *std_bsk, void *out, cons
 int br_tmem_supported(const Params &p);
 int br_tmem_launch(const Params &p, const BRLaunch &a, cudaStream_t st);
 
-// blind_rotate_ws.cu (same parameter set; warp-specialised: Fourier warp + torus warp per ciphertext)
+// blind_rotate_ws.cu (same parameter set; warp-specialised: Fourier warp + torus warp per ciphertext).  A measured-and-rejected
+// experiment: compiled only with `make WS=1` (-DB200TFHE_BUILD_WS), never part of the default library
+#ifdef B200TFHE_BUILD_WS
 int br_ws_supported(const Params &p);
 int br_ws_launch(const Params &p, const BRLaunch &a, cudaStream_t st);
+#endif
 
 // blind_rotate_lat.cu (same parameter set; ONE ciphertext per CTA spread over 128 threads: the single-PBS latency path)
 int br_lat_supported(const Params &p);
@@ -145,6 +152,11 @@ int mod_index_launch(uint32_t *idx, size_t total, uint32_t mod, cudaStream_t st)
 int cmux_layer_supported(const Params &pc);
 int cmux_layer_launch(const Params &pc, const void *in, size_t ct_in_stride, void *out, const void *ggsw, size_t key_stride, int n_luts,
                       int pairs, size_t n_cmux, const void *tw_fwd, const void *tw_inv, cudaStream_t st);
+
+// external_product.cu (stand-alone add_external_product_assign / cmux_assign over a batch, every blind-rotation parameter set)
+int external_product_supported(const Params &p);   // team radix (16/32/256) or 0
+int external_product_launch(const Params &p, void *out, void *src, const void *ggsw_list, const uint32_t *idx, int cmux, int batch,
+                            const void *tw_fwd, const void *tw_inv, cudaStream_t st);
 
 // misc_kernels.cu
 int modswitch_launch(const void *in, uint32_t *out, size_t count, int log2N, int bits, cudaStream_t st);
