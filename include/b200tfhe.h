@@ -318,6 +318,12 @@ int b200tfhe_pool_set_luts(b200tfhe_context *ctx, b200tfhe_pool *pool, const voi
 int b200tfhe_wave_run(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, b200tfhe_pool *pool,
                       const b200tfhe_wave_op *ops, uint32_t n_ops, uint32_t n_pbs);
 
+/* A pre-scheduled circuit in one call: n_waves waves, concatenated in `ops` (wave w: n_ops[w] operations, the first n_pbs[w]
+ * bootstrapped), executed back to back on the context's stream with the semantics of b200tfhe_wave_run per wave.  The host
+ * scheduler (rayon layers in the reference: integer/server_key/radix_parallel/mul.rs:355-404) runs once, the plan is replayed. */
+int b200tfhe_wave_sequence_run(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, b200tfhe_pool *pool,
+                               const b200tfhe_wave_op *ops, const uint32_t *n_ops, const uint32_t *n_pbs, uint32_t n_waves);
+
 /* sustained FP64 FMA rate of the device in TFLOP/s (register-only probe kernel, best of repeated runs over
  * about duration_ms): the measured denominator of the blind rotation's FP64 roofline */
 int b200tfhe_probe_fp64_tflops(b200tfhe_context *ctx, double duration_ms, double *tflops);

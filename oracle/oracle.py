@@ -76,12 +76,30 @@ def build(force=False):
 
 
 _lib = None
+_native = None     # path of a host-tuned build, see use_native_build()
+
+
+def use_native_build():
+    """For the TIMED CPU legs of bench.py only: compile the oracle for the host it runs on (-O3 -march=native, what BASELINE.md
+    section 3 states for the CPU arm) into liboracle_native.so and make lib() load that one.  The portable build (x86-64-v3) is what
+    travels with the repository and what the tests use.  Returns the compiler flags actually in effect."""
+    global _native
+    if _lib is not None:
+        return "portable (library already loaded)"
+    out = os.path.join(_HERE, "liboracle_native.so")
+    try:
+        subprocess.check_call(["make", "-C", _HERE, "-s", "-B", "liboracle_native.so"], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        C.CDLL(out)
+        _native = out
+        return "-O3 -march=native -mprefer-vector-width=512"
+    except (OSError, subprocess.CalledProcessError):
+        return "-O3 -march=x86-64-v3 (native build failed)"
 
 
 def lib():
     global _lib
     if _lib is None:
-        _lib = C.CDLL(build())
+        _lib = C.CDLL(_native or build())
         _lib.orc_closest_representable.restype = C.c_uint64
         _lib.orc_closest_representable.argtypes = [C.c_uint64, C.c_int, C.c_int, C.c_int]
         _lib.orc_modswitch.restype = C.c_uint64

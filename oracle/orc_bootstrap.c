@@ -62,28 +62,36 @@ static scratch_t *get_scratch(size_t tot, int N) {
     return &g_scr;
 }
 
-/* fft64/crypto/ggsw.rs:477-598.  ggsw_f: [level 1..l][row][col][N doubles: re | im] (levels stored 1->l, consumed l->1). */
+/* fft64/crypto/ggsw.rs:477-598.  ggsw_f: [level 1..l][row][col][N doubles: re | im] (levels stored 1->l, consumed l->1).
+ * The integer loops are written branch-free over whole polynomials so that gcc vectorises them (the reference's are SIMD too:
+ * fft64/math/decomposition.rs:27-86 works on slices). */
 void orc_add_external_product(const orc_params *p, uint64_t *acc, const double *ggsw_f, const uint64_t *glwe) {
-    int N = p->N, M = N / 2, k1 = p->k + 1, L = p->pbs_level, b = p->pbs_base_log, bits = p->bits;
-    uint64_t m = maskw(bits), mb = (1ULL << b) - 1;
-    size_t tot = (size_t)k1 * N;
+    const int N = p->N, M = N / 2, k1 = p->k + 1, L = p->pbs_level, b = p->pbs_base_log, bits = p->bits;
+    const uint64_t m = maskw(bits), mb = (1ULL << b) - 1;
+    const size_t tot = (size_t)k1 * N;
     scratch_t *sc = get_scratch(tot, N);
-    uint64_t *states = sc->states, *digits = sc->digits;
+    uint64_t *restrict states = sc->states, *restrict digits = sc->digits;
     double *fourier = sc->fourier, *outf = sc->outf;
     memset(outf, 0, sizeof(double) * tot);
-    int shift = bits - b * L;
-    for (size_t t = 0; t < tot; t++) states[t] = orc_closest_representable(glwe[t], b, L, bits) >> shift;
+    /* SignedDecomposer::closest_representable (decomposer.rs:99-119) then the iterator's initial shift (iter.rs:37-50) */
+    const int shift = bits - b * L, rshift = shift - 1;
+    for (size_t t = 0; t < tot; t++) {
+        uint64_t res = (glwe[t] & m) >> rshift;
+        res += 1;
+        res &= ~1ULL;
+        states[t] = ((res << rshift) & m) >> shift;
+    }
     for (int lvl = L; lvl >= 1; lvl--) {
         const double *mat = ggsw_f + (size_t)(lvl - 1) * k1 * k1 * N;
         for (int r = 0; r < k1; r++) {
             /* collect_next_term: ggsw.rs:601-613 ; decompose_one_level: decomposition.rs:79-86 */
+            uint64_t *restrict st = states + (size_t)r * N;
             for (int j = 0; j < N; j++) {
-                uint64_t *st = &states[(size_t)r * N + j];
-                uint64_t res = *st & mb;
-                *st >>= b;
-                uint64_t carry = (((res - 1) & m) | *st) & res;
+                const uint64_t res = st[j] & mb;
+                const uint64_t s1 = st[j] >> b;
+                uint64_t carry = (((res - 1) & m) | s1) & res;
                 carry >>= (b - 1);
-                *st = (*st + carry) & m;
+                st[j] = (s1 + carry) & m;
                 digits[j] = (res - (carry << b)) & m;
             }
             orc_fft_forward_integer(N, digits, bits, fourier);

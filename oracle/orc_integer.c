@@ -63,12 +63,11 @@ void orc_monomial_mul_sub(uint64_t *out, const uint64_t *in, int N, uint64_t deg
     uint64_t full = deg / (uint64_t)N;
     int r = (int)(deg % (uint64_t)N);
     int flip = (full % 2) == 1;
-    for (int j = 0; j < N; j++) {
-        uint64_t v;
-        if (j < r) v = (0 - in[j + N - r]); else v = in[j - r];
-        if (flip) v = 0 - v;
-        out[j] = (v - in[j]) & m;
-    }
+    /* two branch-free (vectorisable) ranges: the wrapped-around head is negated, the tail is not; `flip` negates both */
+    const uint64_t sh = flip ? 0 : ~0ULL, st = flip ? ~0ULL : 0;      /* v -> (v ^ s) - s negates when s is all-ones */
+    const uint64_t *head = in + (N - r);
+    for (int j = 0; j < r; j++) out[j] = (((head[j] ^ sh) - sh) - in[j]) & m;
+    for (int j = r; j < N; j++) out[j] = (((in[j - r] ^ st) - st) - in[j]) & m;
 }
 
 /* algorithms/glwe_sample_extraction.rs:91-147 with nth = 0 */

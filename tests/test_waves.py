@@ -117,20 +117,21 @@ def test_trivium_keystream_on_device(ctx):
 
 @pytest.mark.gpu
 def test_radix_multiplication_on_device(ctx):
-    """BASELINE configs[3] in small: 16-bit radix integers (8 blocks at PARAM_MESSAGE_2_CARRY_2), schoolbook product in the
+    """BASELINE configs[3] at full width: FheUint32 = 16 blocks at PARAM_MESSAGE_2_CARRY_2, schoolbook product in the
     structure of unchecked_mul_parallelized (radix_parallel/mul.rs:329-424): one wave of bivariate block products, then
-    column-sum waves; result equals x * y mod 2^16 for every pair."""
+    column-sum waves; result equals x * y mod 2^32 for every pair.  The circuit is compiled once into a wave plan and
+    replayed by one C call (b200tfhe_wave_sequence_run)."""
     from tfhe_rs_odd_b200.waves import CiphertextPool, OpGraph
     from tfhe_rs_odd_b200 import radix
     o = get_oracle("MESSAGE_2_CARRY_2")
     p, ksk, bsk, sk = _server_key(ctx, o)
-    M, NB = 6, 8
+    M, NB = 4, 16
     rng = np.random.default_rng(21)
-    x, y = rng.integers(0, 1 << 16, M), rng.integers(0, 1 << 16, M)
-    x[0], y[0] = 0xFFFF, 0xFFFF
-    x[1], y[1] = 0, 0x1234
+    x, y = rng.integers(0, 1 << 32, M), rng.integers(0, 1 << 32, M)
+    x[0], y[0] = 0xFFFFFFFF, 0xFFFFFFFF
+    x[1], y[1] = 0, 0x12345678
     blocks = lambda v: np.stack([(v >> (2 * i)) & 3 for i in range(NB)], axis=1)
-    pool = CiphertextPool(ctx, p, capacity=M * 400, big=True)
+    pool = CiphertextPool(ctx, p, capacity=M * 1200, big=True)
     pool.set_luts(np.stack(radix.radix_luts(sk)))
     X, Y, OUT = 0, M * NB, 2 * M * NB
     pool.write(X, o.encrypt(o.encode(blocks(x).reshape(-1)), "big", seed=0x61))
@@ -139,9 +140,18 @@ def test_radix_multiplication_on_device(ctx):
     alloc = radix.SlotAllocator(3 * M * NB, pool.capacity)
     for m in range(M):
         radix.mul(g, alloc, X + m * NB, Y + m * NB, OUT + m * NB, NB)
-    waves = g.run(ksk, bsk)
-    assert waves[0] == (M * (36 + 28), M * (36 + 28))        # the block-product wave: nb(nb+1)/2 lsb + nb(nb-1)/2 msb terms
+    plan = g.compile()
+    waves = plan.run(ksk, bsk)
+    assert waves[0] == (M * (136 + 120), M * (136 + 120))    # the block-product wave: nb(nb+1)/2 lsb + nb(nb-1)/2 msb terms = 256
     got = o.decode(o.phase(pool.read(OUT, M * NB), "big")).reshape(M, NB) % 4
     total = sum(got[:, i].astype(np.int64) << (2 * i) for i in range(NB))
-    assert np.array_equal(total, (x * y) % (1 << 16))
+    assert np.array_equal(total, (x * y) % (1 << 32))
+    # replaying the compiled plan on fresh operands gives the new product (the plan holds slots, not values)
+    x2, y2 = rng.integers(0, 1 << 32, M), rng.integers(0, 1 << 32, M)
+    pool.write(X, o.encrypt(o.encode(blocks(x2).reshape(-1)), "big", seed=0x63))
+    pool.write(Y, o.encrypt(o.encode(blocks(y2).reshape(-1)), "big", seed=0x64000))
+    plan.run(ksk, bsk)
+    got = o.decode(o.phase(pool.read(OUT, M * NB), "big")).reshape(M, NB) % 4
+    total = sum(got[:, i].astype(np.int64) << (2 * i) for i in range(NB))
+    assert np.array_equal(total, (x2 * y2) % (1 << 32))
     pool.close()

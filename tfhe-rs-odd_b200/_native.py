@@ -75,6 +75,7 @@ _PROTOS = {
     "b200tfhe_pfpks_batch_u64": [_VP, _VP, _U32, _VP, _VP, _U32],
     "b200tfhe_cbs_vertical_packing_batch_u64": [_VP, _VP, _VP, _VP, _U32, _VP, _U32, _U32, _U32, _U32, _VP, _U32],
     "b200tfhe_wave_run": [_VP, _VP, _VP, _VP, _VP, _U32, _U32],
+    "b200tfhe_wave_sequence_run": [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _U32],
 }
 for _s in ("u64", "u32"):
     _PROTOS[f"b200tfhe_keyswitch_batch_{_s}"] = [_VP, _VP, _VP, _VP, _U32]

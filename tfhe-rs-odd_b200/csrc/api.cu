@@ -1364,18 +1364,14 @@ int b200tfhe_pool_set_luts(b200tfhe_context *ctx, b200tfhe_pool *pl, const void 
     pl->n_luts = n_luts;
     return 0;
 }
-int b200tfhe_wave_run(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, b200tfhe_pool *pl,
+// argument checks of one wave (no device work)
+static int wave_check(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, const b200tfhe_pool *pl,
                       const b200tfhe_wave_op *ops, uint32_t n_ops, uint32_t n_pbs) {
-    REQUIRE(ctx && pl && pl->ctx == ctx, "wave_run: bad handle");
-    if (n_ops == 0) return 0;
     REQUIRE(ops && n_pbs <= n_ops, "wave_run: bad operation list");
     if (n_pbs) {
         if (check_pair(ctx, ksk, bsk)) return 1;
         REQUIRE(pl->n_luts > 0, "wave_run: the pool has no accumulators (b200tfhe_pool_set_luts)");
-    }
-    const Params &p = pl->p;
-    if (n_pbs) {
-        const Params &kp = bsk->p;
+        const Params &p = pl->p, &kp = bsk->p;
         REQUIRE(kp.n == p.n && kp.k == p.k && kp.N == p.N && kp.bits == p.bits, "wave_run: keys and pool have different parameters");
     }
     for (uint32_t i = 0; i < n_ops; i++) {
@@ -1385,8 +1381,12 @@ int b200tfhe_wave_run(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200
         if (i < n_pbs) REQUIRE(o.lut >= 0 && (uint32_t)o.lut < pl->n_luts, "wave_run: accumulator index out of range");
         else REQUIRE(o.lut < 0, "wave_run: bootstrapped operations must come first");
     }
-    std::lock_guard<std::mutex> g(ctx->mu);
-    CK(cudaSetDevice(ctx->device));
+    return 0;
+}
+// one wave on the context's stream (caller holds ctx->mu, device is current, arguments are checked)
+static int wave_run_locked(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, b200tfhe_pool *pl,
+                           const b200tfhe_wave_op *ops, uint32_t n_ops, uint32_t n_pbs) {
+    const Params &p = pl->p;
     const size_t s = sz(p), len = pl->len, mid_len = pl->big ? small_len(p) : big_len(p);
     if (pl->ops_cap < n_ops) {
         CK(cudaStreamSynchronize(ctx->stream));
@@ -1401,7 +1401,8 @@ int b200tfhe_wave_run(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200
         CK(cudaMalloc((void **)&pl->d_idx, (size_t)cap * 4));
         pl->ops_cap = cap;
     }
-    // pageable source: cudaMemcpyAsync returns once the operations are staged, so the caller's array can be reused
+    // pageable source: cudaMemcpyAsync returns once the operations are staged, so the caller's array can be reused; the copy is
+    // stream-ordered after the previous wave's kernels, which still read d_ops
     CK(cudaMemcpyAsync(pl->d_ops, ops, (size_t)n_ops * sizeof(WaveOp), cudaMemcpyHostToDevice, ctx->stream));
     int rc = wave_gather_launch(pl->d_slots, len, (const WaveOp *)pl->d_ops, (int)n_ops, pl->d_staging, pl->d_idx, (int)n_pbs, p.bits, ctx->stream);
     ctx->launches++;
@@ -1418,6 +1419,37 @@ int b200tfhe_wave_run(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200
     rc = wave_scatter_launch(pl->d_slots, len, (const WaveOp *)pl->d_ops, (int)n_ops, (int)n_pbs, pl->d_out, pl->d_staging, p.bits, ctx->stream);
     ctx->launches++;
     if (rc) return fail(ctx, "wave scatter launch failed: " + std::to_string(rc));
+    return 0;
+}
+int b200tfhe_wave_run(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, b200tfhe_pool *pl,
+                      const b200tfhe_wave_op *ops, uint32_t n_ops, uint32_t n_pbs) {
+    REQUIRE(ctx && pl && pl->ctx == ctx, "wave_run: bad handle");
+    if (n_ops == 0) return 0;
+    if (wave_check(ctx, ksk, bsk, pl, ops, n_ops, n_pbs)) return 1;
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    return wave_run_locked(ctx, ksk, bsk, pl, ops, n_ops, n_pbs);
+}
+// A whole pre-scheduled circuit in ONE call: the waves of `ops` (concatenated; wave w has n_ops[w] operations, the first
+// n_pbs[w] of them bootstrapped) run back to back on the context's stream -- the host-side scheduler (Python OpGraph, or
+// a Rust caller's rayon layers) is off the critical path: a circuit is compiled once and replayed.
+int b200tfhe_wave_sequence_run(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, b200tfhe_pool *pl,
+                               const b200tfhe_wave_op *ops, const uint32_t *n_ops, const uint32_t *n_pbs, uint32_t n_waves) {
+    REQUIRE(ctx && pl && pl->ctx == ctx, "wave_sequence_run: bad handle");
+    if (n_waves == 0) return 0;
+    REQUIRE(ops && n_ops && n_pbs, "wave_sequence_run: null argument");
+    size_t off = 0;
+    for (uint32_t w = 0; w < n_waves; w++) {
+        if (n_ops[w] && wave_check(ctx, ksk, bsk, pl, ops + off, n_ops[w], n_pbs[w])) return 1;
+        off += n_ops[w];
+    }
+    std::lock_guard<std::mutex> g(ctx->mu);
+    CK(cudaSetDevice(ctx->device));
+    off = 0;
+    for (uint32_t w = 0; w < n_waves; w++) {
+        if (n_ops[w] && wave_run_locked(ctx, ksk, bsk, pl, ops + off, n_ops[w], n_pbs[w])) return 1;
+        off += n_ops[w];
+    }
     return 0;
 }
 

@@ -124,27 +124,54 @@ class OpGraph:
             by[o[0]].append(o)
         return [by[w] for w in sorted(by)]
 
-    def run(self, ksk, bsk):
-        """Executes and clears the recorded operations.  Returns [(n_ops, n_pbs)] per wave."""
-        ctx, lib = self.pool.ctx, self.pool.ctx._lib
-        stats = []
+    def compile(self):
+        """Freezes the recorded operations into a `WavePlan` (ctypes operation arrays, one block per wave) and clears the graph.
+        The plan can be replayed any number of times: the scheduling work is done once, off the critical path."""
+        waves = []
         for wave in self.waves():
             wave = sorted(wave, key=lambda o: o[4] is None)        # bootstrapped operations first
-            n_pbs = sum(1 for o in wave if o[4] is not None)
-            arr = (WaveOp * len(wave))()
-            for i, (_, dst, terms, pt, lut) in enumerate(wave):
+            waves.append((wave, sum(1 for o in wave if o[4] is not None)))
+        total = sum(len(w) for w, _ in waves)
+        arr = (WaveOp * max(1, total))()
+        i = 0
+        for wave, _ in waves:
+            for (_, dst, terms, pt, lut) in wave:
                 arr[i].dst = dst
                 for k, (s, c) in enumerate(terms):
                     arr[i].src[k] = s
                     arr[i].scale[k] = c
                 arr[i].plaintext = pt
                 arr[i].lut = -1 if lut is None else lut
-            ctx.check(lib.b200tfhe_wave_run(ctx._h, ksk._h if ksk else None, bsk._h if bsk else None, self.pool._h, arr, len(wave), n_pbs))
-            stats.append((len(wave), n_pbs))
+                i += 1
+        plan = WavePlan(self.pool, arr, [len(w) for w, _ in waves], [n for _, n in waves])
         self.ops = []
         self._written.clear()
         self._read.clear()
-        return stats
+        return plan
+
+    def run(self, ksk, bsk):
+        """Executes and clears the recorded operations.  Returns [(n_ops, n_pbs)] per wave."""
+        return self.compile().run(ksk, bsk)
+
+
+class WavePlan:
+    """A compiled circuit: every wave's operations in one array, replayed by ONE C call (b200tfhe_wave_sequence_run)."""
+
+    def __init__(self, pool, ops, n_ops, n_pbs):
+        self.pool, self.ops = pool, ops
+        self.n_ops = np.ascontiguousarray(n_ops, dtype=np.uint32)
+        self.n_pbs = np.ascontiguousarray(n_pbs, dtype=np.uint32)
+
+    @property
+    def stats(self):
+        return [(int(a), int(b)) for a, b in zip(self.n_ops, self.n_pbs)]
+
+    def run(self, ksk, bsk):
+        """Asynchronous on the context's stream.  Returns [(n_ops, n_pbs)] per wave."""
+        ctx = self.pool.ctx
+        ctx.check(ctx._lib.b200tfhe_wave_sequence_run(ctx._h, ksk._h if ksk else None, bsk._h if bsk else None, self.pool._h, self.ops,
+                                                      _ptr(self.n_ops), _ptr(self.n_pbs), len(self.n_ops)))
+        return self.stats
 
 
 _native  # noqa: B018  (imported for its side effect of declaring the prototypes)
