@@ -324,6 +324,42 @@ int b200tfhe_wave_run(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200
 int b200tfhe_wave_sequence_run(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200tfhe_bsk *bsk, b200tfhe_pool *pool,
                                const b200tfhe_wave_op *ops, const uint32_t *n_ops, const uint32_t *n_pbs, uint32_t n_waves);
 
+/* ---- several GPUs of one node behind one handle (SURVEY 8(b) ctx_create(n_gpus), 8(e)) ------------------------------------------
+ * The reference parallelises this path with rayon over independent ciphertexts (tfhe/benches/core_crypto/pbs_bench.rs:517-532,
+ * integer/server_key/radix_parallel/mul.rs:355-404); here ONE host batch is split contiguously over the GPUs (remainder to the low
+ * devices), one host thread + stream + workspace per GPU, results written back to the caller's buffer at the same indices, no
+ * per-batch collective.  Keys are uploaded and converted once on device 0 and fanned out device-to-device (cudaMemcpyPeerAsync over
+ * NVLink / NVSwitch).  n_gpus <= 0: every visible device.  Either key pointer may be NULL (keyswitch-only / bootstrap-only sets).
+ * Host pointers throughout (pin them for full PCIe bandwidth); calls are synchronous. */
+typedef struct b200tfhe_multi_context b200tfhe_multi_context;
+typedef struct b200tfhe_multi_keys b200tfhe_multi_keys;
+int b200tfhe_multi_context_create(int n_gpus, b200tfhe_multi_context **out);
+int b200tfhe_multi_context_destroy(b200tfhe_multi_context *m);
+int b200tfhe_multi_context_gpus(const b200tfhe_multi_context *m);
+/* the single-GPU context of device `gpu` (owned by the multi context), or NULL */
+b200tfhe_context *b200tfhe_multi_context_get(b200tfhe_multi_context *m, int gpu);
+const char *b200tfhe_multi_last_error(const b200tfhe_multi_context *m);
+int b200tfhe_multi_keys_upload_u64(b200tfhe_multi_context *m, const b200tfhe_params *p, const uint64_t *std_bsk, const uint64_t *ksk,
+                                   b200tfhe_multi_keys **out);
+int b200tfhe_multi_keys_upload_u32(b200tfhe_multi_context *m, const b200tfhe_params *p, const uint32_t *std_bsk, const uint32_t *ksk,
+                                   b200tfhe_multi_keys **out);
+int b200tfhe_multi_keys_destroy(b200tfhe_multi_keys *k);
+/* the batched operations of the single-GPU section, same buffers and semantics, sharded over the GPUs */
+int b200tfhe_multi_keyswitch_batch_u64(b200tfhe_multi_context *m, const b200tfhe_multi_keys *k, const uint64_t *in, uint64_t *out, uint32_t batch);
+int b200tfhe_multi_keyswitch_batch_u32(b200tfhe_multi_context *m, const b200tfhe_multi_keys *k, const uint32_t *in, uint32_t *out, uint32_t batch);
+int b200tfhe_multi_pbs_batch_u64(b200tfhe_multi_context *m, const b200tfhe_multi_keys *k, const uint64_t *in, uint64_t *out,
+                                 const uint64_t *luts, uint32_t n_luts, const uint32_t *lut_idx, uint32_t batch);
+int b200tfhe_multi_pbs_batch_u32(b200tfhe_multi_context *m, const b200tfhe_multi_keys *k, const uint32_t *in, uint32_t *out,
+                                 const uint32_t *luts, uint32_t n_luts, const uint32_t *lut_idx, uint32_t batch);
+int b200tfhe_multi_ks_pbs_batch_u64(b200tfhe_multi_context *m, const b200tfhe_multi_keys *k, const uint64_t *in, uint64_t *out,
+                                    const uint64_t *luts, uint32_t n_luts, const uint32_t *lut_idx, uint32_t batch);
+int b200tfhe_multi_ks_pbs_batch_u32(b200tfhe_multi_context *m, const b200tfhe_multi_keys *k, const uint32_t *in, uint32_t *out,
+                                    const uint32_t *luts, uint32_t n_luts, const uint32_t *lut_idx, uint32_t batch);
+int b200tfhe_multi_pbs_ks_batch_u64(b200tfhe_multi_context *m, const b200tfhe_multi_keys *k, const uint64_t *in, uint64_t *out,
+                                    const uint64_t *luts, uint32_t n_luts, const uint32_t *lut_idx, uint32_t batch);
+int b200tfhe_multi_pbs_ks_batch_u32(b200tfhe_multi_context *m, const b200tfhe_multi_keys *k, const uint32_t *in, uint32_t *out,
+                                    const uint32_t *luts, uint32_t n_luts, const uint32_t *lut_idx, uint32_t batch);
+
 /* sustained FP64 FMA rate of the device in TFLOP/s (register-only probe kernel, best of repeated runs over
  * about duration_ms): the measured denominator of the blind rotation's FP64 roofline */
 int b200tfhe_probe_fp64_tflops(b200tfhe_context *ctx, double duration_ms, double *tflops);

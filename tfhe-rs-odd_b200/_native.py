@@ -77,7 +77,21 @@ _PROTOS = {
     "b200tfhe_wave_run": [_VP, _VP, _VP, _VP, _VP, _U32, _U32],
     "b200tfhe_wave_sequence_run": [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _U32],
 }
+_PROTOS.update({
+    "b200tfhe_multi_context_create": [_I, _PP],
+    "b200tfhe_multi_context_destroy": [_VP],
+    "b200tfhe_multi_context_gpus": [_VP],
+    "b200tfhe_multi_context_get": [_VP, _I],
+    "b200tfhe_multi_last_error": [_VP],
+    "b200tfhe_multi_keys_upload_u64": [_VP, C.POINTER(Params), _VP, _VP, _PP],
+    "b200tfhe_multi_keys_upload_u32": [_VP, C.POINTER(Params), _VP, _VP, _PP],
+    "b200tfhe_multi_keys_destroy": [_VP],
+})
 for _s in ("u64", "u32"):
+    _PROTOS[f"b200tfhe_multi_keyswitch_batch_{_s}"] = [_VP, _VP, _VP, _VP, _U32]
+    _PROTOS[f"b200tfhe_multi_pbs_batch_{_s}"] = [_VP, _VP, _VP, _VP, _VP, _U32, _VP, _U32]
+    _PROTOS[f"b200tfhe_multi_ks_pbs_batch_{_s}"] = [_VP, _VP, _VP, _VP, _VP, _U32, _VP, _U32]
+    _PROTOS[f"b200tfhe_multi_pbs_ks_batch_{_s}"] = [_VP, _VP, _VP, _VP, _VP, _U32, _VP, _U32]
     _PROTOS[f"b200tfhe_keyswitch_batch_{_s}"] = [_VP, _VP, _VP, _VP, _U32]
     _PROTOS[f"b200tfhe_pbs_batch_{_s}"] = [_VP, _VP, _VP, _VP, _VP, _U32, _VP, _U32]
     _PROTOS[f"b200tfhe_blind_rotate_batch_{_s}"] = [_VP, _VP, _VP, _VP, _VP, _U32, _VP, _U32]
@@ -87,7 +101,7 @@ for _s in ("u64", "u32"):
     _PROTOS[f"b200tfhe_cmux_batch_{_s}"] = [_VP, _VP, _VP, _VP, _VP, _U32]
     _PROTOS[f"b200tfhe_modulus_switch_{_s}"] = [_VP, _VP, _VP, _SZ, _U32]
     _PROTOS[f"b200tfhe_sample_extract_batch_{_s}"] = [_VP, _VP, _VP, _U32, _U32, _U32]
-_RESTYPES = {"b200tfhe_last_error": C.c_char_p, "b200tfhe_context_stream": C.c_void_p, "b200tfhe_launch_count": C.c_uint64,
+_RESTYPES = {"b200tfhe_last_error": C.c_char_p, "b200tfhe_multi_last_error": C.c_char_p, "b200tfhe_multi_context_get": C.c_void_p, "b200tfhe_context_stream": C.c_void_p, "b200tfhe_launch_count": C.c_uint64,
              "b200tfhe_bsk_grouping_factor": C.c_uint32}
 
 EXPORTED_SYMBOLS = tuple(sorted(_PROTOS))
