@@ -4,6 +4,7 @@ import ctypes as C
 import os
 import re
 import subprocess
+import sys
 
 import numpy as np
 import pytest
@@ -205,3 +206,9 @@ def test_big_kernel_stages_on_cpu_match_oracle(emul):
     out = np.zeros((1, o.glwe_len), np.uint64)
     emul.emul_blind_rotate_big(o.n, o.k, o.N, o.b, o.l, o.bits, _p(o.bsk), _p(ct), 1, _p(lut), _p(out))
     assert np.abs((out - ref).astype(np.int64)).max() < 2 ** 36       # one CMUX: f64 FFT precision only
+
+
+def test_constant_table_is_reproducible():
+    """fft_reg.cuh cites tools/gen_tables.py for COS128_TAB: the committed generator must reproduce it bit for bit."""
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "gen_tables.py"), "--check"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr

@@ -200,8 +200,10 @@ int b200tfhe_context_set_option(b200tfhe_context *ctx, const char *key, int64_t 
     std::lock_guard<std::mutex> g(ctx->mu);
     const std::string k(key);
     if (k == "br_kernel") {
-        REQUIRE(value >= BR_AUTO && value <= BR_WS, "context_set_option: br_kernel must be 0 (auto) .. 5");
+        REQUIRE(value >= BR_AUTO && value <= BR_X16, "context_set_option: br_kernel must be 0 (auto) .. 6");
         ctx->opt_br_kernel = (int)value;
+    } else if (k == "x16_variant") {
+        br_x16_set_variant((int)value);
     } else if (k == "lat_max") {
         REQUIRE(value >= 0 && value <= (1 << 20), "context_set_option: lat_max out of range");
         ctx->opt_lat_max = (int)value;

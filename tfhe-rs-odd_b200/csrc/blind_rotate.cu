@@ -229,6 +229,7 @@ int br_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
     // explicit choices (context option "br_kernel": parity tests exercise every kernel on the same inputs); -2: not built for this set
     if (a.force == BR_TMEM) return br_tmem_supported(p) ? br_tmem_launch(p, a, st) : -2;
     if (a.force == BR_LAT) return br_lat_supported(p) ? br_lat_launch(p, a, st) : -2;
+    if (a.force == BR_X16) return br_x16_supported(p) ? br_x16_launch(p, a, st) : -2;
 #ifdef B200TFHE_BUILD_WS
     if (a.force == BR_WS) return br_ws_supported(p) ? br_ws_launch(p, a, st) : -2;
 #else
@@ -237,6 +238,8 @@ int br_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
     if (a.force == BR_AUTO) {
         if (a.batch <= a.lat_max && br_lat_supported(p)) return br_lat_launch(p, a, st);
         if (br_tmem_supported(p)) return br_tmem_launch(p, a, st);
+        // blind_rotate_x16_kernel (half-warp teams + tensor-memory exchange) is parity-green but measured on par with the generic kernel
+        // (boolean, batch 8192: 107.4 ms vs 104.1 ms, profiles/r02_x16_variants.json): selectable with br_kernel = 6, not dispatched by default
     }
     if (a.batch < 3 * 148 || a.force == BR_GENERIC_1CT) {
 #define X(T, R, K, L, BL, CTS) \

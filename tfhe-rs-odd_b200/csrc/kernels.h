@@ -47,7 +47,7 @@ struct BRLaunch {
     int force = 0;
     int lat_max = 2 * 148;
 };
-enum { BR_AUTO = 0, BR_GENERIC = 1, BR_TMEM = 2, BR_LAT = 3, BR_GENERIC_1CT = 4, BR_WS = 5 };
+enum { BR_AUTO = 0, BR_GENERIC = 1, BR_TMEM = 2, BR_LAT = 3, BR_GENERIC_1CT = 4, BR_WS = 5, BR_X16 = 6 };
 
 // blind_rotate.cu
 int br_supported(const Params &p);  // returns team radix R (16/32) or 0
@@ -62,6 +62,11 @@ int bsk_convert_big_launch(const Params &p, const void *std_bsk, void *out, cons
 // blind_rotate_tmem.cu (N = 2048, k = 1, l = 1: Fourier polynomials exchanged through tensor memory, 4 ct per CTA)
 int br_tmem_supported(const Params &p);
 int br_tmem_launch(const Params &p, const BRLaunch &a, cudaStream_t st);
+
+// blind_rotate_x16.cu (boolean DEFAULT_PARAMETERS shape: half-warp teams, Fourier polynomials exchanged through tensor memory, 8 ct per CTA)
+int br_x16_supported(const Params &p);
+int br_x16_launch(const Params &p, const BRLaunch &a, cudaStream_t st);
+void br_x16_set_variant(int v);
 
 // blind_rotate_ws.cu (same parameter set; warp-specialised: Fourier warp + torus warp per ciphertext).  A measured-and-rejected
 // experiment: compiled only with `make WS=1` (-DB200TFHE_BUILD_WS), never part of the default library
