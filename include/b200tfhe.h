@@ -57,7 +57,10 @@ enum { B200TFHE_GATE_AND = 0, B200TFHE_GATE_NAND = 1, B200TFHE_GATE_OR = 2, B200
 
 /* ---- context ------------------------------------------------------------------------------------------ */
 /* One context = one CUDA device + one stream + a private workspace pool (the per-thread ShortintEngine /
- * ComputationBuffers of shortint/engine/mod.rs:23-69).  Calls on one context are serialised internally. */
+ * ComputationBuffers of shortint/engine/mod.rs:23-69).  Calls on one context are serialised internally, but a context (and its
+ * last-error text) belongs to ONE host thread at a time, like the reference's thread_local engines: use one context per thread;
+ * key handles are immutable after upload and belong to the context that created them.
+ * A host-pointer entry point that fails after it started copying drains the context's streams before it returns. */
 int b200tfhe_context_create(int device, b200tfhe_context **out);
 int b200tfhe_context_destroy(b200tfhe_context *ctx);
 int b200tfhe_synchronize(b200tfhe_context *ctx);

@@ -157,3 +157,21 @@ def test_gpu_server_key_from_bincode(ctx, name):
         dev = t.convert_standard_lwe_bootstrap_key_to_fourier(ctx, p, o.bsk)
     ref = shortint.ServerKey(sk.key_switching_key, dev, sk.message_modulus, sk.carry_modulus).apply_lookup_table(cts, lut)
     assert np.array_equal(o.decode(o.phase(ref.data)), o.decode(o.phase(out.data)))
+
+
+def test_fourier_key_sanity_check_rejects_wrong_scaling_or_order():
+    """shortint.ServerKey.from_bincode uploads the serialised Fourier key verbatim; before that it checks that a few polynomials invert to
+    torus coefficients in [-1/2, 1/2) (the layout is not pinned by reference-produced bytes: fail loudly instead of bootstrapping garbage)."""
+    import tfhe_rs_odd_b200 as t
+    from tfhe_rs_odd_b200.shortint import _check_fourier_key
+    N, M = 512, 256
+    rng = np.random.default_rng(4)
+    polys = rng.integers(0, 2 ** 64, size=(6, N), dtype=np.uint64).astype(np.int64).astype(np.float64) * 2.0 ** -64
+    x = (polys[:, :M] + 1j * polys[:, M:]) * np.exp(1j * np.pi * np.arange(M) / N)
+    F = np.fft.fft(x, axis=1)
+    good = np.stack([F.real, F.imag], axis=-1)
+    _check_fourier_key(good, N)                                        # natural order, 2^-64 scaling: accepted
+    with pytest.raises(t.B200TfheError, match="order or scaling"):
+        _check_fourier_key(good * 2.0 ** 64, N)                         # forward_as_integer instead of forward_as_torus
+    with pytest.raises(t.B200TfheError, match="order or scaling"):
+        _check_fourier_key(good * M, N)                                 # an un-normalised transform

@@ -103,6 +103,20 @@ static int fail_cuda(b200tfhe_context *ctx, const char *what, cudaError_t e) {
         if (!(cond)) return fail(ctx, (msg));    \
     } while (0)
 
+// Host-pointer entry points enqueue copies from / into the CALLER's buffers: on any early return after the first enqueue the streams
+// are drained first, so the GPU never touches a buffer the caller may already have freed after seeing the error.
+struct DrainOnExit {
+    b200tfhe_context *ctx;
+    bool armed = true;
+    explicit DrainOnExit(b200tfhe_context *c) : ctx(c) {}
+    ~DrainOnExit() {
+        if (!armed) return;
+        cudaStreamSynchronize(ctx->stream);
+        if (ctx->s_h2d) cudaStreamSynchronize(ctx->s_h2d);
+        if (ctx->s_d2h) cudaStreamSynchronize(ctx->s_d2h);
+    }
+};
+
 static Params to_params(const b200tfhe_params *p) {
     Params q;
     q.n = p->lwe_dimension; q.k = p->glwe_dimension; q.N = p->polynomial_size;
@@ -614,6 +628,7 @@ static int host_op(b200tfhe_context *ctx, Op op, const b200tfhe_ksk *ksk, const 
     const size_t out_len = (op == OP_KS || op == OP_PBS_KS) ? small_len(p) : (op == OP_BR ? glwe_len(p) : big_len(p));
     std::lock_guard<std::mutex> g(ctx->mu);
     CK(cudaSetDevice(ctx->device));
+    DrainOnExit drain(ctx);
     void *d_in, *d_out, *d_mid = nullptr, *d_luts = nullptr, *d_idx = nullptr;
     CK(ctx->ws.get(Workspace::IN, batch * in_len * s, &d_in));
     CK(ctx->ws.get(Workspace::OUT, batch * out_len * s, &d_out));
@@ -665,6 +680,7 @@ static int host_op(b200tfhe_context *ctx, Op op, const b200tfhe_ksk *ksk, const 
         if (run((const char *)d_in, (char *)d_out, (const uint32_t *)d_idx, batch, 0)) return 1;
         CK(cudaMemcpyAsync(out, d_out, batch * out_len * s, cudaMemcpyDeviceToHost, ctx->stream));
         CK(cudaStreamSynchronize(ctx->stream));
+        drain.armed = false;
         return 0;
     }
     if (!ctx->s_h2d) {
@@ -701,6 +717,7 @@ static int host_op(b200tfhe_context *ctx, Op op, const b200tfhe_ksk *ksk, const 
     }
     CK(cudaStreamSynchronize(ctx->s_d2h));
     CK(cudaStreamSynchronize(ctx->stream));
+    drain.armed = false;
     return 0;
 }
 

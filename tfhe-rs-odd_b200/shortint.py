@@ -46,6 +46,23 @@ class CiphertextList:
         return CiphertextList(self.data.copy(), self.degree.copy(), self.noise_level.copy())
 
 
+def _check_fourier_key(fourier, N, polys=4):
+    """Sanity check of a deserialised Fourier bootstrap key before it is uploaded verbatim (EXPERIMENTAL entry point: no
+    reference-produced bytes exist in this repository to pin the element order and scaling of concrete-fft's serialised buffer).
+    A Fourier polynomial produced by forward_as_torus (fft/mod.rs:197-218) in natural frequency order inverts to torus coefficients
+    in [-1/2, 1/2); a different order or scaling (missing 2^-BITS, a factor M) does not -- raise instead of bootstrapping garbage."""
+    M = N // 2
+    f = fourier.reshape(-1)[: 2 * M * polys].reshape(-1, M, 2)
+    j = np.arange(M)
+    untwist = np.exp(-1j * np.pi * j / N)
+    for q in range(f.shape[0]):
+        c = np.fft.ifft(f[q, :, 0] + 1j * f[q, :, 1]) * untwist
+        hi = max(np.abs(c.real).max(), np.abs(c.imag).max())
+        if not np.isfinite(hi) or hi > 0.5 + 1e-6:
+            raise B200TfheError(f"Fourier bootstrap key polynomial {q} does not invert to torus coefficients in [-1/2, 1/2) (max {hi:.3g}): "
+                                "unexpected element order or scaling of the serialised key")
+
+
 class ServerKey:
     """shortint::ServerKey{key_switching_key, bootstrapping_key (Classic or MultiBit: the device key handle carries the
     grouping factor), message_modulus, carry_modulus, pbs_order}."""
@@ -70,6 +87,7 @@ class ServerKey:
         params = cc.make_params(b["input_lwe_dimension"], glwe_dim, N, b["decomp_base_log"], b["decomp_level_count"],
                                 k["decomp_base_log"], k["decomp_level_count"], 64)
         ksk = cc.LweKeyswitchKey.upload(ctx, params, k["data"])
+        _check_fourier_key(np.asarray(b["fourier"], dtype=np.float64), params.polynomial_size)
         bsk = cc.FourierLweBootstrapKey.from_fourier(ctx, params, b["fourier"], b["grouping_factor"])
         sk = cls(ksk, bsk, d["message_modulus"], d["carry_modulus"], d["pbs_order"])
         sk.max_degree, sk.max_noise_level = d["max_degree"], d["max_noise_level"]
@@ -137,6 +155,7 @@ class ServerKey:
     def unchecked_apply_lookup_table_bivariate(self, left, right, lut, factor=None):
         """left*factor + right (wrapping, no PBS) then apply_lookup_table; factor defaults to message_modulus."""
         factor = np.uint64(self.message_modulus if factor is None else factor)
+        # noise of scalar_mul + add as the reference tracks it (bivariate_pbs.rs:167-182 -> unchecked_scalar_mul_assign + unchecked_add_assign)
         tmp = CiphertextList(left.data * factor + right.data, left.degree * factor + right.degree,
-                             np.maximum(left.noise_level, right.noise_level))
+                             left.noise_level * factor + right.noise_level)
         return self.apply_lookup_table_assign(tmp, lut)
