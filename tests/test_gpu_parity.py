@@ -399,3 +399,27 @@ def test_pbs_output_error_variance_matches_oracle_and_theory(ctx):
     assert 0.6 < v_gpu / v_ref < 1.6          # F-ratio of two samples of one distribution (192 vs 1536 draws: sd ~ 11 %)
     assert 0.5 < v_gpu / theory < 2.0
     assert np.abs(err_gpu).max() < 2.0 ** -7   # half the decoding step 2^-5 / 2 with margin: every output decodes
+
+
+def test_partial_last_wave_runs_on_the_latency_kernel(ctx):
+    """br_launch, auto mode, 2_2 shape: full waves (4 x SM count ciphertexts) on the tensor-memory kernel, a remainder of up to lat_max
+    ciphertexts on the one-ciphertext-per-SM kernel (what a strong-scaling split leaves behind).  Each part must be bit-identical to the
+    same inputs run with that kernel forced, and everything must decrypt."""
+    import tfhe_rs_odd_b200 as t
+    o = get_oracle("TOY_2_2")
+    p, bsk, ksk = _keys(ctx, o)
+    B = 4 * 148 + 108
+    msgs = np.arange(B) % o.pmod
+    cts = o.encrypt(o.encode(msgs), "small", seed=0x7A11)
+    lut = o.lut(lambda x: (x + 3) % o.pmod)
+    got = t.programmable_bootstrap_lwe_ciphertext(cts, lut, bsk)
+    assert np.array_equal(o.decode(o.phase(got, "big")) % o.pmod, (msgs + 3) % o.pmod)
+    main = B - 108
+    try:
+        ctx.set_option("br_kernel", 2)
+        tm = t.programmable_bootstrap_lwe_ciphertext(cts[:main], lut, bsk)
+        ctx.set_option("br_kernel", 3)
+        lt = t.programmable_bootstrap_lwe_ciphertext(cts[main:], lut, bsk)
+    finally:
+        ctx.set_option("br_kernel", 0)
+    assert np.array_equal(got[:main], tm) and np.array_equal(got[main:], lt)

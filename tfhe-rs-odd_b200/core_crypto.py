@@ -246,7 +246,7 @@ def _luts(acc, idx, p, batch):
         li = np.ascontiguousarray(idx, dtype=np.uint32).reshape(-1)
         if li.size != batch:
             raise B200TfheError("lut_idx must have one entry per ciphertext")
-    elif luts.shape[0] > 1:
+    elif luts.shape[0] > 1 and batch > 0:
         # several accumulators and no index: one per ciphertext, or an error -- never "silently accumulator 0 for everybody"
         if luts.shape[0] != batch:
             raise B200TfheError(f"{luts.shape[0]} accumulators for {batch} ciphertexts and no lut_idx: pass one accumulator, one per "

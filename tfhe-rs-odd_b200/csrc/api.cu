@@ -510,7 +510,7 @@ static int br_dev_locked(b200tfhe_context *ctx, const b200tfhe_bsk *bsk, const v
     a.force = ctx->opt_br_kernel;
     a.lat_max = ctx->opt_lat_max;
     int rc = bsk->grouping ? br_mb_launch(p, bsk->grouping, a, ctx->stream) : br_launch(p, a, ctx->stream);
-    ctx->launches++;
+    ctx->launches += a.launches;
     if (rc == -2) return fail(ctx, "blind_rotate: the kernel selected with option \"br_kernel\" is not built for this parameter set");
     if (rc) return fail(ctx, "blind_rotate launch failed: " + std::to_string(rc));
     return 0;

@@ -237,7 +237,27 @@ int br_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
 #endif
     if (a.force == BR_AUTO) {
         if (a.batch <= a.lat_max && br_lat_supported(p)) return br_lat_launch(p, a, st);
-        if (br_tmem_supported(p)) return br_tmem_launch(p, a, st);
+        if (br_tmem_supported(p)) {
+            // The TMEM kernel runs in waves of 4 x (number of SMs) ciphertexts and a partial last wave costs a full wave time (7.4 ms).
+            // A remainder of up to lat_max ciphertexts is cheaper on the one-ciphertext-per-SM latency kernel (148: 2.8 ms, 296: 5.5 ms):
+            // what a strong-scaling split of one batch over several GPUs leaves behind (2048 per GPU = 3 full waves + 272).
+            int sms = 148, dev = 0;
+            if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+            const int wave = 4 * sms, rem = a.batch % wave;
+            if (rem > 0 && rem <= a.lat_max && a.batch > wave && br_lat_supported(p)) {
+                BRLaunch main = a, tail = a;
+                main.batch = a.batch - rem;
+                const size_t esz = (size_t)p.bits / 8;
+                tail.batch = rem;
+                tail.lwe_in = (const char *)a.lwe_in + (size_t)main.batch * a.lwe_stride * esz;
+                tail.out = (char *)a.out + (size_t)main.batch * a.out_stride * esz;
+                if (a.lut_idx) tail.lut_idx = a.lut_idx + main.batch;
+                if (int rc = br_tmem_launch(p, main, st)) return rc;
+                a.launches = 2;
+                return br_lat_launch(p, tail, st);
+            }
+            return br_tmem_launch(p, a, st);
+        }
         // blind_rotate_x16_kernel (half-warp teams + tensor-memory exchange) is parity-green but measured on par with the generic kernel
         // (boolean, batch 8192: 107.4 ms vs 104.1 ms, profiles/r02_x16_variants.json): selectable with br_kernel = 6, not dispatched by default
     }

@@ -46,6 +46,7 @@ struct BRLaunch {
     // kernel choice (b200tfhe_context_set_option "br_kernel" / "lat_max"): BR_AUTO picks by parameter set and batch size
     int force = 0;
     int lat_max = 2 * 148;
+    mutable int launches = 1;   // set by br_launch: kernels it actually launched (a tail wave may go to a second kernel)
 };
 enum { BR_AUTO = 0, BR_GENERIC = 1, BR_TMEM = 2, BR_LAT = 3, BR_GENERIC_1CT = 4, BR_WS = 5, BR_X16 = 6 };
 
