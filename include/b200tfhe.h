@@ -73,6 +73,9 @@ void *b200tfhe_context_stream(b200tfhe_context *ctx);
  *                     3 one-ciphertext-per-SM latency kernel | 4 generic kernel, one ciphertext per CTA | 5 warp-specialised
  *                     experiment (only in a `make WS=1` build).  A kernel that is not built for the key's parameter set makes
  *                     the blind rotation fail with an error -- the parity tests run every kernel on the same inputs this way.
+ *                     6 = the half-warp-team tensor-memory kernel of the boolean shape (k 2, N 512, l 3).
+ *   "x16_variant"     organisation of kernel 6 (process-wide): -1 default (= 12: all transforms first + TMA key ring), 4 = all transforms
+ *                     first with the key from L2, 0 / 1 = level-by-level with the key from L2 / from a TMA-staged level block
  *   "lat_max"         largest batch that runs on the latency kernel in auto mode (default 296 = 2 x 148 SMs; 0 = never)
  *   "ks_tensor_core"  0: use the CUDA-core keyswitch even where the tensor-core key planes exist (default 1)
  *   "ks_tc_min"       smallest batch on the tensor-core keyswitch (default 1)

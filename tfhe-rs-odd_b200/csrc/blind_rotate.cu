@@ -258,8 +258,14 @@ int br_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
             }
             return br_tmem_launch(p, a, st);
         }
-        // blind_rotate_x16_kernel (half-warp teams + tensor-memory exchange) is parity-green but measured on par with the generic kernel
-        // (boolean, batch 8192: 107.4 ms vs 104.1 ms, profiles/r02_x16_variants.json): selectable with br_kernel = 6, not dispatched by default
+        if (br_x16_supported(p)) {
+            // boolean shape: blind_rotate_x16b_kernel (8 ciphertexts per CTA, key through a TMA ring) runs a wave of 8 x SMs ciphertexts in
+            // 11.75 ms, the generic kernel a wave of 4 x SMs in 7.85 ms (profiles/r02_x16_variants.json): take the one with less wave time
+            int sms = 148, dev = 0;
+            if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+            const int wx = (a.batch + 8 * sms - 1) / (8 * sms), wg = (a.batch + 4 * sms - 1) / (4 * sms);
+            if (3 * wx <= 2 * wg) return br_x16_launch(p, a, st);
+        }
     }
     if (a.batch < 3 * 148 || a.force == BR_GENERIC_1CT) {
 #define X(T, R, K, L, BL, CTS) \

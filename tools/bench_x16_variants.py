@@ -29,7 +29,7 @@ d_out = torch.zeros((B, o.big + 1), dtype=torch.int32, device="cuda")
 stream = torch.cuda.ExternalStream(ctx.stream)
 VP = C.c_void_p
 res = {}
-variants = [("generic", 1, 0), ("x16_v0", 6, 0), ("x16_v1_tma", 6, 1), ("x16_v2_pair", 6, 2), ("x16_v3_tma_pair", 6, 3), ("generic_again", 1, 0)]
+variants = [("generic", 1, 0), ("x16_v0", 6, 0), ("x16_v1_tma", 6, 1), ("x16b_all_transforms_first", 6, 4), ("x16b_tma_ring", 6, 12), ("generic_again", 1, 0)]
 for name, kern, var in variants:
     ctx.set_option("br_kernel", kern)
     ctx.set_option("x16_variant", var)
@@ -48,4 +48,5 @@ for name, kern, var in variants:
     out = d_out[:64].cpu().numpy().view(np.uint32)
     ok = bool(np.array_equal(o.phase(out.astype(np.uint64), "big") < np.uint64(1 << 31), bits[:64]))
     res[name] = {"ms": ms, "pbs_per_s": B / ms * 1e3, "decrypt_ok": ok}
+ctx.set_option("x16_variant", -1)
 print(json.dumps(res, indent=1))
