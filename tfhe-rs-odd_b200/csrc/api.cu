@@ -665,15 +665,31 @@ static int host_op(b200tfhe_context *ctx, Op op, const b200tfhe_ksk *ksk, const 
     if (op == OP_KS_PBS) CK(ctx->ws.get(Workspace::MID, batch * small_len(p) * s, &d_mid));
     if (op == OP_PBS_KS) CK(ctx->ws.get(Workspace::MID, batch * big_len(p) * s, &d_mid));
 
-    // chunking: only when every chunk still fills the GPU for several waves (unit = 4 ciphertexts x 148 SMs)
+    // chunking: H2D of chunk i+1 and D2H of chunk i-1 overlap the kernels of chunk i.  Chunks are whole waves of the blind-rotation
+    // kernel that will run (unit), the FIRST and the LAST chunk are one wave each -- what stays exposed is the copy-in of the first
+    // chunk and the copy-out of the last, so they are the smallest -- and the middle is cut into at most three pieces.
     const uint32_t min_chunk = ctx->opt_chunk_min;
-    uint32_t n_chunks = 1, chunk = batch;
+    uint32_t bounds[b200tfhe_context::MAX_CHUNKS + 1] = {0};
+    uint32_t n_chunks = 1;
+    bounds[1] = batch;
     if (batch >= 2 * min_chunk && min_chunk > 0) {
-        n_chunks = batch / min_chunk;
-        if (n_chunks > 4) n_chunks = 4;
-        chunk = (batch + n_chunks - 1) / n_chunks;
-        chunk = (chunk + 591) / 592 * 592;
-        n_chunks = (batch + chunk - 1) / chunk;
+        int sms = 148;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+        const uint32_t unit = need_bsk ? (uint32_t)((br_tmem_supported(p) ? 4 : br_x16_supported(p) ? 8 : br_big_supported(p) ? 1 : 4) * sms) : 592u;
+        const uint32_t units = batch / unit, rem = batch % unit;
+        if (units >= 6) {
+            const uint32_t last = rem >= unit / 4 ? rem : unit + rem;           // a very small last chunk would waste a launch
+            const uint32_t mid_units = (batch - unit - last) / unit;
+            const uint32_t pieces = mid_units >= 3 ? 3 : (mid_units >= 1 ? mid_units : 0);
+            n_chunks = 0;
+            bounds[++n_chunks] = unit;
+            for (uint32_t q = 0; q < pieces; q++) bounds[n_chunks + 1] = bounds[n_chunks] + (mid_units / pieces + (q < mid_units % pieces ? 1 : 0)) * unit, n_chunks++;
+            bounds[++n_chunks] = batch;
+        } else if (units >= 2) {
+            n_chunks = 2;
+            bounds[1] = (units / 2) * unit;
+            bounds[2] = batch;
+        }
     }
     if (n_chunks == 1) {
         CK(cudaMemcpyAsync(d_in, in, batch * in_len * s, cudaMemcpyHostToDevice, ctx->stream));
@@ -697,15 +713,15 @@ static int host_op(b200tfhe_context *ctx, Op op, const b200tfhe_ksk *ksk, const 
     CK(cudaStreamWaitEvent(ctx->s_h2d, ctx->ev_start, 0));
     CK(cudaStreamWaitEvent(ctx->s_d2h, ctx->ev_start, 0));
     for (uint32_t c = 0; c < n_chunks; c++) {
-        const size_t first = (size_t)c * chunk;
-        const uint32_t cb = (uint32_t)((first + chunk <= batch) ? chunk : batch - first);
+        const size_t first = bounds[c];
+        const uint32_t cb = bounds[c + 1] - bounds[c];
         CK(cudaMemcpyAsync((char *)d_in + first * in_len * s, (const char *)in + first * in_len * s, (size_t)cb * in_len * s,
                            cudaMemcpyHostToDevice, ctx->s_h2d));
         CK(cudaEventRecord(ctx->ev_in[c], ctx->s_h2d));
     }
     for (uint32_t c = 0; c < n_chunks; c++) {
-        const size_t first = (size_t)c * chunk;
-        const uint32_t cb = (uint32_t)((first + chunk <= batch) ? chunk : batch - first);
+        const size_t first = bounds[c];
+        const uint32_t cb = bounds[c + 1] - bounds[c];
         CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_in[c], 0));
         if (run((const char *)d_in + first * in_len * s, (char *)d_out + first * out_len * s,
                 d_idx ? (const uint32_t *)d_idx + first : nullptr, cb, first))
