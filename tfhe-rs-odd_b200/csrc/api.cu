@@ -16,7 +16,7 @@ using namespace b200tfhe;
 static thread_local std::string g_global_err = "";
 
 struct Workspace {
-    enum { IN = 0, OUT, MID, LUTS, IDX, A, B, DIG, C, D, NSLOTS };
+    enum { IN = 0, OUT, MID, LUTS, IDX, A, B, DIG, C, D, MBK, NSLOTS };
     void *ptr[NSLOTS] = {};
     size_t cap[NSLOTS] = {};
     cudaError_t get(int slot, size_t bytes, void **out) {
@@ -57,6 +57,7 @@ struct b200tfhe_context {
     // tuning / test knobs (b200tfhe_context_set_option); the defaults are what production uses
     int opt_br_kernel = BR_AUTO;     // which blind-rotation kernel (kernels.h: BR_AUTO .. BR_WS)
     int opt_lat_max = 2 * 148;       // largest batch on the one-ciphertext-per-SM latency kernel
+    int opt_mb_lat_max = 148;        // multi-bit keys: largest batch on the two-kernel latency path (16-24 MB of scratch per ciphertext)
     int opt_ks_tensor_core = 1;      // 0: CUDA-core keyswitch even where the tensor-core planes exist
     int opt_ks_tc_min = 1;           // smallest batch on the tensor-core keyswitch
     uint32_t opt_chunk_min = 6 * 592;   // minimum chunk of the H2D / compute / D2H pipeline of host-pointer calls (0: off)
@@ -221,6 +222,9 @@ int b200tfhe_context_set_option(b200tfhe_context *ctx, const char *key, int64_t 
     } else if (k == "lat_max") {
         REQUIRE(value >= 0 && value <= (1 << 20), "context_set_option: lat_max out of range");
         ctx->opt_lat_max = (int)value;
+    } else if (k == "mb_lat_max") {
+        REQUIRE(value >= 0 && value <= 4096, "context_set_option: mb_lat_max out of range (0 .. 4096)");
+        ctx->opt_mb_lat_max = (int)value;
     } else if (k == "ks_tensor_core") {
         ctx->opt_ks_tensor_core = value != 0;
     } else if (k == "ks_tc_min") {
@@ -509,6 +513,12 @@ static int br_dev_locked(b200tfhe_context *ctx, const b200tfhe_bsk *bsk, const v
                p.n, (int)batch, mode, tw_fwd(ctx, R), tw_inv(ctx, R)};
     a.force = ctx->opt_br_kernel;
     a.lat_max = ctx->opt_lat_max;
+    if (bsk->grouping && (int)batch <= ctx->opt_mb_lat_max) {
+        if (const size_t need = br_mb_lat_scratch_bytes(p, bsk->grouping, (int)batch)) {
+            CK(ctx->ws.get(Workspace::MBK, need, &a.mb_scratch));
+            a.mb_lat_max = ctx->opt_mb_lat_max;
+        }
+    }
     int rc = bsk->grouping ? br_mb_launch(p, bsk->grouping, a, ctx->stream) : br_launch(p, a, ctx->stream);
     ctx->launches += a.launches;
     if (rc == -2) return fail(ctx, "blind_rotate: the kernel selected with option \"br_kernel\" is not built for this parameter set");

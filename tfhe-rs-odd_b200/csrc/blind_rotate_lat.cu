@@ -49,10 +49,16 @@ DEV void mbarrier_expect_tx(uint32_t bar, uint32_t bytes) {
 }
 #endif
 
+// BL: base log of the one-level decomposition.  PLAIN = false: the classic CMUX iteration acc += GGSW_i (.) (acc X^{a_i} - acc), n_iter = n.
+// PLAIN = true: acc <- GGSW'_g (.) acc, the iteration of the multi-bit blind rotation once the monomial-weighted sum GGSW'_g of a
+// group's key ciphertexts has been formed (blind_rotate_mb.cu: mb_key_sum_kernel); n_iter = n / grouping, the ciphertext's own list
+// of summed keys starts at bsk + ct * key_ct_stride.  Without the rotated reads the accumulator lives in registers only.
+template <int BL, bool PLAIN>
 __global__ void __launch_bounds__(LAT_THREADS, 1)
 blind_rotate_lat_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride, const uint64_t *__restrict__ luts,
                         const uint32_t *__restrict__ lut_idx, const cplx *__restrict__ bsk, uint64_t *__restrict__ out,
-                        size_t out_stride, int n, int mode, const Fft3::Tables *__restrict__ tables_g) {
+                        size_t out_stride, int n, int mode, const Fft3::Tables *__restrict__ tables_g, int n_iter,
+                        size_t key_ct_stride) {
 #if defined(__CUDA_ARCH__)
     typedef uint64_t T;
     constexpr int N = LAT_N, M = LAT_M, K1 = LAT_K1;
@@ -68,6 +74,7 @@ blind_rotate_lat_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride, 
 
     const int tid = threadIdx.x, r = tid >> 6, t = tid & 63;
     const int ct = blockIdx.x;
+    bsk += (size_t)ct * key_ct_stride;
     T *acc_r = acc + r * N;
     cplx *buf1_r = buf1 + r * Fft3::BUF, *buf2_r = buf2 + r * Fft3::BUF;
 
@@ -90,7 +97,7 @@ blind_rotate_lat_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride, 
 #pragma unroll
         for (int q = 0; q < 4; q++) bulk_load(key_s + q * 16384u, src + q * 16384u, 16384u, bar);
     };
-    if (tid == 0 && n > 0) fetch_key(0);
+    if (tid == 0 && n_iter > 0) fetch_key(0);
     {   // acc <- LUT * X^{-b_hat}  (polynomial_algorithms.rs:315-354)
         const T *lut = luts + (size_t)(lut_idx ? lut_idx[ct] : 0) * K1 * N + (size_t)r * N;
         const int a0 = (2 * N - (int)ahat[n]) & (2 * N - 1);
@@ -112,8 +119,8 @@ blind_rotate_lat_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride, 
         own_im[decltype(q)::value] = acc_r[t + 64 * decltype(q)::value + M];
     });
 
-    for (int i = 0; i < n; i++) {
-        const int a = ahat[i];
+    for (int i = 0; i < n_iter; i++) {
+        const int a = PLAIN ? 0 : ahat[i];
         cplx x[16];
 #pragma unroll 1
         for (int dir = 0; dir < 2; dir++) {
@@ -121,12 +128,21 @@ blind_rotate_lat_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride, 
             int ta_stride, ta_idx;
             if (dir == 0) {
                 // rotate-subtract + one-level signed decomposition, as doubles; then the register part of the twist
-                const uint32_t s8 = 8u * (uint32_t)(t - a);
-                static_for<0, 16>([&](auto p) {
-                    constexpr int v = brev(decltype(p)::value, 4);
-                    x[decltype(p)::value].re = rot_digit_f64<LAT_BL>(accb, s8 + 8u * 64u * v, own_re[v]);
-                    x[decltype(p)::value].im = rot_digit_f64<LAT_BL>(accb, s8 + 8u * 64u * v + 8u * M, own_im[v]);
-                });
+                if constexpr (PLAIN) {
+                    typedef BRCore<T, 32, 1, 1, BL> DC;
+                    static_for<0, 16>([&](auto p) {
+                        constexpr int v = brev(decltype(p)::value, 4);
+                        x[decltype(p)::value].re = int_to_double(DC::single_level_digit(own_re[v]));
+                        x[decltype(p)::value].im = int_to_double(DC::single_level_digit(own_im[v]));
+                    });
+                } else {
+                    const uint32_t s8 = 8u * (uint32_t)(t - a);
+                    static_for<0, 16>([&](auto p) {
+                        constexpr int v = brev(decltype(p)::value, 4);
+                        x[decltype(p)::value].re = rot_digit_f64<BL>(accb, s8 + 8u * 64u * v, own_re[v]);
+                        x[decltype(p)::value].im = rot_digit_f64<BL>(accb, s8 + 8u * 64u * v + 8u * M, own_im[v]);
+                    });
+                }
                 Fft3::pre_twist(x);
                 ta = &tab->ta_fwd[0][0]; ta_stride = 64; ta_idx = t;
             } else {
@@ -139,12 +155,12 @@ blind_rotate_lat_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride, 
                 static_for<0, 16>([&](auto p) {
                     constexpr int v = brev(decltype(p)::value, 4);
                     cplx f = cmul(key_own[64 * v], x[v]);
-                    BRCore<T, 32, 1, 1, LAT_BL>::mac_one(f, key_oth[64 * v], d_oth[64 * v]);
+                    BRCore<T, 32, 1, 1, BL>::mac_one(f, key_oth[64 * v], d_oth[64 * v]);
                     y[decltype(p)::value] = cplx{f.re, -f.im};
                 });
                 static_for<0, 16>([&](auto p) { x[decltype(p)::value] = y[decltype(p)::value]; });
                 __syncthreads();   // both teams are done with D (buf1) and with the key
-                if (tid == 0 && i + 1 < n) fetch_key(i + 1);
+                if (tid == 0 && i + 1 < n_iter) fetch_key(i + 1);
                 ta = &tab->ta_inv[0][0]; ta_stride = 4; ta_idx = t >> 4;
             }
             Fft3::pass_a(t, x, ta, ta_stride, ta_idx, buf1_r);
@@ -154,16 +170,30 @@ blind_rotate_lat_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride, 
             Fft3::pass_c(t, x, buf2_r);
             if (dir == 1) {
                 Fft3::post_twist(x);
-                static_for<0, 16>([&](auto q) {
-                    const int c = t + 64 * decltype(q)::value;
-                    own_re[decltype(q)::value] += torus_from_double<T>(x[decltype(q)::value].re);
-                    own_im[decltype(q)::value] += torus_from_double<T>(-x[decltype(q)::value].im);
-                    acc_r[c] = own_re[decltype(q)::value];
-                    acc_r[c + M] = own_im[decltype(q)::value];
-                });
-                named_bar_sync(1 + r, 64);
+                if constexpr (PLAIN) {
+                    static_for<0, 16>([&](auto q) {
+                        own_re[decltype(q)::value] = torus_from_double<T>(x[decltype(q)::value].re);
+                        own_im[decltype(q)::value] = torus_from_double<T>(-x[decltype(q)::value].im);
+                    });
+                } else {
+                    static_for<0, 16>([&](auto q) {
+                        const int c = t + 64 * decltype(q)::value;
+                        own_re[decltype(q)::value] += torus_from_double<T>(x[decltype(q)::value].re);
+                        own_im[decltype(q)::value] += torus_from_double<T>(-x[decltype(q)::value].im);
+                        acc_r[c] = own_re[decltype(q)::value];
+                        acc_r[c + M] = own_im[decltype(q)::value];
+                    });
+                    named_bar_sync(1 + r, 64);
+                }
             }
         }
+    }
+    if constexpr (PLAIN) {
+        static_for<0, 16>([&](auto q) {
+            acc_r[t + 64 * decltype(q)::value] = own_re[decltype(q)::value];
+            acc_r[t + 64 * decltype(q)::value + M] = own_im[decltype(q)::value];
+        });
+        named_bar_sync(1 + r, 64);
     }
 
     T *o = out + (size_t)ct * out_stride;
@@ -205,6 +235,16 @@ const Fft3::Tables *lat_tables(cudaStream_t st, cudaError_t *err) {
 int br_lat_supported(const Params &p) {
     return p.bits == 64 && p.N == LAT_N && p.k == 1 && p.pbs_level == 1 && p.pbs_base_log == LAT_BL;
 }
+// base logs of PARAM_MULTI_BIT_MESSAGE_2_CARRY_2_GROUP_{2,3}_KS_PBS (shortint/parameters/multi_bit.rs:115-132,173-190)
+#define LAT_PLAIN_INSTANCES(X) X(22) X(21)
+int br_lat_plain_supported(const Params &p) {
+    if (!(p.bits == 64 && p.N == LAT_N && p.k == 1 && p.pbs_level == 1)) return 0;
+#define X(BL) \
+    if (p.pbs_base_log == BL) return 1;
+    LAT_PLAIN_INSTANCES(X)
+#undef X
+    return 0;
+}
 
 int br_lat_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
     if (!br_lat_supported(p)) return -1;
@@ -213,11 +253,33 @@ int br_lat_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
     const Fft3::Tables *tab = lat_tables(st, &e);
     if (!tab) return (int)e;
     const size_t smem = lat_smem_bytes(a.n);
-    if ((e = ensure_dynamic_smem((const void *)blind_rotate_lat_kernel, smem)) != cudaSuccess) return (int)e;
-    blind_rotate_lat_kernel<<<a.batch, LAT_THREADS, smem, st>>>((const uint64_t *)a.lwe_in, a.lwe_stride, (const uint64_t *)a.luts,
-                                                               a.lut_idx, (const cplx *)a.bsk, (uint64_t *)a.out, a.out_stride, a.n,
-                                                               a.mode, tab);
+    auto kern = blind_rotate_lat_kernel<LAT_BL, false>;
+    if ((e = ensure_dynamic_smem((const void *)kern, smem)) != cudaSuccess) return (int)e;
+    kern<<<a.batch, LAT_THREADS, smem, st>>>((const uint64_t *)a.lwe_in, a.lwe_stride, (const uint64_t *)a.luts, a.lut_idx,
+                                             (const cplx *)a.bsk, (uint64_t *)a.out, a.out_stride, a.n, a.mode, tab, a.n, (size_t)0);
     return (int)cudaGetLastError();
+}
+
+// a.bsk: [batch][n_iter] summed Fourier GGSWs (key_ct_stride complex values per ciphertext); n_iter external products each
+int br_lat_plain_launch(const Params &p, const BRLaunch &a, int n_iter, size_t key_ct_stride, cudaStream_t st) {
+    if (!br_lat_plain_supported(p)) return -1;
+    if (a.batch <= 0) return 0;
+    cudaError_t e = cudaSuccess;
+    const Fft3::Tables *tab = lat_tables(st, &e);
+    if (!tab) return (int)e;
+    const size_t smem = lat_smem_bytes(a.n);
+#define X(BL)                                                                                                                       \
+    if (p.pbs_base_log == BL) {                                                                                                     \
+        auto kern = blind_rotate_lat_kernel<BL, true>;                                                                              \
+        if ((e = ensure_dynamic_smem((const void *)kern, smem)) != cudaSuccess) return (int)e;                                      \
+        kern<<<a.batch, LAT_THREADS, smem, st>>>((const uint64_t *)a.lwe_in, a.lwe_stride, (const uint64_t *)a.luts, a.lut_idx,     \
+                                                 (const cplx *)a.bsk, (uint64_t *)a.out, a.out_stride, a.n, a.mode, tab, n_iter,   \
+                                                 key_ct_stride);                                                                    \
+        return (int)cudaGetLastError();                                                                                             \
+    }
+    LAT_PLAIN_INSTANCES(X)
+#undef X
+    return -1;
 }
 
 }  // namespace b200tfhe

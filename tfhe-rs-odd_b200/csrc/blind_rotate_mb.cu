@@ -120,6 +120,61 @@ blind_rotate_mb_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const T 
     }
 }
 
+// ---- two-kernel latency path ---------------------------------------------------------------------------------------
+// With few ciphertexts the fused kernel above leaves most SMs idle while one CTA per ciphertext walks n/G iterations that each
+// read 2^G key ciphertexts.  The reference spends its spare threads on exactly that part (prepare_multi_bit_ggsw_mem_optimized on
+// worker threads, :295-546); here EVERY (ciphertext, group) pair gets a CTA that materialises
+//     GGSW'_g = GGSW_0 + sum_{idx>=1} GGSW_idx (.) FFT(X^{d_idx})                                   (:18-85)
+// in the device's Fourier order, all groups at once across the whole GPU, and the single-ciphertext kernel of
+// blind_rotate_lat.cu then runs n/G plain external products against its ciphertext's list: the sequential depth of a bootstrap
+// is n/G iterations of the classic latency kernel.
+template <typename T, int R, int K, int L, int BL, int G>
+__global__ void __launch_bounds__(256)
+mb_key_sum_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const cplx *__restrict__ bsk, cplx *__restrict__ out, int n) {
+    typedef MBCore<T, R, K, L, BL, G> C;
+    constexpr int NG = C::NG, N = C::N, NMONO = C::NMONO;
+    static_assert(256 % R == 0, "a thread keeps one lane of the team layout");
+    __shared__ cplx wr[R];
+    __shared__ uint16_t deg[NMONO];
+    const int gi = blockIdx.x, ct = blockIdx.y, ngroups = n / G;
+    if (threadIdx.x < R) wr[threadIdx.x] = C::wr_entry(threadIdx.x);
+    if (threadIdx.x >= 64 && threadIdx.x < 64 + NMONO)
+        deg[threadIdx.x - 64] = C::group_degree(lwe_in + (size_t)ct * lwe_stride + (size_t)gi * G, (int)threadIdx.x - 64 + 1);
+    __syncthreads();
+    const int lane = threadIdx.x % R;
+    cplx base[NMONO];
+    int dgs[NMONO];
+    static_for<0, NMONO>([&](auto g) {
+        dgs[decltype(g)::value] = deg[decltype(g)::value];
+        base[decltype(g)::value] = unit_root_pi((dgs[decltype(g)::value] * (1 - 4 * lane)) & (2 * N - 1), N);
+    });
+    const cplx *group = bsk + (size_t)gi * C::GROUP_CPLX;
+    cplx *o = out + ((size_t)ct * ngroups + gi) * C::GGSW_CPLX;
+#pragma unroll 2
+    for (int e = threadIdx.x; e < (int)C::GGSW_CPLX; e += 256) {
+        const int pos = (e / R) % R;     // e = polynomial * M + pos * R + lane
+        cplx s = ldg_stream(group + e);
+        static_for<1, NG>([&](auto g) {
+            const cplx w = wr[(dgs[decltype(g)::value - 1] * pos) & (R - 1)];
+            C::mac_one(s, cmul(base[decltype(g)::value - 1], w), ldg_stream(group + (size_t) decltype(g)::value * C::GGSW_CPLX + e));
+        });
+        o[e] = s;
+    }
+}
+
+template <typename T, int R, int K, int L, int BL, int G>
+static int launch_mb_lat(const Params &p, const BRLaunch &a, cudaStream_t st) {
+    typedef MBCore<T, R, K, L, BL, G> C;
+    const int ngroups = a.n / G;
+    mb_key_sum_kernel<T, R, K, L, BL, G><<<dim3(ngroups, a.batch), 256, 0, st>>>((const T *)a.lwe_in, a.lwe_stride, (const cplx *)a.bsk,
+                                                                                  (cplx *)a.mb_scratch, a.n);
+    if (cudaError_t e = cudaGetLastError()) return (int)e;
+    BRLaunch b = a;
+    b.bsk = a.mb_scratch;
+    a.launches = 2;
+    return br_lat_plain_launch(p, b, ngroups, (size_t)ngroups * C::GGSW_CPLX, st);
+}
+
 template <typename T, int R, int K, int L, int BL, int CTS, int G>
 static int launch_mb(const BRLaunch &a, cudaStream_t st) {
     typedef MBConfig<T, R, K, L, BL, CTS, G> CFG;
@@ -157,8 +212,28 @@ int br_mb_supported(const Params &p, int grouping) {
     return 0;
 }
 
+// the latency path exists where the single-ciphertext kernel does: N = 2048, k = 1, one level
+#define MB_LAT_INSTANCES(X)       \
+    X(uint64_t, 32, 1, 1, 22, 2)  \
+    X(uint64_t, 32, 1, 1, 21, 3)
+
+size_t br_mb_lat_scratch_bytes(const Params &p, int grouping, int batch) {
+    if (!br_lat_plain_supported(p) || batch <= 0) return 0;
+#define X(T, R, K, L, BL, G) \
+    if (MB_MATCH(T, R, K, L, BL, G)) return (size_t)batch * (size_t)(p.n / G) * MBCore<T, R, K, L, BL, G>::GGSW_CPLX * sizeof(cplx);
+    MB_LAT_INSTANCES(X)
+#undef X
+    return 0;
+}
+
 int br_mb_launch(const Params &p, int grouping, const BRLaunch &a, cudaStream_t st) {
     if (a.batch <= 0) return 0;
+    if (a.mb_scratch && a.batch <= a.mb_lat_max && br_lat_plain_supported(p)) {
+#define X(T, R, K, L, BL, G) \
+    if (MB_MATCH(T, R, K, L, BL, G)) return launch_mb_lat<T, R, K, L, BL, G>(p, a, st);
+        MB_LAT_INSTANCES(X)
+#undef X
+    }
     if (a.batch < 3 * 148) {
 #define X(T, R, K, L, BL, CTS, G) \
     if (MB_MATCH(T, R, K, L, BL, G)) return launch_mb<T, R, K, L, BL, CTS, G>(a, st);

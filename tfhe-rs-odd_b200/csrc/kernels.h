@@ -47,6 +47,10 @@ struct BRLaunch {
     int force = 0;
     int lat_max = 2 * 148;
     mutable int launches = 1;   // set by br_launch: kernels it actually launched (a tail wave may go to a second kernel)
+    // multi-bit keys, batches of at most mb_lat_max ciphertexts: scratch for the per-ciphertext summed keys of the two-kernel
+    // latency path (br_mb_lat_scratch_bytes); nullptr = always the fused kernel
+    void *mb_scratch = nullptr;
+    int mb_lat_max = 0;
 };
 enum { BR_AUTO = 0, BR_GENERIC = 1, BR_TMEM = 2, BR_LAT = 3, BR_GENERIC_1CT = 4, BR_WS = 5, BR_X16 = 6 };
 
@@ -79,10 +83,15 @@ int br_ws_launch(const Params &p, const BRLaunch &a, cudaStream_t st);
 // blind_rotate_lat.cu (same parameter set; ONE ciphertext per CTA spread over 128 threads: the single-PBS latency path)
 int br_lat_supported(const Params &p);
 int br_lat_launch(const Params &p, const BRLaunch &a, cudaStream_t st);
+// multi-bit latency path: n_iter plain external products against per-ciphertext summed keys (see blind_rotate_mb.cu)
+int br_lat_plain_supported(const Params &p);
+int br_lat_plain_launch(const Params &p, const BRLaunch &a, int n_iter, size_t key_ct_stride, cudaStream_t st);
 
 // blind_rotate_mb.cu (multi-bit bootstrap keys: 2^G GGSWs per group of G mask elements, n/G iterations)
 int br_mb_supported(const Params &p, int grouping);   // returns team radix R or 0
 int br_mb_launch(const Params &p, int grouping, const BRLaunch &a, cudaStream_t st);
+// bytes of BRLaunch::mb_scratch the two-kernel latency path needs for `batch` ciphertexts; 0 = that path is not built for the set
+size_t br_mb_lat_scratch_bytes(const Params &p, int grouping, int batch);
 // key conversion of `npoly` standard-domain polynomials with an explicit team radix (blind_rotate.cu)
 int bsk_convert_polys_launch(int R, int bits, size_t npoly, const void *std_bsk, void *out, const void *tw_fwd, cudaStream_t st);
 
