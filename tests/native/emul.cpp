@@ -195,39 +195,41 @@ extern "C" int emul_blind_rotate_big(int n, int k, int N, int base_log, int leve
     return 1;
 }
 
-// ---- latency kernel (blind_rotate_lat.cu): 64 threads per polynomial, three-pass FFT of fft3.cuh --------------------
-#include "fft3.cuh"
+// ---- latency kernel (blind_rotate_lat.cu): 128 threads per polynomial, three-pass FFT of fft8.cuh ---------------------
+#include "fft8.cuh"
+// one 1024-point transform of the team: x[t][p] in pass-A register order on entry, pass-C order (x[t][f2] = X[t + 128 f2]) on exit
+static void fft8_team(cplx (*x)[8], const Fft8::Tables &tb, int dir, cplx *b1, cplx *b2) {
+    static cplx z[128][8], send[128][4];
+    for (int t = 0; t < 128; t++) Fft8::pass_a(t, x[t], tb.ta, tb.twist[t], dir == 0, b1);
+    for (int t = 0; t < 128; t++) Fft8::pass_b_first(t, b1, z[t], send[t]);
+    for (int t = 0; t < 128; t++) Fft8::pass_b_second(t, z[t], send[t ^ 8], tb.tb[dir][t], b2);     // the shuffle: partner = lane ^ 8
+    for (int t = 0; t < 128; t++) Fft8::pass_c(t, x[t], b2);
+}
 // forward transform of 1024 folded complex inputs (re, im interleaved); out[f] = sum_j x_j e^{i pi j/N} e^{-2 pi i jf/M}
-extern "C" int emul_fft3_forward(const double *in, double *out) {
-    static Fft3::Tables tb; fill_fft3_tables(tb);
-    std::vector<cplx> b1(Fft3::BUF), b2(Fft3::BUF);
-    static cplx x[64][16];
-    for (int t = 0; t < 64; t++) {
-        for (int p = 0; p < 16; p++) { int j = t + 64 * brev(p, 4); x[t][p] = cplx{in[2 * j], in[2 * j + 1]}; }
-        Fft3::pre_twist(x[t]);
-        Fft3::pass_a(t, x[t], &tb.ta_fwd[0][0], 64, t, b1.data());
+extern "C" int emul_fft8_forward(const double *in, double *out) {
+    static Fft8::Tables tb; fill_fft8_tables(tb);
+    std::vector<cplx> b1(Fft8::BUF1), b2(Fft8::BUF2);
+    static cplx x[128][8];
+    for (int t = 0; t < 128; t++) {
+        for (int p = 0; p < 8; p++) { int j = t + 128 * brev(p, 3); x[t][p] = cplx{in[2 * j], in[2 * j + 1]}; }
+        Fft8::pre_twist(x[t]);
     }
-    for (int t = 0; t < 64; t++) Fft3::pass_b(t, &tb.tb[0][0][0], b1.data(), b2.data());
-    for (int t = 0; t < 64; t++) {
-        Fft3::pass_c(t, x[t], b2.data());
-        for (int f1 = 0; f1 < 16; f1++) { out[2 * (64 * f1 + t)] = x[t][f1].re; out[2 * (64 * f1 + t) + 1] = x[t][f1].im; }
-    }
+    fft8_team(x, tb, 0, b1.data(), b2.data());
+    for (int t = 0; t < 128; t++)
+        for (int f2 = 0; f2 < 8; f2++) { out[2 * (128 * f2 + t)] = x[t][f2].re; out[2 * (128 * f2 + t) + 1] = x[t][f2].im; }
     return 0;
 }
 // inverse: X[1024] (interleaved) -> 2048 real coefficients (c[j] = re, c[j+M] = im of untwisted inverse DFT / M)
-extern "C" int emul_fft3_inverse(const double *in, double *coef) {
-    static Fft3::Tables tb; fill_fft3_tables(tb);
-    std::vector<cplx> b1(Fft3::BUF), b2(Fft3::BUF);
-    static cplx x[64][16];
-    for (int t = 0; t < 64; t++) {
-        for (int p = 0; p < 16; p++) { int f = t + 64 * brev(p, 4); x[t][p] = cplx{in[2 * f], -in[2 * f + 1]}; }
-        Fft3::pass_a(t, x[t], &tb.ta_inv[0][0], 4, t >> 4, b1.data());
-    }
-    for (int t = 0; t < 64; t++) Fft3::pass_b(t, &tb.tb[1][0][0], b1.data(), b2.data());
-    for (int t = 0; t < 64; t++) {
-        Fft3::pass_c(t, x[t], b2.data());
-        Fft3::post_twist(x[t]);
-        for (int q = 0; q < 16; q++) { coef[t + 64 * q] = x[t][q].re; coef[t + 64 * q + 1024] = -x[t][q].im; }
+extern "C" int emul_fft8_inverse(const double *in, double *coef) {
+    static Fft8::Tables tb; fill_fft8_tables(tb);
+    std::vector<cplx> b1(Fft8::BUF1), b2(Fft8::BUF2);
+    static cplx x[128][8];
+    for (int t = 0; t < 128; t++)
+        for (int p = 0; p < 8; p++) { int f = t + 128 * brev(p, 3); x[t][p] = cplx{in[2 * f], -in[2 * f + 1]}; }
+    fft8_team(x, tb, 1, b1.data(), b2.data());
+    for (int t = 0; t < 128; t++) {
+        Fft8::post_twist(x[t]);
+        for (int q = 0; q < 8; q++) { coef[t + 128 * q] = x[t][q].re; coef[t + 128 * q + 1024] = -x[t][q].im; }
     }
     return 0;
 }
@@ -239,11 +241,11 @@ extern "C" int emul_blind_rotate_lat(int n, const uint64_t *bsk_std, const uint6
     typedef uint64_t T;
     typedef BRCore<T, 32, 1, 1, 23> C;
     constexpr int N = 2048, M = 1024, K1 = 2;
-    static Fft3::Tables tb; fill_fft3_tables(tb);
+    static Fft8::Tables tb; fill_fft8_tables(tb);
     std::vector<cplx> fbsk;
     convert_bsk<T, 32, 1, 1, 23>(bsk_std, n, fbsk);
-    std::vector<cplx> b1(K1 * Fft3::BUF), b2(K1 * Fft3::BUF), D(K1 * M);
-    static cplx x[K1][64][16];
+    std::vector<cplx> b1(Fft8::BUF1), b2(Fft8::BUF2), D(K1 * M);
+    static cplx x[K1][128][8];
     for (int b = 0; b < batch; b++) {
         const uint64_t *ct = lwe + (size_t)b * (n + 1);
         std::vector<T> acc((size_t)K1 * N);
@@ -256,38 +258,32 @@ extern "C" int emul_blind_rotate_lat(int n, const uint64_t *bsk_std, const uint6
             const cplx *ggsw = &fbsk[(size_t)i * C::GGSW_CPLX];
             for (int r = 0; r < K1; r++) {
                 const T *acc_r = &acc[(size_t)r * N];
-                for (int t = 0; t < 64; t++) {
-                    for (int p = 0; p < 16; p++) {
-                        int c = t + 64 * brev(p, 4);
+                for (int t = 0; t < 128; t++) {
+                    for (int p = 0; p < 8; p++) {
+                        int c = t + 128 * brev(p, 3);
                         T d0 = rot_read<T, N>(acc_r, c, a) - acc_r[c], d1 = rot_read<T, N>(acc_r, c + M, a) - acc_r[c + M];
                         x[r][t][p] = cplx{(double)C::single_level_digit(d0), (double)C::single_level_digit(d1)};
                     }
-                    Fft3::pre_twist(x[r][t]);
-                    Fft3::pass_a(t, x[r][t], &tb.ta_fwd[0][0], 64, t, &b1[r * Fft3::BUF]);
+                    Fft8::pre_twist(x[r][t]);
                 }
-                for (int t = 0; t < 64; t++) Fft3::pass_b(t, &tb.tb[0][0][0], &b1[r * Fft3::BUF], &b2[r * Fft3::BUF]);
-                for (int t = 0; t < 64; t++) {
-                    Fft3::pass_c(t, x[r][t], &b2[r * Fft3::BUF]);
-                    for (int f1 = 0; f1 < 16; f1++) D[r * M + 64 * f1 + t] = x[r][t][f1];
-                }
+                fft8_team(x[r], tb, 0, b1.data(), b2.data());
+                for (int t = 0; t < 128; t++)
+                    for (int f2 = 0; f2 < 8; f2++) D[r * M + 128 * f2 + t] = x[r][t][f2];
             }
             for (int j = 0; j < K1; j++) {
-                for (int t = 0; t < 64; t++) {
-                    for (int p = 0; p < 16; p++) {
-                        int f = t + 64 * brev(p, 4);
+                for (int t = 0; t < 128; t++)
+                    for (int p = 0; p < 8; p++) {
+                        int f = t + 128 * brev(p, 3);
                         cplx F = cmul(ggsw[(size_t)(j * K1 + j) * M + f], D[j * M + f]);            // own row first
                         C::mac_one(F, ggsw[(size_t)((1 - j) * K1 + j) * M + f], D[(1 - j) * M + f]);
                         x[j][t][p] = cplx{F.re, -F.im};
                     }
-                    Fft3::pass_a(t, x[j][t], &tb.ta_inv[0][0], 4, t >> 4, &b1[j * Fft3::BUF]);
-                }
-                for (int t = 0; t < 64; t++) Fft3::pass_b(t, &tb.tb[1][0][0], &b1[j * Fft3::BUF], &b2[j * Fft3::BUF]);
-                for (int t = 0; t < 64; t++) {
-                    Fft3::pass_c(t, x[j][t], &b2[j * Fft3::BUF]);
-                    Fft3::post_twist(x[j][t]);
-                    for (int q = 0; q < 16; q++) {
-                        acc[(size_t)j * N + t + 64 * q] += torus_from_double<T>(x[j][t][q].re);
-                        acc[(size_t)j * N + t + 64 * q + M] += torus_from_double<T>(-x[j][t][q].im);
+                fft8_team(x[j], tb, 1, b1.data(), b2.data());
+                for (int t = 0; t < 128; t++) {
+                    Fft8::post_twist(x[j][t]);
+                    for (int q = 0; q < 8; q++) {
+                        acc[(size_t)j * N + t + 128 * q] += torus_from_double<T>(x[j][t][q].re);
+                        acc[(size_t)j * N + t + 128 * q + M] += torus_from_double<T>(-x[j][t][q].im);
                     }
                 }
             }

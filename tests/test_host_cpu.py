@@ -143,15 +143,15 @@ def test_kernel_single_cmux_matches_oracle_to_fft_precision(emul):
 
 
 def test_three_pass_fft_matches_numpy(emul):
-    # fft3.cuh (the latency kernel's 64-thread FFT): forward vs numpy's DFT of the twisted input, and the inverse round trip
+    # fft8.cuh (the latency kernel's 128-thread FFT, radix 8 x 16 x 8): forward vs numpy's DFT of the twisted input, and the inverse round trip
     rng = np.random.default_rng(11)
     x = rng.standard_normal(1024) + 1j * rng.standard_normal(1024)
     inp = np.empty(2048); inp[0::2] = x.real; inp[1::2] = x.imag
     out = np.empty(2048); coef = np.empty(2048)
-    assert emul.emul_fft3_forward(_p(inp), _p(out)) == 0
+    assert emul.emul_fft8_forward(_p(inp), _p(out)) == 0
     ref = np.fft.fft(x * np.exp(1j * np.pi * np.arange(1024) / 2048))
     assert np.abs((out[0::2] + 1j * out[1::2]) - ref).max() / np.abs(ref).max() < 2.0 ** -48
-    assert emul.emul_fft3_inverse(_p(out), _p(coef)) == 0
+    assert emul.emul_fft8_inverse(_p(out), _p(coef)) == 0
     assert np.abs((coef[:1024] + 1j * coef[1024:]) - x).max() < 2.0 ** -46
 
 

@@ -5,7 +5,9 @@
 // the iteration bound by instruction issue: 5000 SASS instructions per warp-iteration, 1.1 "no instruction" stall cycles
 // per issue because the unrolled 80 KB loop body misses the instruction cache with nobody to share the fetch
 // (profiles/r01_ncu_latency.json).  This kernel is built for that regime instead:
-//   * 64 threads per polynomial, 16 points each (fft3.cuh: 1024 = 16 x 4 x 16), 4 warps = one per scheduler;
+//   * 128 threads per polynomial, 8 points each (fft8.cuh: 1024 = 8 x 16 x 8), 8 warps = two per scheduler, one of each
+//     polynomial: the shared-memory exchanges of one overlap the butterflies of the other (round 1: 64 threads x 16 points, one
+//     warp per scheduler, shared-memory pipe 66 % + FP64 pipe 38 % busy strictly one after the other);
 //   * the forward and the inverse transform share ONE copy of the FFT code: the inverse is the forward of the conjugate,
 //     the loop over the two directions is not unrolled, direction-dependent work sits in uniform branches around it;
 //   * this iteration's Fourier GGSW (64 KB) is staged into shared memory by the TMA engine (cp.async.bulk + mbarrier)
@@ -13,7 +15,7 @@
 //   * the closed-form rotated digit (tmem_util.cuh) replaces the generic decomposition recurrence.
 // Same mathematics and same bootstrap-key layout as blind_rotate.cu (reference: fft64/crypto/bootstrap.rs:243-412,
 // fft64/crypto/ggsw.rs:477-598); the stage sequence is executed on the CPU by tests/native/emul.cpp.
-#include "fft3.cuh"
+#include "fft8.cuh"
 #include "tmem_util.cuh"
 #include "kernels.h"
 #include "twiddles.hpp"
@@ -24,17 +26,18 @@ namespace b200tfhe {
 
 namespace {
 
-constexpr int LAT_THREADS = 128, LAT_N = 2048, LAT_M = 1024, LAT_K1 = 2, LAT_BL = 23;
+constexpr int LAT_TEAM = Fft8::T, LAT_THREADS = 2 * LAT_TEAM, LAT_N = 2048, LAT_M = 1024, LAT_K1 = 2, LAT_BL = 23;
 constexpr size_t LAT_KEY_BYTES = (size_t)LAT_K1 * LAT_K1 * LAT_M * sizeof(cplx);        // 65536: one Fourier GGSW
 constexpr size_t LAT_ACC_BYTES = (size_t)LAT_K1 * LAT_N * sizeof(uint64_t);             // 32768
-constexpr size_t LAT_BUF_BYTES = (size_t)LAT_K1 * Fft3::BUF * sizeof(cplx);             // 34816 per exchange buffer
+constexpr size_t LAT_BUF1_BYTES = (size_t)LAT_K1 * Fft8::BUF1 * sizeof(cplx);           // 32768
+constexpr size_t LAT_BUF2_BYTES = (size_t)LAT_K1 * Fft8::BUF2 * sizeof(cplx);           // 36864
 constexpr size_t LAT_OFF_ACC = LAT_KEY_BYTES;
 constexpr size_t LAT_OFF_BUF1 = LAT_OFF_ACC + LAT_ACC_BYTES;
-constexpr size_t LAT_OFF_BUF2 = LAT_OFF_BUF1 + LAT_BUF_BYTES;
-constexpr size_t LAT_OFF_TAB = LAT_OFF_BUF2 + LAT_BUF_BYTES;
-constexpr size_t LAT_OFF_MBAR = LAT_OFF_TAB + sizeof(Fft3::Tables);
+constexpr size_t LAT_OFF_BUF2 = LAT_OFF_BUF1 + LAT_BUF1_BYTES;
+constexpr size_t LAT_OFF_TAB = LAT_OFF_BUF2 + LAT_BUF2_BYTES;
+constexpr size_t LAT_OFF_MBAR = LAT_OFF_TAB + sizeof(Fft8::Tables);
 constexpr size_t LAT_OFF_AHAT = LAT_OFF_MBAR + 16;
-static_assert(sizeof(Fft3::Tables) % 16 == 0, "table block keeps 16-byte alignment");
+static_assert(sizeof(Fft8::Tables) % 16 == 0, "table block keeps 16-byte alignment");
 
 size_t lat_smem_bytes(int n) { return LAT_OFF_AHAT + ((((size_t)(n + 1) * sizeof(uint16_t)) + 15) & ~(size_t)15); }
 
@@ -47,6 +50,9 @@ DEV void bulk_load(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) 
 DEV void mbarrier_expect_tx(uint32_t bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
+DEV cplx shfl_xor_cplx(cplx v, int mask) {
+    return cplx{__shfl_xor_sync(0xffffffffu, v.re, mask), __shfl_xor_sync(0xffffffffu, v.im, mask)};
+}
 #endif
 
 // BL: base log of the one-level decomposition.  PLAIN = false: the classic CMUX iteration acc += GGSW_i (.) (acc X^{a_i} - acc), n_iter = n.
@@ -57,26 +63,32 @@ template <int BL, bool PLAIN>
 __global__ void __launch_bounds__(LAT_THREADS, 1)
 blind_rotate_lat_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride, const uint64_t *__restrict__ luts,
                         const uint32_t *__restrict__ lut_idx, const cplx *__restrict__ bsk, uint64_t *__restrict__ out,
-                        size_t out_stride, int n, int mode, const Fft3::Tables *__restrict__ tables_g, int n_iter,
+                        size_t out_stride, int n, int mode, const Fft8::Tables *__restrict__ tables_g, int n_iter,
                         size_t key_ct_stride) {
 #if defined(__CUDA_ARCH__)
     typedef uint64_t T;
-    constexpr int N = LAT_N, M = LAT_M, K1 = LAT_K1;
+    constexpr int N = LAT_N, M = LAT_M, K1 = LAT_K1, TM = LAT_TEAM;
     extern __shared__ __align__(128) unsigned char smem[];
     cplx *key = reinterpret_cast<cplx *>(smem);                               // [r][j][M], refilled every iteration by TMA
     T *acc = reinterpret_cast<T *>(smem + LAT_OFF_ACC);                       // [K1][N]
-    cplx *buf1 = reinterpret_cast<cplx *>(smem + LAT_OFF_BUF1);               // [K1][BUF]; also D[r][M] between the transforms
-    cplx *buf2 = reinterpret_cast<cplx *>(smem + LAT_OFF_BUF2);
-    Fft3::Tables *tab = reinterpret_cast<Fft3::Tables *>(smem + LAT_OFF_TAB);
+    cplx *buf1 = reinterpret_cast<cplx *>(smem + LAT_OFF_BUF1);               // [K1][BUF1]
+    cplx *buf2 = reinterpret_cast<cplx *>(smem + LAT_OFF_BUF2);               // [K1][BUF2]
+    Fft8::Tables *tab = reinterpret_cast<Fft8::Tables *>(smem + LAT_OFF_TAB);
     uint16_t *ahat = reinterpret_cast<uint16_t *>(smem + LAT_OFF_AHAT);
     const uint32_t bar = smem_addr_u32(smem + LAT_OFF_MBAR);
     const uint32_t key_s = smem_addr_u32(key);
+    __shared__ uint32_t tmem_base_smem;
 
-    const int tid = threadIdx.x, r = tid >> 6, t = tid & 63;
+    const int tid = threadIdx.x, r = tid >> 7, t = tid & (TM - 1);
+    if (tid < 32) {   // 64 tensor-memory columns: the two teams hand each other their Fourier polynomial D_r through them
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_addr_u32(&tmem_base_smem)), "n"(64));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    tmem_fence_before();
     const int ct = blockIdx.x;
     bsk += (size_t)ct * key_ct_stride;
     T *acc_r = acc + r * N;
-    cplx *buf1_r = buf1 + r * Fft3::BUF, *buf2_r = buf2 + r * Fft3::BUF;
+    cplx *buf1_r = buf1 + r * Fft8::BUF1, *buf2_r = buf2 + r * Fft8::BUF2;
 
     if (tid == 0) {
         mbarrier_init(bar, 1);
@@ -85,12 +97,17 @@ blind_rotate_lat_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride, 
     {   // twiddle tables: global -> shared, once
         const int4 *src = reinterpret_cast<const int4 *>(tables_g);
         int4 *dst = reinterpret_cast<int4 *>(tab);
-        for (int e = tid; e < (int)(sizeof(Fft3::Tables) / 16); e += LAT_THREADS) dst[e] = src[e];
+        for (int e = tid; e < (int)(sizeof(Fft8::Tables) / 16); e += LAT_THREADS) dst[e] = src[e];
     }
     // modulus switch of the whole input (fft_impl/common.rs:26-43)
     const T *lwe = lwe_in + (size_t)ct * lwe_stride;
     for (int i = tid; i <= n; i += LAT_THREADS) ahat[i] = (uint16_t)(modswitch<T>(lwe[i], 11) & (2 * N - 1));
     __syncthreads();
+    tmem_fence_after();
+    // thread (r, t) and thread (1 - r, t) sit in warps w and w + 4: same lane quadrant, same lane, so what one stores in
+    // columns [32 r, 32 r + 32) the other can load (32x32b: a thread reaches only its own lane)
+    const uint32_t t_lane = tmem_base_smem + ((uint32_t)(((tid >> 5) & 3) * 32) << 16);
+    const uint32_t t_own = t_lane + (uint32_t)(32 * r), t_oth = t_lane + (uint32_t)(32 * (1 - r));
     auto fetch_key = [&](int i) {   // thread 0: this iteration's GGSW, four 16 KB rows
         mbarrier_expect_tx(bar, (uint32_t)LAT_KEY_BYTES);
         const unsigned char *src = reinterpret_cast<const unsigned char *>(bsk) + (size_t)i * LAT_KEY_BYTES;
@@ -101,106 +118,122 @@ blind_rotate_lat_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride, 
     {   // acc <- LUT * X^{-b_hat}  (polynomial_algorithms.rs:315-354)
         const T *lut = luts + (size_t)(lut_idx ? lut_idx[ct] : 0) * K1 * N + (size_t)r * N;
         const int a0 = (2 * N - (int)ahat[n]) & (2 * N - 1);
-        for (int c = t; c < N; c += 64) acc_r[c] = rot_read<T, N>(lut, c, a0);
+        for (int c = t; c < N; c += TM) acc_r[c] = rot_read<T, N>(lut, c, a0);
     }
     __syncthreads();
 
     const unsigned char *accb = reinterpret_cast<const unsigned char *>(acc_r);
     const cplx *key_own = key + (size_t)(r * K1 + r) * M + t;            // row r (own transform), column j = r
     const cplx *key_oth = key + (size_t)((1 - r) * K1 + r) * M + t;      // row 1-r, column j = r
-    const cplx *d_oth = buf1 + (1 - r) * Fft3::BUF + t;
-    cplx *d_own = buf1_r + t;
 
-    // the 32 accumulator coefficients this thread rounds into (t + 64 q, and + M) stay in registers from one
+    // the 16 accumulator coefficients this thread rounds into (t + 128 q, and + M) stay in registers from one
     // accumulation to the next decomposition; shared memory keeps the copy the rotated reads need
-    T own_re[16], own_im[16];
-    static_for<0, 16>([&](auto q) {
-        own_re[decltype(q)::value] = acc_r[t + 64 * decltype(q)::value];
-        own_im[decltype(q)::value] = acc_r[t + 64 * decltype(q)::value + M];
+    // this thread's twiddle factors (fft8.cuh), in registers for the whole blind rotation
+    const cplx twist_t = tab->twist[t];
+    const Fft8::TwB twb_fwd = tab->tb[0][t], twb_inv = tab->tb[1][t];
+    T own_re[8], own_im[8];
+    static_for<0, 8>([&](auto q) {
+        own_re[decltype(q)::value] = acc_r[t + TM * decltype(q)::value];
+        own_im[decltype(q)::value] = acc_r[t + TM * decltype(q)::value + M];
     });
 
     for (int i = 0; i < n_iter; i++) {
         const int a = PLAIN ? 0 : ahat[i];
-        cplx x[16];
+        cplx x[8];
 #pragma unroll 1
         for (int dir = 0; dir < 2; dir++) {
-            const cplx *ta;
-            int ta_stride, ta_idx;
             if (dir == 0) {
                 // rotate-subtract + one-level signed decomposition, as doubles; then the register part of the twist
                 if constexpr (PLAIN) {
                     typedef BRCore<T, 32, 1, 1, BL> DC;
-                    static_for<0, 16>([&](auto p) {
-                        constexpr int v = brev(decltype(p)::value, 4);
+                    static_for<0, 8>([&](auto p) {
+                        constexpr int v = brev(decltype(p)::value, 3);
                         x[decltype(p)::value].re = int_to_double(DC::single_level_digit(own_re[v]));
                         x[decltype(p)::value].im = int_to_double(DC::single_level_digit(own_im[v]));
                     });
                 } else {
                     const uint32_t s8 = 8u * (uint32_t)(t - a);
-                    static_for<0, 16>([&](auto p) {
-                        constexpr int v = brev(decltype(p)::value, 4);
-                        x[decltype(p)::value].re = rot_digit_f64<BL>(accb, s8 + 8u * 64u * v, own_re[v]);
-                        x[decltype(p)::value].im = rot_digit_f64<BL>(accb, s8 + 8u * 64u * v + 8u * M, own_im[v]);
+                    static_for<0, 8>([&](auto p) {
+                        constexpr int v = brev(decltype(p)::value, 3);
+                        x[decltype(p)::value].re = rot_digit_f64<BL>(accb, s8 + 8u * (uint32_t)TM * v, own_re[v]);
+                        x[decltype(p)::value].im = rot_digit_f64<BL>(accb, s8 + 8u * (uint32_t)TM * v + 8u * M, own_im[v]);
                     });
                 }
-                Fft3::pre_twist(x);
-                ta = &tab->ta_fwd[0][0]; ta_stride = 64; ta_idx = t;
+                Fft8::pre_twist(x);
             } else {
-                // x holds D_r[t + 64 f1]; publish it, then F_j = G[r][j] D_r + G[1-r][j] D_{1-r} for j = r, conjugated, in
-                // the register order pass A wants (element brev4(p))
-                static_for<0, 16>([&](auto f1) { d_own[64 * decltype(f1)::value] = x[decltype(f1)::value]; });
+                // x holds D_r[t + 128 f2]; publish it, then F_j = G[r][j] D_r + G[1-r][j] D_{1-r} for j = r, conjugated, in
+                // the register order pass A wants (element brev3(p))
+                tmem_store_cplx8(t_own, x[0], x[1], x[2], x[3], x[4], x[5], x[6], x[7]);
+                tmem_wait_st();
+                tmem_fence_before();
                 __syncthreads();
+                tmem_fence_after();
+                uint32_t dw[32];
+                tmem_ld32(t_oth, dw);
                 mbarrier_wait(bar, (uint32_t)(i & 1));
-                cplx y[16];
-                static_for<0, 16>([&](auto p) {
-                    constexpr int v = brev(decltype(p)::value, 4);
-                    cplx f = cmul(key_own[64 * v], x[v]);
-                    BRCore<T, 32, 1, 1, BL>::mac_one(f, key_oth[64 * v], d_oth[64 * v]);
-                    y[decltype(p)::value] = cplx{f.re, -f.im};
+                cplx y[8];
+                static_for<0, 8>([&](auto p) {       // own row first: needs no tensor-memory data
+                    constexpr int v = brev(decltype(p)::value, 3);
+                    y[decltype(p)::value] = cmul(key_own[TM * v], x[v]);
                 });
-                static_for<0, 16>([&](auto p) { x[decltype(p)::value] = y[decltype(p)::value]; });
-                __syncthreads();   // both teams are done with D (buf1) and with the key
+                tmem_wait_ld();
+                static_for<0, 8>([&](auto p) {
+                    constexpr int v = brev(decltype(p)::value, 3);
+                    cplx f = y[decltype(p)::value];
+                    BRCore<T, 32, 1, 1, BL>::mac_one(f, key_oth[TM * v], cplx_from_words(dw, v));
+                    x[decltype(p)::value] = cplx{f.re, -f.im};
+                });
+                tmem_fence_before();
+                __syncthreads();   // both teams are done with D (tensor memory) and with the key
+                tmem_fence_after();
                 if (tid == 0 && i + 1 < n_iter) fetch_key(i + 1);
-                ta = &tab->ta_inv[0][0]; ta_stride = 4; ta_idx = t >> 4;
             }
-            Fft3::pass_a(t, x, ta, ta_stride, ta_idx, buf1_r);
-            named_bar_sync(1 + r, 64);
-            Fft3::pass_b(t, &tab->tb[dir][0][0], buf1_r, buf2_r);
-            named_bar_sync(1 + r, 64);
-            Fft3::pass_c(t, x, buf2_r);
+            Fft8::pass_a(t, x, tab->ta, twist_t, dir == 0, buf1_r);
+            named_bar_sync(1 + r, TM);
+            {
+                cplx z[8], send[4], recv[4];
+                Fft8::pass_b_first(t, buf1_r, z, send);
+                static_for<0, 4>([&](auto e) { recv[decltype(e)::value] = shfl_xor_cplx(send[decltype(e)::value], 8); });
+                Fft8::pass_b_second(t, z, recv, dir ? twb_inv : twb_fwd, buf2_r);
+            }
+            named_bar_sync(1 + r, TM);
+            Fft8::pass_c(t, x, buf2_r);
             if (dir == 1) {
-                Fft3::post_twist(x);
+                Fft8::post_twist(x);
                 if constexpr (PLAIN) {
-                    static_for<0, 16>([&](auto q) {
+                    static_for<0, 8>([&](auto q) {
                         own_re[decltype(q)::value] = torus_from_double<T>(x[decltype(q)::value].re);
                         own_im[decltype(q)::value] = torus_from_double<T>(-x[decltype(q)::value].im);
                     });
                 } else {
-                    static_for<0, 16>([&](auto q) {
-                        const int c = t + 64 * decltype(q)::value;
+                    static_for<0, 8>([&](auto q) {
+                        const int c = t + TM * decltype(q)::value;
                         own_re[decltype(q)::value] += torus_from_double<T>(x[decltype(q)::value].re);
                         own_im[decltype(q)::value] += torus_from_double<T>(-x[decltype(q)::value].im);
                         acc_r[c] = own_re[decltype(q)::value];
                         acc_r[c + M] = own_im[decltype(q)::value];
                     });
-                    named_bar_sync(1 + r, 64);
+                    named_bar_sync(1 + r, TM);
                 }
             }
         }
     }
     if constexpr (PLAIN) {
-        static_for<0, 16>([&](auto q) {
-            acc_r[t + 64 * decltype(q)::value] = own_re[decltype(q)::value];
-            acc_r[t + 64 * decltype(q)::value + M] = own_im[decltype(q)::value];
+        static_for<0, 8>([&](auto q) {
+            acc_r[t + TM * decltype(q)::value] = own_re[decltype(q)::value];
+            acc_r[t + TM * decltype(q)::value + M] = own_im[decltype(q)::value];
         });
-        named_bar_sync(1 + r, 64);
+        named_bar_sync(1 + r, TM);
     }
 
+    tmem_fence_before();
+    __syncthreads();
+    if (tid < 32) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base_smem), "n"(64));
     T *o = out + (size_t)ct * out_stride;
     if (mode == BR_MODE_GLWE) {
-        for (int c = t; c < N; c += 64) o[(size_t)r * N + c] = acc_r[c];
+        for (int c = t; c < N; c += TM) o[(size_t)r * N + c] = acc_r[c];
     } else if (r == 0) {   // sample extract, coefficient 0 (algorithms/glwe_sample_extraction.rs:91-147), k = 1
-        for (int c = t; c < N; c += 64) o[c] = (c == 0) ? acc_r[0] : (T)(0 - acc_r[N - c]);
+        for (int c = t; c < N; c += TM) o[c] = (c == 0) ? acc_r[0] : (T)(0 - acc_r[N - c]);
     } else if (t == 0) {
         o[N] = acc_r[0];
     }
@@ -208,20 +241,20 @@ blind_rotate_lat_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride, 
 }
 
 // per-device copy of the twiddle tables, uploaded on first use
-const Fft3::Tables *lat_tables(cudaStream_t st, cudaError_t *err) {
+const Fft8::Tables *lat_tables(cudaStream_t st, cudaError_t *err) {
     static std::mutex mu;
-    static std::map<int, Fft3::Tables *> per_device;
-    static Fft3::Tables host;
+    static std::map<int, Fft8::Tables *> per_device;
+    static Fft8::Tables host;
     static bool filled = false;
     int dev = 0;
     if ((*err = cudaGetDevice(&dev)) != cudaSuccess) return nullptr;
     std::lock_guard<std::mutex> g(mu);
     auto it = per_device.find(dev);
     if (it != per_device.end()) return it->second;
-    if (!filled) { fill_fft3_tables(host); filled = true; }
-    Fft3::Tables *d = nullptr;
-    if ((*err = cudaMalloc(&d, sizeof(Fft3::Tables))) != cudaSuccess) return nullptr;
-    if ((*err = cudaMemcpyAsync(d, &host, sizeof(Fft3::Tables), cudaMemcpyHostToDevice, st)) != cudaSuccess ||
+    if (!filled) { fill_fft8_tables(host); filled = true; }
+    Fft8::Tables *d = nullptr;
+    if ((*err = cudaMalloc(&d, sizeof(Fft8::Tables))) != cudaSuccess) return nullptr;
+    if ((*err = cudaMemcpyAsync(d, &host, sizeof(Fft8::Tables), cudaMemcpyHostToDevice, st)) != cudaSuccess ||
         (*err = cudaStreamSynchronize(st)) != cudaSuccess) {
         cudaFree(d);
         return nullptr;
@@ -250,7 +283,7 @@ int br_lat_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
     if (!br_lat_supported(p)) return -1;
     if (a.batch <= 0) return 0;
     cudaError_t e = cudaSuccess;
-    const Fft3::Tables *tab = lat_tables(st, &e);
+    const Fft8::Tables *tab = lat_tables(st, &e);
     if (!tab) return (int)e;
     const size_t smem = lat_smem_bytes(a.n);
     auto kern = blind_rotate_lat_kernel<LAT_BL, false>;
@@ -265,7 +298,7 @@ int br_lat_plain_launch(const Params &p, const BRLaunch &a, int n_iter, size_t k
     if (!br_lat_plain_supported(p)) return -1;
     if (a.batch <= 0) return 0;
     cudaError_t e = cudaSuccess;
-    const Fft3::Tables *tab = lat_tables(st, &e);
+    const Fft8::Tables *tab = lat_tables(st, &e);
     if (!tab) return (int)e;
     const size_t smem = lat_smem_bytes(a.n);
 #define X(BL)                                                                                                                       \
@@ -274,7 +307,7 @@ int br_lat_plain_launch(const Params &p, const BRLaunch &a, int n_iter, size_t k
         if ((e = ensure_dynamic_smem((const void *)kern, smem)) != cudaSuccess) return (int)e;                                      \
         kern<<<a.batch, LAT_THREADS, smem, st>>>((const uint64_t *)a.lwe_in, a.lwe_stride, (const uint64_t *)a.luts, a.lut_idx,     \
                                                  (const cplx *)a.bsk, (uint64_t *)a.out, a.out_stride, a.n, a.mode, tab, n_iter,   \
-                                                 key_ct_stride);                                                                    \
+                                                 key_ct_stride);                                                                               \
         return (int)cudaGetLastError();                                                                                             \
     }
     LAT_PLAIN_INSTANCES(X)

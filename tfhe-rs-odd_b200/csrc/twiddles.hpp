@@ -2,7 +2,7 @@
 #pragma once
 #include "fft_reg.cuh"
 #include "br_big.cuh"
-#include "fft3.cuh"
+#include "fft8.cuh"
 #include <cmath>
 
 namespace b200tfhe {
@@ -48,22 +48,22 @@ inline void fill_big_tables(BigTables &t) {
     }
 }
 
-// tables of the 64-thread three-pass FFT (fft3.cuh)
-inline void fill_fft3_tables(Fft3::Tables &t) {
-    const int N = Fft3::N, M = Fft3::M;
-    for (int g2 = 0; g2 < 16; g2++) {
-        for (int tau = 0; tau < 64; tau++) t.ta_fwd[g2][tau] = root_2N((long long)tau - 64LL * (tau >> 4) * g2, N);
-        for (int u = 0; u < 4; u++) t.ta_inv[g2][u] = root_2N(-64LL * u * g2, N);
-    }
-    for (int beta = 0; beta < 64; beta++) {
-        const int j1 = beta & 15, gq = beta >> 4;
-        for (int e = 0; e < 4; e++)
-            for (int g1 = 0; g1 < 4; g1++) {
-                const long long f2 = 16 * g1 + 4 * gq + e;
-                t.tb[0][e * 4 + g1][beta] = root_2N(-4LL * j1 * f2, N);
-                cplx z = root_2N(-4LL * j1 * f2 + f2, N);
-                t.tb[1][e * 4 + g1][beta] = cplx{z.re / M, z.im / M};    // exact: M is a power of two
-            }
+// tables of the 128-thread three-pass FFT (fft8.cuh)
+inline void fill_fft8_tables(Fft8::Tables &t) {
+    const int N = Fft8::N, M = Fft8::M;
+    for (int tau = 0; tau < 128; tau++) t.twist[tau] = root_2N(tau, N);
+    for (int g = 0; g < 8; g++)
+        for (int u = 0; u < 16; u++) t.ta[g][u] = root_2N(-32LL * u * g, N);
+    for (int beta = 0; beta < 128; beta++) {
+        const long long tau0 = beta & 7, half = (beta >> 3) & 1, g = beta >> 4, c0 = g + 32 * half;
+        Fft8::TwB &f = t.tb[0][beta], &v = t.tb[1][beta];
+        f.a = root_2N(-4 * tau0 * c0, N);
+        f.b1 = root_2N(-4 * tau0 * 8, N); f.b2 = root_2N(-4 * tau0 * 16, N); f.b3 = root_2N(-4 * tau0 * 24, N);
+        f.c = root_2N(-4 * tau0 * 64, N);
+        cplx z = root_2N(-4 * tau0 * c0 + c0, N);
+        v.a = cplx{z.re / M, z.im / M};    // exact: M is a power of two
+        v.b1 = root_2N(-4 * tau0 * 8 + 8, N); v.b2 = root_2N(-4 * tau0 * 16 + 16, N); v.b3 = root_2N(-4 * tau0 * 24 + 24, N);
+        v.c = root_2N(-4 * tau0 * 64 + 64, N);
     }
 }
 
