@@ -212,3 +212,20 @@ def test_constant_table_is_reproducible():
     """fft_reg.cuh cites tools/gen_tables.py for COS128_TAB: the committed generator must reproduce it bit for bit."""
     r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "gen_tables.py"), "--check"], capture_output=True, text=True)
     assert r.returncode == 0, r.stdout + r.stderr
+
+
+def test_rust_sys_crate_matches_the_header_and_the_makefile():
+    """bindings/rust/b200tfhe-sys: lib.rs is the generated transcription of include/b200tfhe.h (every prototype), build.rs compiles
+    the same sources as csrc/Makefile."""
+    import re
+    import subprocess
+    assert subprocess.run([sys.executable, os.path.join(ROOT, "tools", "gen_rust_sys.py"), "--check"]).returncode == 0
+    rs = open(os.path.join(ROOT, "bindings", "rust", "b200tfhe-sys", "src", "lib.rs")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "b200tfhe.h")).read(), flags=re.S)
+    names = set(re.findall(r"\b(b200tfhe_[a-z0-9_]+)\s*\(", hdr))
+    assert len(names) > 80 and all(f"pub fn {n}(" in rs for n in names)
+    mk = open(os.path.join(ROOT, "tfhe-rs-odd_b200", "csrc", "Makefile")).read()
+    objs = re.search(r"^OBJS = (.*)$", mk, flags=re.M).group(1).split()
+    brs = open(os.path.join(ROOT, "bindings", "rust", "b200tfhe-sys", "build.rs")).read()
+    listed = re.findall(r'"([a-z0-9_]+)"', re.search(r"SOURCES: &\[&str\] = &\[(.*?)\];", brs, flags=re.S).group(1))
+    assert sorted(listed) == sorted(o[:-2] for o in objs)
