@@ -6,7 +6,7 @@ use std::path::PathBuf;
 use std::process::Command;
 
 const SOURCES: &[&str] = &[
-    "api", "blind_rotate", "blind_rotate_big", "blind_rotate_tmem", "blind_rotate_lat", "blind_rotate_x16", "blind_rotate_mb",
+    "api", "blind_rotate", "blind_rotate_big", "blind_rotate_tmem", "blind_rotate_lat", "blind_rotate_x16", "blind_rotate_pair", "blind_rotate_mb",
     "keyswitch", "keyswitch_tc", "misc_kernels", "wave_kernels", "gadget_kernels", "wopbs_kernels", "cmux_tree", "noalloc",
     "external_product", "multi_gpu",
 ];

@@ -15,13 +15,13 @@ from conftest import fft_bound, get_oracle, params_of
 
 pytestmark = pytest.mark.gpu
 
-BR_AUTO, BR_GENERIC, BR_TMEM, BR_LAT, BR_GENERIC_1CT, BR_X16 = 0, 1, 2, 3, 4, 6
+BR_AUTO, BR_GENERIC, BR_TMEM, BR_LAT, BR_GENERIC_1CT, BR_X16, BR_PAIR = 0, 1, 2, 3, 4, 6, 7
 BR_X16B = 600 + 4      # kernel 6 with x16_variant 4 ("all transforms first")
 BR_X16C = 600 + 12     # the same with the bootstrap key streamed through a TMA ring in shared memory
 # (oracle set, kernels that are built for it)
 KERNELS = [
     ("TOY_2_2", [BR_GENERIC, BR_TMEM, BR_LAT, BR_GENERIC_1CT]),
-    ("TOY_1_1", [BR_GENERIC]),
+    ("TOY_1_1", [BR_GENERIC, BR_PAIR]),   # BR_PAIR: six ciphertexts per CTA, two per warp (blind_rotate_pair.cu)
     ("TOY_U64", [BR_GENERIC]),
     ("TOY_U32", [BR_GENERIC, BR_X16, BR_X16B, BR_X16C]),  # the boolean shape (k 2, N 512, l 3) on the 2^32 torus; x16 = half-warp teams + tensor memory
     ("TOY_3_3", [BR_GENERIC]),          # N = 8192: br_launch falls through to blind_rotate_big_kernel
@@ -167,10 +167,10 @@ def _rot(poly, a, N, bits):
     return out
 
 
-@pytest.mark.parametrize("name,kernel", CASES + [("MESSAGE_2_CARRY_2", BR_TMEM), ("MESSAGE_2_CARRY_2", BR_LAT), ("BOOLEAN_DEFAULT", BR_X16), ("BOOLEAN_DEFAULT", BR_X16B), ("BOOLEAN_DEFAULT", BR_X16C)])
+@pytest.mark.parametrize("name,kernel", CASES + [("MESSAGE_2_CARRY_2", BR_TMEM), ("MESSAGE_2_CARRY_2", BR_LAT), ("BOOLEAN_DEFAULT", BR_X16), ("BOOLEAN_DEFAULT", BR_X16B), ("BOOLEAN_DEFAULT", BR_X16C), ("MESSAGE_1_CARRY_1", BR_PAIR)])
 def test_noiseless_key_blind_rotation_is_an_exact_rotation(ctx, name, kernel):
     import tfhe_rs_odd_b200 as t
-    o = get_oracle(name) if name not in ("MESSAGE_2_CARRY_2", "BOOLEAN_DEFAULT") else _shape_only(name)
+    o = get_oracle(name) if name not in ("MESSAGE_2_CARRY_2", "BOOLEAN_DEFAULT", "MESSAGE_1_CARRY_1") else _shape_only(name)
     N, n, bits = o.N, o.n, o.bits
     rng = np.random.default_rng(0x90 + kernel)
     s = rng.integers(0, 2, size=n)

@@ -215,7 +215,7 @@ int b200tfhe_context_set_option(b200tfhe_context *ctx, const char *key, int64_t 
     std::lock_guard<std::mutex> g(ctx->mu);
     const std::string k(key);
     if (k == "br_kernel") {
-        REQUIRE(value >= BR_AUTO && value <= BR_X16, "context_set_option: br_kernel must be 0 (auto) .. 6");
+        REQUIRE(value >= BR_AUTO && value <= BR_PAIR, "context_set_option: br_kernel must be 0 (auto) .. 7");
         ctx->opt_br_kernel = (int)value;
     } else if (k == "x16_variant") {
         br_x16_set_variant((int)value);

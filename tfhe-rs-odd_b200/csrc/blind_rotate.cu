@@ -230,6 +230,7 @@ int br_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
     if (a.force == BR_TMEM) return br_tmem_supported(p) ? br_tmem_launch(p, a, st) : -2;
     if (a.force == BR_LAT) return br_lat_supported(p) ? br_lat_launch(p, a, st) : -2;
     if (a.force == BR_X16) return br_x16_supported(p) ? br_x16_launch(p, a, st) : -2;
+    if (a.force == BR_PAIR) return br_pair_supported(p) ? br_pair_launch(p, a, st) : -2;
 #ifdef B200TFHE_BUILD_WS
     if (a.force == BR_WS) return br_ws_supported(p) ? br_ws_launch(p, a, st) : -2;
 #else
@@ -266,6 +267,8 @@ int br_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
             const int wx = (a.batch + 8 * sms - 1) / (8 * sms), wg = (a.batch + 4 * sms - 1) / (4 * sms);
             if (3 * wx <= 2 * wg) return br_x16_launch(p, a, st);
         }
+        // PARAM_MESSAGE_1_CARRY_1 shape: six ciphertexts per CTA once there is more than a ciphertext per SM-slot of the generic kernel
+        if (br_pair_supported(p) && a.batch >= 5 * 148) return br_pair_launch(p, a, st);
     }
     if (a.batch < 3 * 148 || a.force == BR_GENERIC_1CT) {
 #define X(T, R, K, L, BL, CTS) \

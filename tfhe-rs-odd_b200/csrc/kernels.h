@@ -52,7 +52,7 @@ struct BRLaunch {
     void *mb_scratch = nullptr;
     int mb_lat_max = 0;
 };
-enum { BR_AUTO = 0, BR_GENERIC = 1, BR_TMEM = 2, BR_LAT = 3, BR_GENERIC_1CT = 4, BR_WS = 5, BR_X16 = 6 };
+enum { BR_AUTO = 0, BR_GENERIC = 1, BR_TMEM = 2, BR_LAT = 3, BR_GENERIC_1CT = 4, BR_WS = 5, BR_X16 = 6, BR_PAIR = 7 };
 
 // blind_rotate.cu
 int br_supported(const Params &p);  // returns team radix R (16/32) or 0
@@ -72,6 +72,10 @@ int br_tmem_launch(const Params &p, const BRLaunch &a, cudaStream_t st);
 int br_x16_supported(const Params &p);
 int br_x16_launch(const Params &p, const BRLaunch &a, cudaStream_t st);
 void br_x16_set_variant(int v);
+
+// blind_rotate_pair.cu (k = 3, N = 512, one level: six ciphertexts per CTA, two per warp)
+int br_pair_supported(const Params &p);
+int br_pair_launch(const Params &p, const BRLaunch &a, cudaStream_t st);
 
 // blind_rotate_ws.cu (same parameter set; warp-specialised: Fourier warp + torus warp per ciphertext).  A measured-and-rejected
 // experiment: compiled only with `make WS=1` (-DB200TFHE_BUILD_WS), never part of the default library
