@@ -40,7 +40,7 @@ blind_rotate_big_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const T
     const int tid = threadIdx.x;
     const int ct = blockIdx.x;
     if (ct >= batch) return;
-    if (tid < 32) {   // tensor-memory columns [0,256): the Fourier accumulators of the 8 warps; [256,320): second-level digits
+    if (tid < 32) {   // all 512 tensor-memory columns: the transformed polynomials of an iteration (see the main loop)
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(&tmem_base_smem)), "n"(512));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
@@ -61,91 +61,91 @@ blind_rotate_big_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const T
     }
     __syncthreads();
 
-    // Fourier accumulators F[j][p] live in TENSOR MEMORY between the (level, row) steps of an iteration (tcgen05.st/ld, 32x32b:
-    // thread = TMEM lane; warps w and w+4 share a lane quadrant and use columns [0,128) / [128,256)).  That frees 128 registers,
-    // which hold the step's 32 bootstrap-key values instead: their loads are issued BEFORE the step's digits + forward FFT, so
-    // the L2 latency that used to be exposed at every multiply-accumulate (long_scoreboard 4.2 / issue,
-    // profiles/r01_ncu_other_kernels.json) is covered by the transform.
+    // Round 2: ALL forward transforms of an iteration first, then the Fourier product.  The L*K1 transformed polynomials D[s]
+    // (s = t*K1 + r, 16 complex values per thread each) are parked in TENSOR MEMORY (tcgen05.st/ld, 32x32b: thread = TMEM lane;
+    // warps w and w+4 share a lane quadrant and use columns [0,256) / [256,512): 4 x 64 columns per thread = the whole TMEM).  A
+    // thread reads back exactly what it stored (position p*256 + tid of every polynomial is produced and consumed by thread tid), so
+    // no barrier separates the two phases.  What that buys over round 1 (Fourier accumulators in tensor memory, one
+    // multiply-accumulate per transform): the forward phase holds no bootstrap-key registers (round 1: 128 of 255, 340 bytes of
+    // spill), and the product phase is a software pipeline -- the key values and the D values of step s+1 are requested before step
+    // s is multiplied -- with the Fourier accumulator of ONE output polynomial in registers, handed to the inverse transform directly.
+    // Summation order: level L down to 1, rows ascending, as the reference (ggsw.rs:524-577).
     const int warp = tid >> 5;
-    const uint32_t t_f = tmem_base_smem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((warp >> 2) * 128);
-    // L = 2: the decomposition of a row runs ONCE per iteration; the level-(L-1) digits wait in tensor memory (16 packed words per
-    // thread and row) for their own step, which keeps the reference's summation order (level-major) at half the integer work
-    const uint32_t t_dig = tmem_base_smem + ((uint32_t)((warp & 3) * 32) << 16) + 256u + (uint32_t)((warp >> 2) * (16 * K1));
+    const uint32_t t_d = tmem_base_smem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((warp >> 2) * 256);
+    constexpr int NS = L * K1;     // transforms per iteration
+    static_assert(NS * 64 * 2 <= 512, "the transformed polynomials of an iteration must fit the tensor memory");
 
     for (int i = 0; i < n; i++) {
         const int a = ahat[i];
         const cplx *ggsw = bsk + (size_t)i * C::GGSW_CPLX;
-        // level L down to 1 (t ascending), rows ascending: the reference's summation order (ggsw.rs:524-577); both loops
-        // rolled: one copy of the forward transform in the instruction stream
+        // ---- forward phase: row by row; the decomposition of a row runs once, its level-(L-1) digits wait packed in registers ------
+        // (measured and rejected: computing the register-only first half of the NEXT transform between the exchange loads of the
+        // current one and their use -- 374 ms against 306 ms for 2048 ciphertexts: two 16-point register sets do not schedule well)
 #pragma unroll 1
-        for (int s = 0; s < L * K1; s++) {
-            const int t = s / K1, r = s % K1, lvl = L - 1 - t;
-            // key values of output polynomial 0: issued before the transform; those of polynomial j+1 while polynomial j is
-            // multiplied (64 registers in flight at a time: 128 spilled)
-            const cplx *gbase = ggsw + (size_t)(lvl * K1 + r) * K1 * C::M + tid;
-            cplx gv[P];
-            static_for<0, P>([&](auto p) { gv[decltype(p)::value] = ldg_stream(gbase + decltype(p)::value * 256); });
+        for (int r = 0; r < K1; r++) {
             cplx x[P];
-            if constexpr (L == 2) {
-                uint32_t packed[P];
-                if (t == 0) {
-                    C::digits_both(tid, acc + (size_t)r * N, a, x, packed);
-                    tmem_st16(t_dig + (uint32_t)(r * 16), packed);     // completed by the tmem_wait_st at the end of the step
+            uint32_t packed[P];
+            if constexpr (L == 2) C::digits_both(tid, acc + (size_t)r * N, a, x, packed);
+#pragma unroll 1
+            for (int t = 0; t < L; t++) {
+                if constexpr (L == 2) {
+                    if (t == 1) C::digits_unpack(packed, x);
                 } else {
-                    tmem_ld16(t_dig + (uint32_t)(r * 16), packed);
-                    tmem_wait_ld();
-                    C::digits_unpack(packed, x);
+                    C::digits_rt(tid, acc + (size_t)r * N, a, t, x);
                 }
-            } else {
-                C::digits_rt(tid, acc + (size_t)r * N, a, t, x);
+                __syncthreads();               // previous user of S1 is done
+                C::fwdA(tid, x, S1, ta, tq);
+                __syncthreads();
+                C::fwdB_load(tid, x, S1);
+                __syncwarp();
+                C::fwdB_pass1(tid, x, S1, tb);
+                __syncwarp();
+                C::fwdB_pass2(tid, x, S1);
+                const uint32_t slot = t_d + (uint32_t)((t * K1 + r) * 64);
+                tmem_store_cplx8(slot, x[0], x[1], x[2], x[3], x[4], x[5], x[6], x[7]);
+                tmem_store_cplx8(slot + 32, x[8], x[9], x[10], x[11], x[12], x[13], x[14], x[15]);
             }
-            __syncthreads();               // previous user of S1 is done
-            C::fwdA(tid, x, S1, ta, tq);
-            __syncthreads();
-            C::fwdB_load(tid, x, S1);
-            __syncwarp();
-            C::fwdB_pass1(tid, x, S1, tb);
-            __syncwarp();
-            C::fwdB_pass2(tid, x, S1);
-            static_for<0, K1>([&](auto j) {
-                cplx f[P], gn[P];
-                if constexpr (decltype(j)::value + 1 < K1) {
-                    static_for<0, P>([&](auto p) { gn[decltype(p)::value] = ldg_stream(gbase + (size_t)(decltype(j)::value + 1) * C::M + decltype(p)::value * 256); });
-                }
-                if (s == 0) {
-                    static_for<0, P>([&](auto p) { f[decltype(p)::value] = cplx{0.0, 0.0}; });
-                } else {
-                    uint32_t v0[32], v1[32];
-                    tmem_ld32(t_f + decltype(j)::value * 64, v0);
-                    tmem_ld32(t_f + decltype(j)::value * 64 + 32, v1);
-                    tmem_wait_ld();
-                    static_for<0, 8>([&](auto e) {
-                        f[decltype(e)::value] = cplx_from_words(v0, decltype(e)::value);
-                        f[8 + decltype(e)::value] = cplx_from_words(v1, decltype(e)::value);
-                    });
-                }
-                C::mac_one_poly(gv, x, f);
-                tmem_store_cplx8(t_f + decltype(j)::value * 64, f[0], f[1], f[2], f[3], f[4], f[5], f[6], f[7]);
-                tmem_store_cplx8(t_f + decltype(j)::value * 64 + 32, f[8], f[9], f[10], f[11], f[12], f[13], f[14], f[15]);
-                if constexpr (decltype(j)::value + 1 < K1) {
-                    static_for<0, P>([&](auto p) { gv[decltype(p)::value] = gn[decltype(p)::value]; });
-                }
-            });
-            tmem_wait_st();
         }
-        static_for<0, K1>([&](auto j) {
-            cplx x[P];
-            {
-                uint32_t v0[32], v1[32];
-                tmem_ld32(t_f + decltype(j)::value * 64, v0);
-                tmem_ld32(t_f + decltype(j)::value * 64 + 32, v1);
-                tmem_wait_ld();
-                static_for<0, P>([&](auto pp) {
-                    constexpr int p = brev(decltype(pp)::value, C::LOGP);
-                    if constexpr (p < 8) x[decltype(pp)::value] = cplx_from_words(v0, p);
-                    else x[decltype(pp)::value] = cplx_from_words(v1, p - 8);
+        tmem_wait_st();
+        // ---- product + inverse phase, one output polynomial at a time ----------------------------------------------------------------
+        static_for<0, K1>([&](auto j_) {
+            constexpr int j = decltype(j_)::value;
+            cplx f[P];
+            static_for<0, P>([&](auto p) { f[decltype(p)::value] = cplx{0.0, 0.0}; });
+            // half-steps h = 2 s + e: positions p = 8 e .. 8 e + 7 of transform s; the loads of half-step h + 1 are in flight while h is used
+            auto key_ptr = [&](int s) {
+                const int t = s / K1, r = s % K1, lvl = L - 1 - t;
+                return ggsw + ((size_t)(lvl * K1 + r) * K1 + j) * C::M + tid;
+            };
+            // key values: a ring of KD register slices (8 positions each), KD - 1 half-steps ahead of their use: with 256 threads that
+            // is (KD - 1) x 32 KB in flight against ~700 cycles of L2 latency; D values: one half-step ahead (tensor memory is close)
+            constexpr int KD = 2, NH = 2 * NS;
+            cplx g[KD][8];
+            uint32_t d[2][32];
+            auto load_key = [&](auto hh) {
+                constexpr int h = decltype(hh)::value;
+                const cplx *kp = key_ptr(h / 2) + (h & 1) * 8 * 256;
+                static_for<0, 8>([&](auto e) { g[h % KD][decltype(e)::value] = ldg_stream(kp + decltype(e)::value * 256); });
+            };
+            static_for<0, KD - 1>([&](auto hh) { load_key(hh); });
+            tmem_ld32(t_d, d[0]);
+            static_for<0, NH>([&](auto h_) {
+                constexpr int h = decltype(h_)::value, e8 = (h & 1) * 8;
+                if constexpr (h + KD - 1 < NH) load_key(std::integral_constant<int, h + KD - 1>{});
+                tmem_wait_ld();                       // the D values of half-step h (requested one half-step ago)
+                if constexpr (h + 1 < NH) tmem_ld32(t_d + (uint32_t)(((h + 1) / 2) * 64 + ((h + 1) & 1) * 32), d[(h + 1) & 1]);
+                static_for<0, 8>([&](auto e) {
+                    const cplx kv = g[h % KD][decltype(e)::value];
+                    const cplx dv = cplx_from_words(d[h & 1], decltype(e)::value);
+                    cplx &o = f[e8 + decltype(e)::value];
+                    o.re = fma_(kv.re, dv.re, o.re);
+                    o.re = fma_(-kv.im, dv.im, o.re);
+                    o.im = fma_(kv.re, dv.im, o.im);
+                    o.im = fma_(kv.im, dv.re, o.im);
                 });
-            }
+            });
+            cplx x[P];
+            static_for<0, P>([&](auto pp) { x[decltype(pp)::value] = f[brev(decltype(pp)::value, C::LOGP)]; });
             __syncthreads();
             C::invA(tid, x, S1, tb);
             __syncwarp();
@@ -154,7 +154,7 @@ blind_rotate_big_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const T
             C::invB_store(tid, x, S1);
             __syncthreads();
             C::invC(tid, x, S1, ta, tq);
-            C::accumulate(tid, x, acc + (size_t)decltype(j)::value * N);
+            C::accumulate(tid, x, acc + (size_t)j * N);
         });
         __syncthreads();                        // acc complete before the next iteration's rotated reads
     }

@@ -120,14 +120,21 @@ template <typename T, int K, int L, int BASE_LOG> struct BigCore {
         else return cmul(ta[K1_ & 3][tid], tq[K1_ >> 2][tid]);
     }
     HD static void fwdA(int tid, cplx (&x)[P], cplx *S1, const cplx (*ta)[TH], const cplx (*tq)[TH]) {
+        fwdA_compute(tid, x, ta, tq);
+        fwdA_store(tid, x, S1);
+    }
+    // the two halves of fwdA: everything that stays in registers (twist, radix-16 pass, middle twiddle), and the exchange store --
+    // a kernel can compute the first half of the NEXT transform while the exchange of the current one is in flight
+    HD static void fwdA_compute(int tid, cplx (&x)[P], const cplx (*ta)[TH], const cplx (*tq)[TH]) {
         static_for<0, P>([&](auto p) {
             constexpr int m = brev(decltype(p)::value, LOGP);
             x[decltype(p)::value] = cmul_root<m * TWQ>(x[decltype(p)::value]);
         });
         fft_dit<P, -1>(x);
-        static_for<0, P>([&](auto k1) {
-            S1[decltype(k1)::value * TH + tid] = cmul(x[decltype(k1)::value], mid_tw<decltype(k1)::value>(tid, ta, tq));
-        });
+        static_for<0, P>([&](auto k1) { x[decltype(k1)::value] = cmul(x[decltype(k1)::value], mid_tw<decltype(k1)::value>(tid, ta, tq)); });
+    }
+    HD static void fwdA_store(int tid, const cplx (&x)[P], cplx *S1) {
+        static_for<0, P>([&](auto k1) { S1[decltype(k1)::value * TH + tid] = x[decltype(k1)::value]; });
     }
     HD static void fwdB_load(int tid, cplx (&x)[P], const cplx *S1) {
         const int team = tid >> 4, lane = tid & 15;
