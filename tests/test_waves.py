@@ -116,6 +116,31 @@ def test_trivium_keystream_on_device(ctx):
 
 
 @pytest.mark.gpu
+def test_trivium_bool_keystream_on_device(ctx):
+    """The FheBool variant (apps/trivium/src/trivium/trivium_bool.rs): 14 boolean gate bootstraps per step in three waves at
+    boolean DEFAULT_PARAMETERS; decrypted bits equal plain Trivium (stream 0 = the all-zero eSTREAM vector)."""
+    import tfhe_rs_odd_b200 as t
+    from tfhe_rs_odd_b200.trivium import BOOL_FALSE, BOOL_TRUE, TriviumStreamBool, trivium_reference_bits
+    o = get_oracle("BOOLEAN_DEFAULT")
+    p = params_of(o)
+    bsk = t.convert_standard_lwe_bootstrap_key_to_fourier(ctx, p, o.bsk.astype(np.uint32))
+    ksk = t.LweKeyswitchKey.upload(ctx, p, o.ksk.astype(np.uint32))
+    rng = np.random.default_rng(4)
+    S = 2
+    keys, ivs = rng.integers(0, 2, (S, 80)), rng.integers(0, 2, (S, 80))
+    keys[0, :] = 0; ivs[0, :] = 0
+    pts = np.where(keys.reshape(-1) == 1, BOOL_TRUE, BOOL_FALSE).astype(np.uint64)
+    key_cts = o.encrypt(pts, "small", seed=0x7718).astype(np.uint32).reshape(S, 80, -1)
+    tr = TriviumStreamBool(ctx, p, ksk, bsk, o.boolean_lut().astype(np.uint32), key_cts, ivs)
+    out = tr.next_64()
+    assert len(tr.waves_run) == 19 and all(w == (64 * S * g, 64 * S * g) for batch in tr.waves_run for w, g in zip(batch, (6, 4, 4)))
+    for s in range(S):
+        bits = o.decode_bool(o.phase(out[s].astype(np.uint64), "small")).astype(np.int64)
+        assert np.array_equal(bits, trivium_reference_bits(keys[s], ivs[s], 64)), s
+    tr.pool.close()
+
+
+@pytest.mark.gpu
 def test_radix_multiplication_on_device(ctx):
     """BASELINE configs[3] at full width: FheUint32 = 16 blocks at PARAM_MESSAGE_2_CARRY_2, schoolbook product in the
     structure of unchecked_mul_parallelized (radix_parallel/mul.rs:329-424): one wave of bivariate block products, then
