@@ -61,6 +61,50 @@ def _server_key(ctx, o):
     return p, ksk, bsk, shortint.ServerKey(ksk, bsk, mm, mm, "ks_pbs")
 
 
+def _bits_of_hex(h):
+    """kreyvium/test.rs:135-156: byte i of the string -> bits 8i .. 8i+7, least significant first."""
+    return [(int(h[i:i + 2], 16) >> j) & 1 for i in range(0, len(h), 2) for j in range(8)]
+
+
+def test_plain_kreyvium_model_matches_reference_vectors():
+    """apps/trivium/src/kreyvium/test.rs:80-168 (values from renaud1239/Kreyvium)."""
+    from tfhe_rs_odd_b200.trivium import hex_lsb_first, kreyvium_reference_bits
+    z = [0] * 128
+    one = [1] + [0] * 127
+    assert hex_lsb_first(kreyvium_reference_bits(z, z, 64)) == "26DCF1F4BC0F1922"
+    assert hex_lsb_first(kreyvium_reference_bits(one, z, 64)) == "4FD421D4DA3D2C8A"
+    assert hex_lsb_first(kreyvium_reference_bits(z, one, 64)) == "C9217BA0D762ACA1"
+    key, iv = _bits_of_hex("0053A6F94C9FF24598EB000000000000"), _bits_of_hex("0D74DB42A91077DE45AC000000000000")
+    assert hex_lsb_first(kreyvium_reference_bits(key, iv, 64)) == "D1F0303482061111"
+
+
+@pytest.mark.gpu
+def test_kreyvium_bool_keystream_on_device(ctx):
+    """KreyviumStream<FheBool> (apps/trivium/src/kreyvium/kreyvium.rs): 15 gate bootstraps per step in three waves; stream 0 is the
+    reference's test vector 4, stream 1 random; 128 keystream bits so that both halves of the rotating key / IV registers are used."""
+    import tfhe_rs_odd_b200 as t
+    from tfhe_rs_odd_b200.trivium import BOOL_FALSE, BOOL_TRUE, KreyviumStreamBool, hex_lsb_first, kreyvium_reference_bits
+    o = get_oracle("BOOLEAN_DEFAULT")
+    p = params_of(o)
+    bsk = t.convert_standard_lwe_bootstrap_key_to_fourier(ctx, p, o.bsk.astype(np.uint32))
+    ksk = t.LweKeyswitchKey.upload(ctx, p, o.ksk.astype(np.uint32))
+    rng = np.random.default_rng(5)
+    S = 2
+    keys, ivs = rng.integers(0, 2, (S, 128)), rng.integers(0, 2, (S, 128))
+    keys[0], ivs[0] = _bits_of_hex("0053A6F94C9FF24598EB000000000000"), _bits_of_hex("0D74DB42A91077DE45AC000000000000")
+    pts = np.where(keys.reshape(-1) == 1, BOOL_TRUE, BOOL_FALSE).astype(np.uint64)
+    key_cts = o.encrypt(pts, "small", seed=0x7719).astype(np.uint32).reshape(S, 128, -1)
+    kr = KreyviumStreamBool(ctx, p, ksk, bsk, o.boolean_lut().astype(np.uint32), key_cts, ivs)
+    out = np.concatenate([kr.next_64(), kr.next_64()], axis=1)
+    assert all(w == (64 * S * g, 64 * S * g) for batch in kr.waves_run for w, g in zip(batch, (6, 5, 4)))
+    for s in range(S):
+        bits = o.decode_bool(o.phase(out[s].astype(np.uint64), "small")).astype(np.int64)
+        assert np.array_equal(bits, kreyvium_reference_bits(keys[s], ivs[s], 128)), s
+    bits0 = o.decode_bool(o.phase(out[0, :64].astype(np.uint64), "small")).astype(np.int64)
+    assert hex_lsb_first(list(bits0)) == "D1F0303482061111"
+    kr.pool.close()
+
+
 @pytest.mark.gpu
 def test_radix_addition_with_carry_propagation(ctx):
     """16-bit radix integers (8 blocks of 2 message bits at PARAM_MESSAGE_2_CARRY_2): block-wise unchecked_add, then the
