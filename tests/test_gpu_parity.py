@@ -423,3 +423,30 @@ def test_partial_last_wave_runs_on_the_latency_kernel(ctx):
     finally:
         ctx.set_option("br_kernel", 0)
     assert np.array_equal(got[:main], tm) and np.array_equal(got[main:], lt)
+
+
+@pytest.mark.gpu
+def test_pair_kernel_dispatch_and_ragged_last_cta(ctx):
+    """1_1 shape: batches of at least 740 ciphertexts go to blind_rotate_pair_kernel (six per CTA); a batch that does not fill the
+    last CTA must give, ciphertext by ciphertext, what the forced pair kernel and (within f64 summation order) the generic kernel give."""
+    import tfhe_rs_odd_b200 as t
+    o = get_oracle("TOY_1_1")
+    p, bsk, ksk = _keys(ctx, o)
+    B = 745                                   # 124 full CTAs + one with a single live ciphertext
+    msgs = np.arange(B) % o.pmod
+    cts = o.encrypt(o.encode(msgs), "small", seed=0x7A12)
+    lut = o.lut(lambda x: (x + 1) % o.pmod)
+    auto = t.programmable_bootstrap_lwe_ciphertext(cts, lut, bsk)
+    assert np.array_equal(o.decode(o.phase(auto, "big")) % o.pmod, (msgs + 1) % o.pmod)
+    try:
+        ctx.set_option("br_kernel", 7)
+        pair = t.programmable_bootstrap_lwe_ciphertext(cts, lut, bsk)
+        small = t.programmable_bootstrap_lwe_ciphertext(cts[:5], lut, bsk)       # fewer than one CTA
+        ctx.set_option("br_kernel", 1)
+        gen = t.programmable_bootstrap_lwe_ciphertext(cts, lut, bsk)
+    finally:
+        ctx.set_option("br_kernel", 0)
+    assert np.array_equal(auto, pair) and np.array_equal(small, pair[:5])
+    d = np.abs((o.phase(pair, "big") - o.phase(gen, "big")).astype(np.int64).astype(np.float64)) / 2.0 ** 64
+    assert d.max() < phase_bound(o)
+    assert np.array_equal(o.decode(o.phase(gen, "big")), o.decode(o.phase(pair, "big")))

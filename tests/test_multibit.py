@@ -224,3 +224,29 @@ def test_gpu_multibit_rejects_bad_arguments(ctx):
     assert cb.grouping_factor == 1
     with pytest.raises(t.B200TfheError, match="multi-bit"):
         t.core_crypto.multi_bit_programmable_bootstrap_lwe_ciphertext(np.zeros(classic.n + 1, np.uint64), classic.lut(lambda x: x), cb)
+
+
+@pytest.mark.gpu
+def test_gpu_multibit_latency_path_boundary(ctx):
+    """mb_lat_max is the largest batch on the two-kernel path: one ciphertext more runs the fused kernel; both sides decrypt, and the
+    option can move the boundary."""
+    import tfhe_rs_odd_b200 as t
+    o = get_oracle("TOY_MB22_G3")
+    p, bsk, ksk = _keys(ctx, o)
+    B = 149
+    msgs = np.arange(B) % o.pmod
+    cts = o.encrypt(o.encode(msgs), under="small", std=1e-9)
+    lut = o.lut(_f(o))
+    want = np.array([_f(o)(int(m)) for m in msgs], np.uint64)
+    for batch, launches in ((148, 2), (149, 1)):
+        n0 = ctx.launch_count
+        got = t.core_crypto.multi_bit_programmable_bootstrap_lwe_ciphertext(cts[:batch], lut, bsk)
+        assert ctx.launch_count - n0 == launches, batch
+        assert np.array_equal(o.decode(o.phase(got)), want[:batch])
+    ctx.set_option("mb_lat_max", 10)
+    try:
+        n0 = ctx.launch_count
+        t.core_crypto.multi_bit_programmable_bootstrap_lwe_ciphertext(cts[:11], lut, bsk)
+        assert ctx.launch_count - n0 == 1
+    finally:
+        ctx.set_option("mb_lat_max", 148)
