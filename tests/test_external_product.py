@@ -16,11 +16,12 @@ from conftest import fft_bound, get_oracle, params_of
 pytestmark = pytest.mark.gpu
 
 BR_AUTO, BR_GENERIC, BR_TMEM, BR_LAT, BR_GENERIC_1CT, BR_X16, BR_PAIR = 0, 1, 2, 3, 4, 6, 7
+BR_LAT_1SM = 13        # kernel 3 with lat_cluster_max = 0: one CTA per ciphertext (default for small batches: a two-CTA cluster)
 BR_X16B = 600 + 4      # kernel 6 with x16_variant 4 ("all transforms first")
 BR_X16C = 600 + 12     # the same with the bootstrap key streamed through a TMA ring in shared memory
 # (oracle set, kernels that are built for it)
 KERNELS = [
-    ("TOY_2_2", [BR_GENERIC, BR_TMEM, BR_LAT, BR_GENERIC_1CT]),
+    ("TOY_2_2", [BR_GENERIC, BR_TMEM, BR_LAT, BR_LAT_1SM, BR_GENERIC_1CT]),
     ("TOY_1_1", [BR_GENERIC, BR_PAIR]),   # BR_PAIR: six ciphertexts per CTA, two per warp (blind_rotate_pair.cu)
     ("TOY_U64", [BR_GENERIC]),
     ("TOY_U32", [BR_GENERIC, BR_X16, BR_X16B, BR_X16C]),  # the boolean shape (k 2, N 512, l 3) on the 2^32 torus; x16 = half-warp teams + tensor memory
@@ -46,12 +47,17 @@ class _kernel:
         self.ctx, self.which = ctx, which
 
     def __enter__(self):
+        if self.which == BR_LAT_1SM:
+            self.ctx.set_option("br_kernel", BR_LAT)
+            self.ctx.set_option("lat_cluster_max", 0)
+            return
         self.ctx.set_option("br_kernel", self.which // 100 if self.which >= 100 else self.which)
         self.ctx.set_option("x16_variant", self.which % 100 if self.which >= 100 else 0)
 
     def __exit__(self, *a):
         self.ctx.set_option("br_kernel", BR_AUTO)
         self.ctx.set_option("x16_variant", -1)      # back to the default organisation
+        self.ctx.set_option("lat_cluster_max", 74)
 
 
 def _bsk(ctx, o):
@@ -167,7 +173,7 @@ def _rot(poly, a, N, bits):
     return out
 
 
-@pytest.mark.parametrize("name,kernel", CASES + [("MESSAGE_2_CARRY_2", BR_TMEM), ("MESSAGE_2_CARRY_2", BR_LAT), ("BOOLEAN_DEFAULT", BR_X16), ("BOOLEAN_DEFAULT", BR_X16B), ("BOOLEAN_DEFAULT", BR_X16C), ("MESSAGE_1_CARRY_1", BR_PAIR)])
+@pytest.mark.parametrize("name,kernel", CASES + [("MESSAGE_2_CARRY_2", BR_TMEM), ("MESSAGE_2_CARRY_2", BR_LAT), ("MESSAGE_2_CARRY_2", BR_LAT_1SM), ("BOOLEAN_DEFAULT", BR_X16), ("BOOLEAN_DEFAULT", BR_X16B), ("BOOLEAN_DEFAULT", BR_X16C), ("MESSAGE_1_CARRY_1", BR_PAIR)])
 def test_noiseless_key_blind_rotation_is_an_exact_rotation(ctx, name, kernel):
     import tfhe_rs_odd_b200 as t
     o = get_oracle(name) if name not in ("MESSAGE_2_CARRY_2", "BOOLEAN_DEFAULT", "MESSAGE_1_CARRY_1") else _shape_only(name)

@@ -54,7 +54,7 @@ class Context:
         self.check(self._lib.b200tfhe_synchronize(self._h))
 
     def set_option(self, key, value):
-        """Tuning / test knob of this context (b200tfhe_context_set_option): "br_kernel", "lat_max", "mb_lat_max", "ks_tensor_core", "ks_tc_min", "chunk_min"."""
+        """Tuning / test knob of this context (b200tfhe_context_set_option): "br_kernel", "lat_max", "lat_cluster_max", "mb_lat_max", "ks_tensor_core", "ks_tc_min", "chunk_min"."""
         self.check(self._lib.b200tfhe_context_set_option(self._h, key.encode(), int(value)))
 
     @property

@@ -57,6 +57,7 @@ struct b200tfhe_context {
     // tuning / test knobs (b200tfhe_context_set_option); the defaults are what production uses
     int opt_br_kernel = BR_AUTO;     // which blind-rotation kernel (kernels.h: BR_AUTO .. BR_WS)
     int opt_lat_max = 2 * 148;       // largest batch on the one-ciphertext-per-SM latency kernel
+    int opt_lat_cluster_max = 74;    // largest batch that gives every ciphertext a two-CTA cluster (two SMs) on the latency kernel
     int opt_mb_lat_max = 148;        // multi-bit keys: largest batch on the two-kernel latency path (16-24 MB of scratch per ciphertext)
     int opt_ks_tensor_core = 1;      // 0: CUDA-core keyswitch even where the tensor-core planes exist
     int opt_ks_tc_min = 1;           // smallest batch on the tensor-core keyswitch
@@ -222,6 +223,9 @@ int b200tfhe_context_set_option(b200tfhe_context *ctx, const char *key, int64_t 
     } else if (k == "lat_max") {
         REQUIRE(value >= 0 && value <= (1 << 20), "context_set_option: lat_max out of range");
         ctx->opt_lat_max = (int)value;
+    } else if (k == "lat_cluster_max") {
+        REQUIRE(value >= 0 && value <= 4096, "context_set_option: lat_cluster_max out of range (0 .. 4096)");
+        ctx->opt_lat_cluster_max = (int)value;
     } else if (k == "mb_lat_max") {
         REQUIRE(value >= 0 && value <= 4096, "context_set_option: mb_lat_max out of range (0 .. 4096)");
         ctx->opt_mb_lat_max = (int)value;
@@ -513,6 +517,7 @@ static int br_dev_locked(b200tfhe_context *ctx, const b200tfhe_bsk *bsk, const v
                p.n, (int)batch, mode, tw_fwd(ctx, R), tw_inv(ctx, R)};
     a.force = ctx->opt_br_kernel;
     a.lat_max = ctx->opt_lat_max;
+    a.lat_cluster_max = ctx->opt_lat_cluster_max;
     if (bsk->grouping && (int)batch <= ctx->opt_mb_lat_max) {
         if (const size_t need = br_mb_lat_scratch_bytes(p, bsk->grouping, (int)batch)) {
             CK(ctx->ws.get(Workspace::MBK, need, &a.mb_scratch));

@@ -240,6 +240,193 @@ blind_rotate_lat_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride, 
 #endif
 }
 
+// ---- one ciphertext on a CLUSTER of two CTAs (two SMs): CTA r owns polynomial row r -------------------------------------------------
+// Each CTA runs one 128-thread team (one warp per scheduler) with its own accumulator row, exchange buffers and the key COLUMN
+// j = r (two 16 KB blocks per iteration, by TMA).  The only data that crosses between the SMs is the transformed polynomial D_r: every
+// thread stores its eight values into the PEER's shared memory (st.shared::cluster through distributed shared memory), the cluster
+// barrier (arrive.release right after the stores, wait.acquire after the product with the CTA's own row) publishes them; the landing
+// buffer is double-buffered by iteration parity so one barrier per iteration suffices.  Half the shared-memory traffic and half the
+// FP64 work per SM; the price is the 16 KB that cross at ~20 B/clk and the barrier (~400 cycles).  Used for batches of at most
+// `lat_cluster_max` ciphertexts (two SMs each).
+constexpr size_t L2_KEY_BYTES = LAT_KEY_BYTES / 2;                                   // column j = r: rows 0 and 1
+constexpr size_t L2_OFF_ACC = L2_KEY_BYTES;
+constexpr size_t L2_OFF_BUF1 = L2_OFF_ACC + (size_t)LAT_N * sizeof(uint64_t);
+constexpr size_t L2_OFF_BUF2 = L2_OFF_BUF1 + (size_t)Fft8::BUF1 * sizeof(cplx);
+constexpr size_t L2_OFF_DIN = L2_OFF_BUF2 + (size_t)Fft8::BUF2 * sizeof(cplx);       // [2][M] landing buffers for the peer's D
+constexpr size_t L2_OFF_TAB = L2_OFF_DIN + 2 * (size_t)LAT_M * sizeof(cplx);
+constexpr size_t L2_OFF_MBAR = L2_OFF_TAB + sizeof(Fft8::Tables);
+constexpr size_t L2_OFF_AHAT = L2_OFF_MBAR + 16;
+size_t lat2_smem_bytes(int n) { return L2_OFF_AHAT + ((((size_t)(n + 1) * sizeof(uint16_t)) + 15) & ~(size_t)15); }
+
+template <int BL, bool PLAIN>
+__global__ void __launch_bounds__(LAT_TEAM, 1)
+blind_rotate_lat2_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride, const uint64_t *__restrict__ luts,
+                         const uint32_t *__restrict__ lut_idx, const cplx *__restrict__ bsk, uint64_t *__restrict__ out,
+                         size_t out_stride, int n, int mode, const Fft8::Tables *__restrict__ tables_g, int n_iter,
+                         size_t key_ct_stride) {
+#if defined(__CUDA_ARCH__)
+    typedef uint64_t T;
+    constexpr int N = LAT_N, M = LAT_M, K1 = LAT_K1, TM = LAT_TEAM;
+    extern __shared__ __align__(128) unsigned char smem[];
+    cplx *key = reinterpret_cast<cplx *>(smem);                               // [row q][M]: G[q][j = r], refilled every iteration by TMA
+    T *acc_r = reinterpret_cast<T *>(smem + L2_OFF_ACC);                      // this CTA's accumulator row
+    cplx *buf1 = reinterpret_cast<cplx *>(smem + L2_OFF_BUF1);
+    cplx *buf2 = reinterpret_cast<cplx *>(smem + L2_OFF_BUF2);
+    cplx *din = reinterpret_cast<cplx *>(smem + L2_OFF_DIN);
+    Fft8::Tables *tab = reinterpret_cast<Fft8::Tables *>(smem + L2_OFF_TAB);
+    uint16_t *ahat = reinterpret_cast<uint16_t *>(smem + L2_OFF_AHAT);
+    const uint32_t bar = smem_addr_u32(smem + L2_OFF_MBAR);
+    const uint32_t key_s = smem_addr_u32(key);
+
+    const int t = threadIdx.x;
+    uint32_t rank;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+    const int r = (int)rank, ct = blockIdx.x >> 1;
+    bsk += (size_t)ct * key_ct_stride;
+    // the peer's landing buffer, as a shared::cluster address
+    uint32_t din_peer;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(din_peer) : "r"(smem_addr_u32(din)), "r"(rank ^ 1u));
+
+    if (t == 0) {
+        mbarrier_init(bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    {
+        const int4 *src = reinterpret_cast<const int4 *>(tables_g);
+        int4 *dst = reinterpret_cast<int4 *>(tab);
+        for (int e = t; e < (int)(sizeof(Fft8::Tables) / 16); e += TM) dst[e] = src[e];
+    }
+    const T *lwe = lwe_in + (size_t)ct * lwe_stride;
+    for (int i = t; i <= n; i += TM) ahat[i] = (uint16_t)(modswitch<T>(lwe[i], 11) & (2 * N - 1));
+    __syncthreads();
+    auto fetch_key = [&](int i) {   // thread 0: column j = r of this iteration's GGSW (rows 0 and 1, 16 KB each)
+        mbarrier_expect_tx(bar, (uint32_t)L2_KEY_BYTES);
+        const unsigned char *src = reinterpret_cast<const unsigned char *>(bsk) + (size_t)i * LAT_KEY_BYTES;
+#pragma unroll
+        for (int q = 0; q < 2; q++) bulk_load(key_s + q * 16384u, src + (size_t)(q * K1 + r) * 16384u, 16384u, bar);
+    };
+    if (t == 0 && n_iter > 0) fetch_key(0);
+    {
+        const T *lut = luts + (size_t)(lut_idx ? lut_idx[ct] : 0) * K1 * N + (size_t)r * N;
+        const int a0 = (2 * N - (int)ahat[n]) & (2 * N - 1);
+        for (int c = t; c < N; c += TM) acc_r[c] = rot_read<T, N>(lut, c, a0);
+    }
+    __syncthreads();
+    // both CTAs are up (their shared memory exists) before anyone stores into the peer
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+
+    const unsigned char *accb = reinterpret_cast<const unsigned char *>(acc_r);
+    const cplx *key_own = key + (size_t)r * M + t;             // row r, column r
+    const cplx *key_oth = key + (size_t)(1 - r) * M + t;       // row 1 - r, column r
+    const cplx twist_t = tab->twist[t];
+    const Fft8::TwB twb_fwd = tab->tb[0][t], twb_inv = tab->tb[1][t];
+    T own_re[8], own_im[8];
+    static_for<0, 8>([&](auto q) {
+        own_re[decltype(q)::value] = acc_r[t + TM * decltype(q)::value];
+        own_im[decltype(q)::value] = acc_r[t + TM * decltype(q)::value + M];
+    });
+
+    for (int i = 0; i < n_iter; i++) {
+        const int a = PLAIN ? 0 : ahat[i];
+        cplx x[8];
+#pragma unroll 1
+        for (int dir = 0; dir < 2; dir++) {
+            if (dir == 0) {
+                if constexpr (PLAIN) {
+                    typedef BRCore<T, 32, 1, 1, BL> DC;
+                    static_for<0, 8>([&](auto p) {
+                        constexpr int v = brev(decltype(p)::value, 3);
+                        x[decltype(p)::value].re = int_to_double(DC::single_level_digit(own_re[v]));
+                        x[decltype(p)::value].im = int_to_double(DC::single_level_digit(own_im[v]));
+                    });
+                } else {
+                    const uint32_t s8 = 8u * (uint32_t)(t - a);
+                    static_for<0, 8>([&](auto p) {
+                        constexpr int v = brev(decltype(p)::value, 3);
+                        x[decltype(p)::value].re = rot_digit_f64<BL>(accb, s8 + 8u * (uint32_t)TM * v, own_re[v]);
+                        x[decltype(p)::value].im = rot_digit_f64<BL>(accb, s8 + 8u * (uint32_t)TM * v + 8u * M, own_im[v]);
+                    });
+                }
+                Fft8::pre_twist(x);
+            } else {
+                // x holds D_r[t + 128 f2]: into the peer's landing buffer of this iteration's parity, then publish
+                const uint32_t dst = din_peer + (uint32_t)(((i & 1) * M + t) * sizeof(cplx));
+                static_for<0, 8>([&](auto f2) {
+                    asm volatile("st.shared::cluster.v2.f64 [%0], {%1, %2};" ::"r"(dst + (uint32_t)(TM * decltype(f2)::value * sizeof(cplx))),
+                                 "d"(x[decltype(f2)::value].re), "d"(x[decltype(f2)::value].im)
+                                 : "memory");
+                });
+                asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+                mbarrier_wait(bar, (uint32_t)(i & 1));
+                cplx y[8];
+                static_for<0, 8>([&](auto p) {       // own row first: needs nothing from the peer
+                    constexpr int v = brev(decltype(p)::value, 3);
+                    y[decltype(p)::value] = cmul(key_own[TM * v], x[v]);
+                });
+                asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+                const cplx *d_oth = din + (i & 1) * M + t;
+                static_for<0, 8>([&](auto p) {
+                    constexpr int v = brev(decltype(p)::value, 3);
+                    cplx f = y[decltype(p)::value];
+                    BRCore<T, 32, 1, 1, BL>::mac_one(f, key_oth[TM * v], d_oth[TM * v]);
+                    x[decltype(p)::value] = cplx{f.re, -f.im};
+                });
+            }
+            Fft8::pass_a(t, x, tab->ta, twist_t, dir == 0, buf1);
+            __syncthreads();
+            // every thread of the CTA is past its key reads: refill the key column for the next iteration
+            if (dir == 1 && t == 0 && i + 1 < n_iter) fetch_key(i + 1);
+            {
+                cplx z[8], send[4], recv[4];
+                Fft8::pass_b_first(t, buf1, z, send);
+                static_for<0, 4>([&](auto e) { recv[decltype(e)::value] = shfl_xor_cplx(send[decltype(e)::value], 8); });
+                Fft8::pass_b_second(t, z, recv, dir ? twb_inv : twb_fwd, buf2);
+            }
+            __syncthreads();
+            Fft8::pass_c(t, x, buf2);
+            if (dir == 1) {
+                Fft8::post_twist(x);
+                if constexpr (PLAIN) {
+                    static_for<0, 8>([&](auto q) {
+                        own_re[decltype(q)::value] = torus_from_double<T>(x[decltype(q)::value].re);
+                        own_im[decltype(q)::value] = torus_from_double<T>(-x[decltype(q)::value].im);
+                    });
+                } else {
+                    static_for<0, 8>([&](auto q) {
+                        const int c = t + TM * decltype(q)::value;
+                        own_re[decltype(q)::value] += torus_from_double<T>(x[decltype(q)::value].re);
+                        own_im[decltype(q)::value] += torus_from_double<T>(-x[decltype(q)::value].im);
+                        acc_r[c] = own_re[decltype(q)::value];
+                        acc_r[c + M] = own_im[decltype(q)::value];
+                    });
+                    __syncthreads();
+                }
+            }
+        }
+    }
+    if constexpr (PLAIN) {
+        static_for<0, 8>([&](auto q) {
+            acc_r[t + TM * decltype(q)::value] = own_re[decltype(q)::value];
+            acc_r[t + TM * decltype(q)::value + M] = own_im[decltype(q)::value];
+        });
+        __syncthreads();
+    }
+    // no CTA of the cluster exits while the other may still store into it
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+
+    T *o = out + (size_t)ct * out_stride;
+    if (mode == BR_MODE_GLWE) {
+        for (int c = t; c < N; c += TM) o[(size_t)r * N + c] = acc_r[c];
+    } else if (r == 0) {   // sample extract, coefficient 0 (algorithms/glwe_sample_extraction.rs:91-147), k = 1
+        for (int c = t; c < N; c += TM) o[c] = (c == 0) ? acc_r[0] : (T)(0 - acc_r[N - c]);
+    } else if (t == 0) {
+        o[N] = acc_r[0];
+    }
+#endif
+}
+
 // per-device copy of the twiddle tables, uploaded on first use
 const Fft8::Tables *lat_tables(cudaStream_t st, cudaError_t *err) {
     static std::mutex mu;
@@ -265,6 +452,27 @@ const Fft8::Tables *lat_tables(cudaStream_t st, cudaError_t *err) {
 
 }  // namespace
 
+template <int BL, bool PLAIN>
+static int launch_lat2(const BRLaunch &a, const Fft8::Tables *tab, int n_iter, size_t key_ct_stride, cudaStream_t st) {
+    auto kern = blind_rotate_lat2_kernel<BL, PLAIN>;
+    const size_t smem = lat2_smem_bytes(a.n);
+    if (cudaError_t e = ensure_dynamic_smem((const void *)kern, smem)) return (int)e;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * (unsigned)a.batch);
+    cfg.blockDim = dim3(LAT_TEAM);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return (int)cudaLaunchKernelEx(&cfg, kern, (const uint64_t *)a.lwe_in, a.lwe_stride, (const uint64_t *)a.luts, a.lut_idx, (const cplx *)a.bsk,
+                                   (uint64_t *)a.out, a.out_stride, a.n, a.mode, tab, n_iter, key_ct_stride);
+}
+
 int br_lat_supported(const Params &p) {
     return p.bits == 64 && p.N == LAT_N && p.k == 1 && p.pbs_level == 1 && p.pbs_base_log == LAT_BL;
 }
@@ -285,6 +493,10 @@ int br_lat_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
     cudaError_t e = cudaSuccess;
     const Fft8::Tables *tab = lat_tables(st, &e);
     if (!tab) return (int)e;
+    if (a.batch <= a.lat_cluster_max) {
+        if (launch_lat2<LAT_BL, false>(a, tab, a.n, (size_t)0, st) == 0) return 0;
+        (void)cudaGetLastError();      // a cluster that cannot be scheduled here (e.g. a partitioned device): one CTA per ciphertext instead
+    }
     const size_t smem = lat_smem_bytes(a.n);
     auto kern = blind_rotate_lat_kernel<LAT_BL, false>;
     if ((e = ensure_dynamic_smem((const void *)kern, smem)) != cudaSuccess) return (int)e;
@@ -302,6 +514,10 @@ int br_lat_plain_launch(const Params &p, const BRLaunch &a, int n_iter, size_t k
     if (!tab) return (int)e;
     const size_t smem = lat_smem_bytes(a.n);
 #define X(BL)                                                                                                                       \
+    if (p.pbs_base_log == BL && a.batch <= a.lat_cluster_max) {                                                                     \
+        if (launch_lat2<BL, true>(a, tab, n_iter, key_ct_stride, st) == 0) return 0;                                                \
+        (void)cudaGetLastError();                                                                                                   \
+    }                                                                                                                               \
     if (p.pbs_base_log == BL) {                                                                                                     \
         auto kern = blind_rotate_lat_kernel<BL, true>;                                                                              \
         if ((e = ensure_dynamic_smem((const void *)kern, smem)) != cudaSuccess) return (int)e;                                      \

@@ -46,6 +46,7 @@ struct BRLaunch {
     // kernel choice (b200tfhe_context_set_option "br_kernel" / "lat_max"): BR_AUTO picks by parameter set and batch size
     int force = 0;
     int lat_max = 2 * 148;
+    int lat_cluster_max = 74;   // latency kernel: at most this many ciphertexts run on a two-CTA cluster each (two SMs per ciphertext)
     mutable int launches = 1;   // set by br_launch: kernels it actually launched (a tail wave may go to a second kernel)
     // multi-bit keys, batches of at most mb_lat_max ciphertexts: scratch for the per-ciphertext summed keys of the two-kernel
     // latency path (br_mb_lat_scratch_bytes); nullptr = always the fused kernel
