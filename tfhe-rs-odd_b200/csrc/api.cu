@@ -504,7 +504,7 @@ static int ks_dev_locked(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const v
         ctx->launches += 2;
     } else {
         rc = ks_launch(a, ctx->stream);
-        ctx->launches++;
+        ctx->launches += a.launches;
     }
     if (rc) return fail(ctx, "keyswitch launch failed: " + std::to_string(rc));
     return 0;

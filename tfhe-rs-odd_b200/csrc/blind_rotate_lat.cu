@@ -140,7 +140,7 @@ blind_rotate_lat_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride, 
     for (int i = 0; i < n_iter; i++) {
         const int a = PLAIN ? 0 : ahat[i];
         cplx x[8];
-#pragma unroll 1
+#pragma unroll
         for (int dir = 0; dir < 2; dir++) {
             if (dir == 0) {
                 // rotate-subtract + one-level signed decomposition, as doubles; then the register part of the twist
@@ -253,9 +253,10 @@ constexpr size_t L2_OFF_ACC = L2_KEY_BYTES;
 constexpr size_t L2_OFF_BUF1 = L2_OFF_ACC + (size_t)LAT_N * sizeof(uint64_t);
 constexpr size_t L2_OFF_BUF2 = L2_OFF_BUF1 + (size_t)Fft8::BUF1 * sizeof(cplx);
 constexpr size_t L2_OFF_DIN = L2_OFF_BUF2 + (size_t)Fft8::BUF2 * sizeof(cplx);       // [2][M] landing buffers for the peer's D
-constexpr size_t L2_OFF_TAB = L2_OFF_DIN + 2 * (size_t)LAT_M * sizeof(cplx);
+constexpr size_t L2_OFF_DOUT = L2_OFF_DIN + 2 * (size_t)LAT_M * sizeof(cplx);      // [2][M] staging of this CTA's D for the bulk copy to the peer
+constexpr size_t L2_OFF_TAB = L2_OFF_DOUT + 2 * (size_t)LAT_M * sizeof(cplx);
 constexpr size_t L2_OFF_MBAR = L2_OFF_TAB + sizeof(Fft8::Tables);
-constexpr size_t L2_OFF_AHAT = L2_OFF_MBAR + 16;
+constexpr size_t L2_OFF_AHAT = L2_OFF_MBAR + 16;   // two mbarriers: key, landing buffer
 size_t lat2_smem_bytes(int n) { return L2_OFF_AHAT + ((((size_t)(n + 1) * sizeof(uint16_t)) + 15) & ~(size_t)15); }
 
 template <int BL, bool PLAIN>
@@ -273,6 +274,7 @@ blind_rotate_lat2_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride,
     cplx *buf1 = reinterpret_cast<cplx *>(smem + L2_OFF_BUF1);
     cplx *buf2 = reinterpret_cast<cplx *>(smem + L2_OFF_BUF2);
     cplx *din = reinterpret_cast<cplx *>(smem + L2_OFF_DIN);
+    cplx *dout = reinterpret_cast<cplx *>(smem + L2_OFF_DOUT);
     Fft8::Tables *tab = reinterpret_cast<Fft8::Tables *>(smem + L2_OFF_TAB);
     uint16_t *ahat = reinterpret_cast<uint16_t *>(smem + L2_OFF_AHAT);
     const uint32_t bar = smem_addr_u32(smem + L2_OFF_MBAR);
@@ -283,12 +285,15 @@ blind_rotate_lat2_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride,
     asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
     const int r = (int)rank, ct = blockIdx.x >> 1;
     bsk += (size_t)ct * key_ct_stride;
-    // the peer's landing buffer, as a shared::cluster address
-    uint32_t din_peer;
+    // the peer's landing buffer and its "D has landed" mbarrier, as shared::cluster addresses
+    const uint32_t bar_din = bar + 8;
+    uint32_t din_peer, bar_din_peer;
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(din_peer) : "r"(smem_addr_u32(din)), "r"(rank ^ 1u));
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(bar_din_peer) : "r"(bar_din), "r"(rank ^ 1u));
 
     if (t == 0) {
         mbarrier_init(bar, 1);
+        mbarrier_init(bar_din, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     {
@@ -330,7 +335,7 @@ blind_rotate_lat2_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride,
     for (int i = 0; i < n_iter; i++) {
         const int a = PLAIN ? 0 : ahat[i];
         cplx x[8];
-#pragma unroll 1
+#pragma unroll
         for (int dir = 0; dir < 2; dir++) {
             if (dir == 0) {
                 if constexpr (PLAIN) {
@@ -350,21 +355,29 @@ blind_rotate_lat2_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride,
                 }
                 Fft8::pre_twist(x);
             } else {
-                // x holds D_r[t + 128 f2]: into the peer's landing buffer of this iteration's parity, then publish
-                const uint32_t dst = din_peer + (uint32_t)(((i & 1) * M + t) * sizeof(cplx));
-                static_for<0, 8>([&](auto f2) {
-                    asm volatile("st.shared::cluster.v2.f64 [%0], {%1, %2};" ::"r"(dst + (uint32_t)(TM * decltype(f2)::value * sizeof(cplx))),
-                                 "d"(x[decltype(f2)::value].re), "d"(x[decltype(f2)::value].im)
+                // x holds D_r[t + 128 f2].  It goes to the peer as ONE bulk copy through distributed shared memory (the copy engine moves
+                // 16 KB far faster than 1024 sixteen-byte remote stores drain): stage it locally, make the generic-proxy writes visible
+                // to the async proxy, and let thread 0 send it; the copy signals the peer's mbarrier on arrival.  No cluster barrier in the
+                // loop: "the peer's D of iteration i+1 has landed" implies the peer has consumed what this CTA sent in iteration i, so the
+                // two-slot staging and landing buffers are safe to reuse two iterations later.
+                cplx *stage = dout + (i & 1) * M + t;
+                static_for<0, 8>([&](auto f2) { stage[TM * decltype(f2)::value] = x[decltype(f2)::value]; });
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncthreads();
+                if (t == 0) {
+                    mbarrier_expect_tx(bar_din, (uint32_t)(M * sizeof(cplx)));        // arm this CTA's own landing barrier
+                    asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                                     din_peer + (uint32_t)((i & 1) * M * sizeof(cplx))),
+                                 "r"(smem_addr_u32(dout + (i & 1) * M)), "r"((uint32_t)(M * sizeof(cplx))), "r"(bar_din_peer)
                                  : "memory");
-                });
-                asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+                }
                 mbarrier_wait(bar, (uint32_t)(i & 1));
                 cplx y[8];
                 static_for<0, 8>([&](auto p) {       // own row first: needs nothing from the peer
                     constexpr int v = brev(decltype(p)::value, 3);
                     y[decltype(p)::value] = cmul(key_own[TM * v], x[v]);
                 });
-                asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+                mbarrier_wait(bar_din, (uint32_t)(i & 1));
                 const cplx *d_oth = din + (i & 1) * M + t;
                 static_for<0, 8>([&](auto p) {
                     constexpr int v = brev(decltype(p)::value, 3);

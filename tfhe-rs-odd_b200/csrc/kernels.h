@@ -114,6 +114,7 @@ struct KSLaunch {
     // 2^(sub_bits * (sub-1-s)), so sum_s d_s * (K << ...) == digit * K mod 2^W and the int8 GEMM stays bit-exact
     int sub = 1, sub_bits = 0;
     bool no_body = false;                  // the input body is an ordinary decomposed row (n_in counts it); nothing is added
+    mutable int launches = 1;              // set by ks_launch: kernels it launched (2 on the split-row path of tiny batches)
 };
 int ks_launch(const KSLaunch &a, cudaStream_t st);
 int ks_colsum_launch(const void *ksk, void *colsum, int n_in, int n_out, int level, int base_log, int bits, cudaStream_t st);

@@ -110,9 +110,74 @@ int ks_colsum_launch(const void *ksk, void *colsum, int n_in, int n_out, int lev
     return (int)cudaGetLastError();
 }
 
+// ---- a handful of ciphertexts (the single-bootstrap latency path): split the key ROWS over the whole GPU -------------------------
+// ks_kernel gives a batch of <= 32 ciphertexts to six CTAs (one per 128 output columns), each walking all n_in*l key rows: 0.12 ms for ONE
+// ciphertext at PARAM_MESSAGE_2_CARRY_2, 6 % of a single KS+PBS.  Here a CTA owns KS_SK_IC input coefficients x 128 columns for all (<= 8)
+// ciphertexts and adds its partial sums into the output with atomic adds: wrapping addition is associative and commutative, so the
+// result is bit-identical to the serial loop whatever the order.  The output is pre-set to body + B/2 * colsum by ks_splitk_init_kernel.
+constexpr int KS_SK_MAX = 8;       // ciphertexts
+constexpr int KS_SK_IC = 16;       // input coefficients per CTA
+
+template <typename T>
+__global__ void ks_splitk_init_kernel(const T *__restrict__ in, size_t in_stride, T *__restrict__ out, size_t out_stride,
+                                      const T *__restrict__ colsum, int n_in, int width, int base_log, int batch, int body_col) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
+    if (j >= width || b >= batch) return;
+    T v = (T)(1u << (base_log - 1)) * colsum[j];
+    if (j == body_col) v += in[(size_t)b * in_stride + n_in];
+    out[(size_t)b * out_stride + j] = v;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(128)
+ks_splitk_kernel(const T *__restrict__ in, size_t in_stride, T *__restrict__ out, size_t out_stride, const T *__restrict__ ksk,
+                 int n_in, int width, int level, int base_log, int batch) {
+    __shared__ unsigned char dig[KS_SK_IC * 8 * KS_SK_MAX];     // [(ii*level + t)][b], level <= 8
+    const int tid = threadIdx.x, i0 = blockIdx.x * KS_SK_IC, j = blockIdx.y * 128 + tid;
+    const uint32_t half_b = 1u << (base_log - 1);
+    const int ni = min(KS_SK_IC, n_in - i0);
+    for (int e = tid; e < ni * batch; e += 128) {
+        const int ii = e / batch, b = e % batch;
+        T state = decomp_init_state<T>(in[(size_t)b * in_stride + i0 + ii], base_log, level);
+        for (int t = 0; t < level; t++) dig[(ii * level + t) * KS_SK_MAX + b] = (unsigned char)((int)decomp_next_digit<T>(state, base_log) + (int)half_b);
+    }
+    __syncthreads();
+    if (j >= width) return;
+    T acc[KS_SK_MAX];
+#pragma unroll
+    for (int b = 0; b < KS_SK_MAX; b++) acc[b] = 0;
+    const T *krow = ksk + (size_t)i0 * level * width + j;
+    const int rows = ni * level;
+#pragma unroll 4
+    for (int rr = 0; rr < rows; rr++, krow += width) {
+        const T kv = *krow;
+        const uint2 pk = *reinterpret_cast<const uint2 *>(dig + rr * KS_SK_MAX);
+#pragma unroll
+        for (int b = 0; b < KS_SK_MAX; b++) acc[b] += (T)(((b < 4 ? pk.x : pk.y) >> (8 * (b & 3))) & 0xFFu) * kv;
+    }
+#pragma unroll
+    for (int b = 0; b < KS_SK_MAX; b++) {
+        if (b >= batch) break;
+        T *o = out + (size_t)b * out_stride + j;
+        if constexpr (sizeof(T) == 8) atomicAdd(reinterpret_cast<unsigned long long *>(o), (unsigned long long)(0 - acc[b]));
+        else atomicAdd(reinterpret_cast<unsigned int *>(o), (unsigned int)(0 - acc[b]));
+    }
+}
+
+template <typename T> static int ks_splitk_launch(const KSLaunch &a, cudaStream_t st) {
+    const int width = a.n_out + 1, body = a.body_col < 0 ? a.n_out : a.body_col;
+    ks_splitk_init_kernel<T><<<dim3((width + 127) / 128, a.batch), 128, 0, st>>>((const T *)a.in, a.in_stride, (T *)a.out, a.out_stride, (const T *)a.colsum,
+                                                                               a.n_in, width, a.base_log, a.batch, body);
+    ks_splitk_kernel<T><<<dim3((a.n_in + KS_SK_IC - 1) / KS_SK_IC, (width + 127) / 128), 128, 0, st>>>((const T *)a.in, a.in_stride, (T *)a.out, a.out_stride,
+                                                                                                   (const T *)a.ksk, a.n_in, width, a.level, a.base_log, a.batch);
+    return (int)cudaGetLastError();
+}
+
 int ks_launch(const KSLaunch &a, cudaStream_t st) {
     if (a.batch <= 0) return 0;
     if (a.base_log < 1 || a.base_log > 7 || a.level < 1 || a.level * a.base_log >= a.bits) return -1;
+    if (a.batch <= KS_SK_MAX && a.level <= 8 && a.sub <= 1 && !a.no_body) a.launches = 2;
+    if (a.batch <= KS_SK_MAX && a.level <= 8 && a.sub <= 1 && !a.no_body) return a.bits == 64 ? ks_splitk_launch<uint64_t>(a, st) : ks_splitk_launch<uint32_t>(a, st);
     dim3 grid((a.batch + KS_BT - 1) / KS_BT, (a.n_out + 1 + KS_JT - 1) / KS_JT);
     size_t smem = (size_t)KS_IC * a.level * KS_BT;
     if (a.bits == 64)
