@@ -86,7 +86,7 @@ blind_rotate_big_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const T
             cplx x[P];
             uint32_t packed[P];
             if constexpr (L == 2) C::digits_both(tid, acc + (size_t)r * N, a, x, packed);
-#pragma unroll 1
+#pragma unroll
             for (int t = 0; t < L; t++) {
                 if constexpr (L == 2) {
                     if (t == 1) C::digits_unpack(packed, x);
@@ -108,8 +108,8 @@ blind_rotate_big_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const T
         }
         tmem_wait_st();
         // ---- product + inverse phase, one output polynomial at a time ----------------------------------------------------------------
-        static_for<0, K1>([&](auto j_) {
-            constexpr int j = decltype(j_)::value;
+#pragma unroll 1
+        for (int j = 0; j < K1; j++) {      // rolled: one copy of the product + inverse code (the unrolled forward pair already fills the instruction cache)
             cplx f[P];
             static_for<0, P>([&](auto p) { f[decltype(p)::value] = cplx{0.0, 0.0}; });
             // half-steps h = 2 s + e: positions p = 8 e .. 8 e + 7 of transform s; the loads of half-step h + 1 are in flight while h is used
@@ -155,7 +155,7 @@ blind_rotate_big_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const T
             __syncthreads();
             C::invC(tid, x, S1, ta, tq);
             C::accumulate(tid, x, acc + (size_t)j * N);
-        });
+        }
         __syncthreads();                        // acc complete before the next iteration's rotated reads
     }
 
