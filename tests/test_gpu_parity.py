@@ -450,3 +450,47 @@ def test_pair_kernel_dispatch_and_ragged_last_cta(ctx):
     d = np.abs((o.phase(pair, "big") - o.phase(gen, "big")).astype(np.int64).astype(np.float64)) / 2.0 ** 64
     assert d.max() < phase_bound(o)
     assert np.array_equal(o.decode(o.phase(gen, "big")), o.decode(o.phase(pair, "big")))
+
+
+@pytest.mark.gpu
+def test_cluster_latency_kernel_is_bit_identical_to_the_one_sm_kernel(ctx):
+    """blind_rotate_lat2_kernel (two-CTA cluster per ciphertext, D exchanged by bulk copies through distributed shared memory with
+    double-buffered landing / staging slots and no cluster barrier in the loop) runs the same arithmetic in the same order as the one-SM
+    kernel: outputs must be bit-identical for every batch size of its range, run after run (a race in the slot reuse would show here)."""
+    import tfhe_rs_odd_b200 as t
+    o = get_oracle("TOY_2_2")
+    p, bsk, ksk = _keys(ctx, o)
+    msgs = np.arange(74) % o.pmod
+    cts = o.encrypt(o.encode(msgs), "small", seed=0x7A13)
+    lut = o.lut(lambda x: (x + 2) % o.pmod)
+    try:
+        ctx.set_option("br_kernel", 3)
+        ctx.set_option("lat_cluster_max", 0)
+        ref = t.programmable_bootstrap_lwe_ciphertext(cts, lut, bsk)
+        ctx.set_option("lat_cluster_max", 74)
+        for B in (1, 2, 3, 37, 74, 74, 74):
+            got = t.programmable_bootstrap_lwe_ciphertext(cts[:B], lut, bsk)
+            assert np.array_equal(got, ref[:B]), B
+        glwe = t.programmable_bootstrap_lwe_ciphertext_without_sample_extract(cts[:5], lut, bsk)
+        assert np.array_equal(t.extract_lwe_sample_from_glwe_ciphertext(ctx, glwe, o.k, o.N, 64), ref[:5])
+    finally:
+        ctx.set_option("br_kernel", 0)
+        ctx.set_option("lat_cluster_max", 74)
+    assert np.array_equal(o.decode(o.phase(ref, "big")) % o.pmod, (msgs + 2) % o.pmod)
+    # the same at full size (742 iterations: every landing / staging slot is reused 371 times)
+    o = get_oracle("MESSAGE_2_CARRY_2")
+    p, bsk, ksk = _keys(ctx, o)
+    msgs = np.arange(74) % o.pmod
+    cts = o.encrypt(o.encode(msgs), "small", seed=0x7A14)
+    lut = o.lut(lambda x: (3 * x) % o.pmod)
+    try:
+        ctx.set_option("br_kernel", 3)
+        ctx.set_option("lat_cluster_max", 0)
+        ref = t.programmable_bootstrap_lwe_ciphertext(cts, lut, bsk)
+        ctx.set_option("lat_cluster_max", 74)
+        for B in (1, 74, 74):
+            assert np.array_equal(t.programmable_bootstrap_lwe_ciphertext(cts[:B], lut, bsk), ref[:B]), B
+    finally:
+        ctx.set_option("br_kernel", 0)
+        ctx.set_option("lat_cluster_max", 74)
+    assert np.array_equal(o.decode(o.phase(ref, "big")) % o.pmod, (3 * msgs) % o.pmod)
