@@ -344,7 +344,7 @@ blind_rotate_x16b_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const 
                 s0[decltype(p)::value] = (S)decomp_init_state<T>(rot_read<T, N>(acc_r, c, a) - acc_r[c], BL, L);
                 s1[decltype(p)::value] = (S)decomp_init_state<T>(rot_read<T, N>(acc_r, c + M, a) - acc_r[c + M], BL, L);
             });
-#pragma unroll 1
+#pragma unroll
             for (int t = 0; t < L; t++) {             // t = 0 <-> level L, the first digit the recurrence emits
                 cplx x[R];
                 static_for<0, R>([&](auto p) {
