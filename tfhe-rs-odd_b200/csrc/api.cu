@@ -60,7 +60,7 @@ struct b200tfhe_context {
     int opt_lat_cluster_max = 74;    // largest batch that gives every ciphertext a two-CTA cluster (two SMs) on the latency kernel
     int opt_mb_lat_max = 148;        // multi-bit keys: largest batch on the two-kernel latency path (16-24 MB of scratch per ciphertext)
     int opt_ks_tensor_core = 1;      // 0: CUDA-core keyswitch even where the tensor-core planes exist
-    int opt_ks_tc_min = 1;           // smallest batch on the tensor-core keyswitch
+    int opt_ks_tc_min = 9;           // smallest batch on the tensor-core keyswitch (up to 8: the split-row kernel, which leaves L2 to the bootstrap key)
     uint32_t opt_chunk_min = 6 * 592;   // minimum chunk of the H2D / compute / D2H pipeline of host-pointer calls (0: off)
 };
 struct b200tfhe_bsk {

@@ -249,14 +249,14 @@ blind_rotate_lat_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride, 
 // FP64 work per SM; the price is the 16 KB that cross at ~20 B/clk and the barrier (~400 cycles).  Used for batches of at most
 // `lat_cluster_max` ciphertexts (two SMs each).
 constexpr size_t L2_KEY_BYTES = LAT_KEY_BYTES / 2;                                   // column j = r: rows 0 and 1
-constexpr size_t L2_OFF_ACC = L2_KEY_BYTES;
+constexpr size_t L2_OFF_ACC = 2 * L2_KEY_BYTES;                                       // two key slots: the fetch runs two iterations ahead
 constexpr size_t L2_OFF_BUF1 = L2_OFF_ACC + (size_t)LAT_N * sizeof(uint64_t);
 constexpr size_t L2_OFF_BUF2 = L2_OFF_BUF1 + (size_t)Fft8::BUF1 * sizeof(cplx);
 constexpr size_t L2_OFF_DIN = L2_OFF_BUF2 + (size_t)Fft8::BUF2 * sizeof(cplx);       // [2][M] landing buffers for the peer's D
 constexpr size_t L2_OFF_DOUT = L2_OFF_DIN + 2 * (size_t)LAT_M * sizeof(cplx);      // [2][M] staging of this CTA's D for the bulk copy to the peer
 constexpr size_t L2_OFF_TAB = L2_OFF_DOUT + 2 * (size_t)LAT_M * sizeof(cplx);
 constexpr size_t L2_OFF_MBAR = L2_OFF_TAB + sizeof(Fft8::Tables);
-constexpr size_t L2_OFF_AHAT = L2_OFF_MBAR + 16;   // two mbarriers: key, landing buffer
+constexpr size_t L2_OFF_AHAT = L2_OFF_MBAR + 32;   // three mbarriers: key slot 0, key slot 1, landing buffer
 size_t lat2_smem_bytes(int n) { return L2_OFF_AHAT + ((((size_t)(n + 1) * sizeof(uint16_t)) + 15) & ~(size_t)15); }
 
 template <int BL, bool PLAIN>
@@ -286,13 +286,14 @@ blind_rotate_lat2_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride,
     const int r = (int)rank, ct = blockIdx.x >> 1;
     bsk += (size_t)ct * key_ct_stride;
     // the peer's landing buffer and its "D has landed" mbarrier, as shared::cluster addresses
-    const uint32_t bar_din = bar + 8;
+    const uint32_t bar_din = bar + 16;
     uint32_t din_peer, bar_din_peer;
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(din_peer) : "r"(smem_addr_u32(din)), "r"(rank ^ 1u));
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(bar_din_peer) : "r"(bar_din), "r"(rank ^ 1u));
 
     if (t == 0) {
         mbarrier_init(bar, 1);
+        mbarrier_init(bar + 8, 1);
         mbarrier_init(bar_din, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -304,13 +305,17 @@ blind_rotate_lat2_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride,
     const T *lwe = lwe_in + (size_t)ct * lwe_stride;
     for (int i = t; i <= n; i += TM) ahat[i] = (uint16_t)(modswitch<T>(lwe[i], 11) & (2 * N - 1));
     __syncthreads();
-    auto fetch_key = [&](int i) {   // thread 0: column j = r of this iteration's GGSW (rows 0 and 1, 16 KB each)
-        mbarrier_expect_tx(bar, (uint32_t)L2_KEY_BYTES);
+    // thread 0: column j = r of iteration i's GGSW (rows 0 and 1, 16 KB each) into key slot i & 1.  The fetch runs TWO iterations ahead
+    // of its use, so that it is covered even when the key comes from HBM (a keyswitch in front of the bootstrap streams 61 MB through L2)
+    auto fetch_key = [&](int i) {
+        const uint32_t kb = bar + 8u * (uint32_t)(i & 1), ks = key_s + (uint32_t)((i & 1) * L2_KEY_BYTES);
+        mbarrier_expect_tx(kb, (uint32_t)L2_KEY_BYTES);
         const unsigned char *src = reinterpret_cast<const unsigned char *>(bsk) + (size_t)i * LAT_KEY_BYTES;
 #pragma unroll
-        for (int q = 0; q < 2; q++) bulk_load(key_s + q * 16384u, src + (size_t)(q * K1 + r) * 16384u, 16384u, bar);
+        for (int q = 0; q < 2; q++) bulk_load(ks + q * 16384u, src + (size_t)(q * K1 + r) * 16384u, 16384u, kb);
     };
     if (t == 0 && n_iter > 0) fetch_key(0);
+    if (t == 0 && n_iter > 1) fetch_key(1);
     {
         const T *lut = luts + (size_t)(lut_idx ? lut_idx[ct] : 0) * K1 * N + (size_t)r * N;
         const int a0 = (2 * N - (int)ahat[n]) & (2 * N - 1);
@@ -322,8 +327,8 @@ blind_rotate_lat2_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride,
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 
     const unsigned char *accb = reinterpret_cast<const unsigned char *>(acc_r);
-    const cplx *key_own = key + (size_t)r * M + t;             // row r, column r
-    const cplx *key_oth = key + (size_t)(1 - r) * M + t;       // row 1 - r, column r
+    const cplx *key_own0 = key + (size_t)r * M + t;            // row r, column r       (slot 0; slot 1 is 2 M further)
+    const cplx *key_oth0 = key + (size_t)(1 - r) * M + t;      // row 1 - r, column r
     const cplx twist_t = tab->twist[t];
     const Fft8::TwB twb_fwd = tab->tb[0][t], twb_inv = tab->tb[1][t];
     T own_re[8], own_im[8];
@@ -371,7 +376,8 @@ blind_rotate_lat2_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride,
                                  "r"(smem_addr_u32(dout + (i & 1) * M)), "r"((uint32_t)(M * sizeof(cplx))), "r"(bar_din_peer)
                                  : "memory");
                 }
-                mbarrier_wait(bar, (uint32_t)(i & 1));
+                const cplx *key_own = key_own0 + (i & 1) * 2 * M, *key_oth = key_oth0 + (i & 1) * 2 * M;
+                mbarrier_wait(bar + 8u * (uint32_t)(i & 1), (uint32_t)((i >> 1) & 1));
                 cplx y[8];
                 static_for<0, 8>([&](auto p) {       // own row first: needs nothing from the peer
                     constexpr int v = brev(decltype(p)::value, 3);
@@ -389,7 +395,7 @@ blind_rotate_lat2_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride,
             Fft8::pass_a(t, x, tab->ta, twist_t, dir == 0, buf1);
             __syncthreads();
             // every thread of the CTA is past its key reads: refill the key column for the next iteration
-            if (dir == 1 && t == 0 && i + 1 < n_iter) fetch_key(i + 1);
+            if (dir == 1 && t == 0 && i + 2 < n_iter) fetch_key(i + 2);
             {
                 cplx z[8], send[4], recv[4];
                 Fft8::pass_b_first(t, buf1, z, send);

@@ -148,9 +148,14 @@ ks_splitk_kernel(const T *__restrict__ in, size_t in_stride, T *__restrict__ out
     for (int b = 0; b < KS_SK_MAX; b++) acc[b] = 0;
     const T *krow = ksk + (size_t)i0 * level * width + j;
     const int rows = ni * level;
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
 #pragma unroll 4
     for (int rr = 0; rr < rows; rr++, krow += width) {
-        const T kv = *krow;
+        // the key is read once: evict-first, so that streaming its 61 MB does not push the bootstrap key of the bootstrap that follows out of L2
+        T kv;
+        if constexpr (sizeof(T) == 8) asm volatile("ld.global.L2::cache_hint.u64 %0, [%1], %2;" : "=l"(kv) : "l"(krow), "l"(pol));
+        else asm volatile("ld.global.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(kv) : "l"(krow), "l"(pol));
         const uint2 pk = *reinterpret_cast<const uint2 *>(dig + rr * KS_SK_MAX);
 #pragma unroll
         for (int b = 0; b < KS_SK_MAX; b++) acc[b] += (T)(((b < 4 ? pk.x : pk.y) >> (8 * (b & 3))) & 0xFFu) * kv;
