@@ -242,19 +242,18 @@ blind_rotate_lat_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride, 
 
 // ---- one ciphertext on a CLUSTER of two CTAs (two SMs): CTA r owns polynomial row r -------------------------------------------------
 // Each CTA runs one 128-thread team (one warp per scheduler) with its own accumulator row, exchange buffers and the key COLUMN
-// j = r (two 16 KB blocks per iteration, by TMA).  The only data that crosses between the SMs is the transformed polynomial D_r: every
-// thread stores its eight values into the PEER's shared memory (st.shared::cluster through distributed shared memory), the cluster
-// barrier (arrive.release right after the stores, wait.acquire after the product with the CTA's own row) publishes them; the landing
-// buffer is double-buffered by iteration parity so one barrier per iteration suffices.  Half the shared-memory traffic and half the
-// FP64 work per SM; the price is the 16 KB that cross at ~20 B/clk and the barrier (~400 cycles).  Used for batches of at most
-// `lat_cluster_max` ciphertexts (two SMs each).
+// j = r (two 16 KB blocks per iteration, by TMA, two iterations ahead).  The only data that crosses between the SMs is the transformed
+// polynomial D_r: every thread sends its eight values into the PEER's shared memory with st.async (distributed shared memory), each store
+// signalling the peer's mbarrier; the landing buffer is double-buffered by iteration parity and there is no cluster barrier in the loop.
+// Half the shared-memory traffic and half the FP64 work per SM; the price is the 16 KB that cross at ~20 B/clk.  Used for batches of at
+// most `lat_cluster_max` ciphertexts (two SMs each).  History of the exchange: remote stores + cluster barrier 2.06 ms,
+// one staged 16 KB bulk copy 1.80 ms, st.async 1.71 ms of blind rotation.
 constexpr size_t L2_KEY_BYTES = LAT_KEY_BYTES / 2;                                   // column j = r: rows 0 and 1
 constexpr size_t L2_OFF_ACC = 2 * L2_KEY_BYTES;                                       // two key slots: the fetch runs two iterations ahead
 constexpr size_t L2_OFF_BUF1 = L2_OFF_ACC + (size_t)LAT_N * sizeof(uint64_t);
 constexpr size_t L2_OFF_BUF2 = L2_OFF_BUF1 + (size_t)Fft8::BUF1 * sizeof(cplx);
 constexpr size_t L2_OFF_DIN = L2_OFF_BUF2 + (size_t)Fft8::BUF2 * sizeof(cplx);       // [2][M] landing buffers for the peer's D
-constexpr size_t L2_OFF_DOUT = L2_OFF_DIN + 2 * (size_t)LAT_M * sizeof(cplx);      // [2][M] staging of this CTA's D for the bulk copy to the peer
-constexpr size_t L2_OFF_TAB = L2_OFF_DOUT + 2 * (size_t)LAT_M * sizeof(cplx);
+constexpr size_t L2_OFF_TAB = L2_OFF_DIN + 2 * (size_t)LAT_M * sizeof(cplx);
 constexpr size_t L2_OFF_MBAR = L2_OFF_TAB + sizeof(Fft8::Tables);
 constexpr size_t L2_OFF_AHAT = L2_OFF_MBAR + 32;   // three mbarriers: key slot 0, key slot 1, landing buffer
 size_t lat2_smem_bytes(int n) { return L2_OFF_AHAT + ((((size_t)(n + 1) * sizeof(uint16_t)) + 15) & ~(size_t)15); }
@@ -274,7 +273,6 @@ blind_rotate_lat2_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride,
     cplx *buf1 = reinterpret_cast<cplx *>(smem + L2_OFF_BUF1);
     cplx *buf2 = reinterpret_cast<cplx *>(smem + L2_OFF_BUF2);
     cplx *din = reinterpret_cast<cplx *>(smem + L2_OFF_DIN);
-    cplx *dout = reinterpret_cast<cplx *>(smem + L2_OFF_DOUT);
     Fft8::Tables *tab = reinterpret_cast<Fft8::Tables *>(smem + L2_OFF_TAB);
     uint16_t *ahat = reinterpret_cast<uint16_t *>(smem + L2_OFF_AHAT);
     const uint32_t bar = smem_addr_u32(smem + L2_OFF_MBAR);
@@ -360,21 +358,20 @@ blind_rotate_lat2_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride,
                 }
                 Fft8::pre_twist(x);
             } else {
-                // x holds D_r[t + 128 f2].  It goes to the peer as ONE bulk copy through distributed shared memory (the copy engine moves
-                // 16 KB far faster than 1024 sixteen-byte remote stores drain): stage it locally, make the generic-proxy writes visible
-                // to the async proxy, and let thread 0 send it; the copy signals the peer's mbarrier on arrival.  No cluster barrier in the
-                // loop: "the peer's D of iteration i+1 has landed" implies the peer has consumed what this CTA sent in iteration i, so the
-                // two-slot staging and landing buffers are safe to reuse two iterations later.
-                cplx *stage = dout + (i & 1) * M + t;
-                static_for<0, 8>([&](auto f2) { stage[TM * decltype(f2)::value] = x[decltype(f2)::value]; });
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                __syncthreads();
-                if (t == 0) {
-                    mbarrier_expect_tx(bar_din, (uint32_t)(M * sizeof(cplx)));        // arm this CTA's own landing barrier
-                    asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                                     din_peer + (uint32_t)((i & 1) * M * sizeof(cplx))),
-                                 "r"(smem_addr_u32(dout + (i & 1) * M)), "r"((uint32_t)(M * sizeof(cplx))), "r"(bar_din_peer)
-                                 : "memory");
+                // x holds D_r[t + 128 f2].  Every thread sends its eight values into the peer's landing buffer with st.async: a remote store
+                // through distributed shared memory that signals the PEER's mbarrier with the bytes it delivered.  The sender never waits
+                // (no fence, no staging, no barrier); the receiver waits for 16 KB on its own mbarrier.  No cluster barrier in the loop: "the
+                // peer's D of iteration i+1 has landed" implies the peer has consumed what this CTA sent in iteration i, so the two landing
+                // slots are safe to reuse two iterations later.
+                if (t == 0) mbarrier_expect_tx(bar_din, (uint32_t)(M * sizeof(cplx)));   // arm this CTA's own landing barrier
+                {
+                    const uint32_t dst = din_peer + (uint32_t)(((i & 1) * M + t) * sizeof(cplx));
+                    static_for<0, 8>([&](auto f2) {
+                        asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f64 [%0], {%1, %2}, [%3];" ::"r"(
+                                         dst + (uint32_t)(TM * decltype(f2)::value * sizeof(cplx))),
+                                     "d"(x[decltype(f2)::value].re), "d"(x[decltype(f2)::value].im), "r"(bar_din_peer)
+                                     : "memory");
+                    });
                 }
                 const cplx *key_own = key_own0 + (i & 1) * 2 * M, *key_oth = key_oth0 + (i & 1) * 2 * M;
                 mbarrier_wait(bar + 8u * (uint32_t)(i & 1), (uint32_t)((i >> 1) & 1));
