@@ -247,7 +247,8 @@ blind_rotate_lat_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride, 
 // signalling the peer's mbarrier; the landing buffer is double-buffered by iteration parity and there is no cluster barrier in the loop.
 // Half the shared-memory traffic and half the FP64 work per SM; the price is the 16 KB that cross at ~20 B/clk.  Used for batches of at
 // most `lat_cluster_max` ciphertexts (two SMs each).  History of the exchange: remote stores + cluster barrier 2.06 ms,
-// one staged 16 KB bulk copy 1.80 ms, st.async 1.71 ms of blind rotation.
+// one staged 16 KB bulk copy 1.80 ms, st.async 1.71 ms of blind rotation.  -DLAT2_EXP_NO_SEND / -DLAT2_EXP_NO_DIN_WAIT build a kernel without
+// the exchange (WRONG results; timing experiments only: 1.385 ms, i.e. the exchange costs ~855 cycles of the 4.5 k of an iteration).
 constexpr size_t L2_KEY_BYTES = LAT_KEY_BYTES / 2;                                   // column j = r: rows 0 and 1
 constexpr size_t L2_OFF_ACC = 2 * L2_KEY_BYTES;                                       // two key slots: the fetch runs two iterations ahead
 constexpr size_t L2_OFF_BUF1 = L2_OFF_ACC + (size_t)LAT_N * sizeof(uint64_t);
@@ -363,7 +364,10 @@ blind_rotate_lat2_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride,
                 // (no fence, no staging, no barrier); the receiver waits for 16 KB on its own mbarrier.  No cluster barrier in the loop: "the
                 // peer's D of iteration i+1 has landed" implies the peer has consumed what this CTA sent in iteration i, so the two landing
                 // slots are safe to reuse two iterations later.
+#ifndef LAT2_EXP_NO_SEND
                 if (t == 0) mbarrier_expect_tx(bar_din, (uint32_t)(M * sizeof(cplx)));   // arm this CTA's own landing barrier
+#endif
+#ifndef LAT2_EXP_NO_SEND
                 {
                     const uint32_t dst = din_peer + (uint32_t)(((i & 1) * M + t) * sizeof(cplx));
                     static_for<0, 8>([&](auto f2) {
@@ -373,6 +377,7 @@ blind_rotate_lat2_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride,
                                      : "memory");
                     });
                 }
+#endif
                 const cplx *key_own = key_own0 + (i & 1) * 2 * M, *key_oth = key_oth0 + (i & 1) * 2 * M;
                 mbarrier_wait(bar + 8u * (uint32_t)(i & 1), (uint32_t)((i >> 1) & 1));
                 cplx y[8];
@@ -380,7 +385,9 @@ blind_rotate_lat2_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride,
                     constexpr int v = brev(decltype(p)::value, 3);
                     y[decltype(p)::value] = cmul(key_own[TM * v], x[v]);
                 });
+#ifndef LAT2_EXP_NO_DIN_WAIT
                 mbarrier_wait(bar_din, (uint32_t)(i & 1));
+#endif
                 const cplx *d_oth = din + (i & 1) * M + t;
                 static_for<0, 8>([&](auto p) {
                     constexpr int v = brev(decltype(p)::value, 3);
