@@ -299,18 +299,19 @@ int b200tfhe_cbs_vertical_packing_batch_u64(b200tfhe_context *ctx, const b200tfh
  *   bivariate packing lhs*factor + rhs: shortint/server_key/bivariate_pbs.rs:167-182)  +  apply_lookup_table
  * (integer/server_key/radix_parallel/mul.rs:329-424, apps/trivium/src/trivium/trivium_shortint.rs:81-168).  A pool keeps
  * the ciphertexts of such a circuit in HBM; b200tfhe_wave_run executes one layer:
- *     pool[dst] <- LUT_lut( sum_k scale[k] * pool[src[k]] + (0,...,0,plaintext) )      for every op, lut < 0: no bootstrap
+ *     pool[dst] <- LUT_lut( sum_k scale[k] * pool[src[k]] + (0,...,0,plaintext) )      for every op (up to five terms), lut < 0: no bootstrap
  * Every op of a wave reads the pool as it was before the wave.  The first n_pbs ops are the bootstrapped ones (lut >= 0),
  * the rest are purely linear (lut < 0).  Asynchronous on the context's stream. */
 typedef struct b200tfhe_pool b200tfhe_pool;
 typedef struct {
     uint32_t dst;          /* pool slot written */
     uint32_t src[4];       /* pool slots read (ignored where scale == 0) */
-    uint32_t reserved;
+    uint32_t src4;         /* fifth term (a column sum of radix blocks takes (p - 1)/(m - 1) = 5 terms at MESSAGE_2_CARRY_2:
+                            * integer/server_key/radix_parallel/sum.rs); ignored where scale4 == 0 */
     int64_t scale[4];      /* cleartext multipliers, wrapping */
     uint64_t plaintext;    /* added to the body (already encoded, e.g. value * delta) */
     int32_t lut;           /* accumulator index into the pool's LUT table, or < 0 */
-    uint32_t reserved2;
+    int32_t scale4;        /* multiplier of the fifth term; 0 = no fifth term (these two words were reserved-zero before) */
 } b200tfhe_wave_op;
 /* big != 0: slots hold kN+1 scalars and a bootstrap is keyswitch -> PBS (shortint *_KS_PBS sets); big == 0: n+1 scalars,
  * PBS -> keyswitch (boolean DEFAULT_PARAMETERS) */

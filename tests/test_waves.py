@@ -33,7 +33,11 @@ def test_opgraph_levels_respect_hazards():
     assert g.ops[-1][2] == [(7, 3)]
     assert [len(w) for w in g.waves()] == [4, 2, 1]
     with pytest.raises(B200TfheError):
-        g.op(15, [(i, 1) for i in range(5)])                 # more than four terms
+        g.op(15, [(i, 1) for i in range(6)])                 # more than five terms
+    with pytest.raises(B200TfheError):
+        g.op(15, [(i, 2 ** 40) for i in range(5)])           # five terms: one multiplier has to fit 32 bits
+    g.op(15, [(0, 2 ** 40), (1, 1), (2, 2 ** 41), (3, -(2 ** 40)), (4, 2 ** 42)])
+    assert g.ops[-1][2][-1] == (1, 1)                        # ... and it is moved to the fifth place
     with pytest.raises(B200TfheError):
         g.op(64, [(0, 1)])                                   # slot out of range
     with pytest.raises(B200TfheError):
@@ -185,6 +189,35 @@ def test_trivium_bool_keystream_on_device(ctx):
 
 
 @pytest.mark.gpu
+def test_five_term_linear_wave_is_bit_exact(ctx):
+    """A wave operation takes up to five terms (the chunk of a radix column sum at MESSAGE_2_CARRY_2); the fifth one travels in the
+    two formerly reserved words of b200tfhe_wave_op.  Linear operations (no bootstrap) are wrapping u64 arithmetic: bit-exact."""
+    from tfhe_rs_odd_b200.waves import CiphertextPool, OpGraph
+    o = get_oracle("MESSAGE_2_CARRY_2")
+    p = params_of(o)
+    pool = CiphertextPool(ctx, p, capacity=16, big=True)
+    rng = np.random.default_rng(31)
+    cts = rng.integers(0, 2 ** 64, (8, pool.len), dtype=np.uint64)
+    pool.write(0, cts)
+    g = OpGraph(pool)
+    scales = [3, -5, 2 ** 40 + 1, -(2 ** 33), 7]
+    g.op(8, [(i, c) for i, c in enumerate(scales)], plaintext=0x1234)
+    g.op(9, [(i, 1) for i in range(3, 8)])
+    g.op(10, [(0, 1), (1, 1), (2, 1), (3, 1)])               # four terms: the fifth multiplier stays zero
+    g.run(None, None)
+    got = pool.read(8, 3)
+    want = np.zeros((3, pool.len), np.uint64)
+    with np.errstate(over="ignore"):
+        for i, c in enumerate(scales):
+            want[0] += np.uint64(c % 2 ** 64) * cts[i]
+        want[0, -1] += np.uint64(0x1234)
+        want[1] = cts[3:8].sum(axis=0, dtype=np.uint64)
+        want[2] = cts[0:4].sum(axis=0, dtype=np.uint64)
+    assert np.array_equal(got, want)
+    pool.close()
+
+
+@pytest.mark.gpu
 def test_radix_multiplication_on_device(ctx):
     """BASELINE configs[3] at full width: FheUint32 = 16 blocks at PARAM_MESSAGE_2_CARRY_2, schoolbook product in the
     structure of unchecked_mul_parallelized (radix_parallel/mul.rs:329-424): one wave of bivariate block products, then
@@ -212,6 +245,7 @@ def test_radix_multiplication_on_device(ctx):
     plan = g.compile()
     waves = plan.run(ksk, bsk)
     assert waves[0] == (M * (136 + 120), M * (136 + 120))    # the block-product wave: nb(nb+1)/2 lsb + nb(nb-1)/2 msb terms = 256
+    assert sum(w[1] for w in waves) == M * 547 and len(waves) == 17   # five-term column chunks (+ the final copy wave)
     got = o.decode(o.phase(pool.read(OUT, M * NB), "big")).reshape(M, NB) % 4
     total = sum(got[:, i].astype(np.int64) << (2 * i) for i in range(NB))
     assert np.array_equal(total, (x * y) % (1 << 32))

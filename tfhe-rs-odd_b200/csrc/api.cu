@@ -1428,6 +1428,7 @@ static int wave_check(b200tfhe_context *ctx, const b200tfhe_ksk *ksk, const b200
         const b200tfhe_wave_op &o = ops[i];
         REQUIRE(o.dst < pl->capacity, "wave_run: destination slot out of range");
         for (int k = 0; k < 4; k++) REQUIRE(o.scale[k] == 0 || o.src[k] < pl->capacity, "wave_run: source slot out of range");
+        REQUIRE(o.scale4 == 0 || o.src4 < pl->capacity, "wave_run: source slot out of range");
         if (i < n_pbs) REQUIRE(o.lut >= 0 && (uint32_t)o.lut < pl->n_luts, "wave_run: accumulator index out of range");
         else REQUIRE(o.lut < 0, "wave_run: bootstrapped operations must come first");
     }

@@ -142,11 +142,11 @@ int ks_tc_noalloc_launch(const KSLaunch &a, const KSTensorKey &tk, int device, c
 struct WaveOp {
     uint32_t dst;
     uint32_t src[4];
-    uint32_t reserved;
+    uint32_t src4;
     int64_t scale[4];
     uint64_t plaintext;
     int32_t lut;
-    uint32_t reserved2;
+    int32_t scale4;
 };
 int wave_gather_launch(const void *pool, size_t len, const WaveOp *d_ops, int n_ops, void *staging, uint32_t *d_lut_idx, int n_pbs,
                        int bits, cudaStream_t st);

@@ -21,8 +21,8 @@ __global__ void wave_gather_kernel(const T *__restrict__ pool, size_t len, const
     const WaveOp o = ops[op];
     if (op < n_pbs && blockIdx.y == 0 && threadIdx.x == 0) lut_idx[op] = (uint32_t)o.lut;
     const T *s0 = pool + (size_t)o.src[0] * len, *s1 = pool + (size_t)o.src[1] * len;
-    const T *s2 = pool + (size_t)o.src[2] * len, *s3 = pool + (size_t)o.src[3] * len;
-    const T c0 = (T)o.scale[0], c1 = (T)o.scale[1], c2 = (T)o.scale[2], c3 = (T)o.scale[3];
+    const T *s2 = pool + (size_t)o.src[2] * len, *s3 = pool + (size_t)o.src[3] * len, *s4 = pool + (size_t)o.src4 * len;
+    const T c0 = (T)o.scale[0], c1 = (T)o.scale[1], c2 = (T)o.scale[2], c3 = (T)o.scale[3], c4 = (T)(int64_t)o.scale4;
     T *dst = staging + (size_t)op * len;
     for (size_t e = (size_t)blockIdx.y * blockDim.x + threadIdx.x; e < len; e += (size_t)gridDim.y * blockDim.x) {
         T v = 0;                              // wrapping arithmetic on the torus; a zero scale skips the term
@@ -30,6 +30,7 @@ __global__ void wave_gather_kernel(const T *__restrict__ pool, size_t len, const
         if (c1) v += c1 * s1[e];
         if (c2) v += c2 * s2[e];
         if (c3) v += c3 * s3[e];
+        if (c4) v += c4 * s4[e];
         if (e == len - 1) v += (T)o.plaintext;
         dst[e] = v;
     }

@@ -24,8 +24,8 @@ from .core_crypto import B200TfheError, _dtype, _ptr
 
 class WaveOp(C.Structure):
     """Layout of b200tfhe_wave_op (include/b200tfhe.h)."""
-    _fields_ = [("dst", C.c_uint32), ("src", C.c_uint32 * 4), ("reserved", C.c_uint32), ("scale", C.c_int64 * 4),
-                ("plaintext", C.c_uint64), ("lut", C.c_int32), ("reserved2", C.c_uint32)]
+    _fields_ = [("dst", C.c_uint32), ("src", C.c_uint32 * 4), ("src4", C.c_uint32), ("scale", C.c_int64 * 4),
+                ("plaintext", C.c_uint64), ("lut", C.c_int32), ("scale4", C.c_int32)]
 
 
 class CiphertextPool:
@@ -75,7 +75,7 @@ class OpGraph:
     L, so:  RAW  L > wave of the last write of every source;  WAR  L >= wave of every earlier reader of dst;
     WAW  L > wave of the last write of dst."""
 
-    MAX_TERMS = 4
+    MAX_TERMS = 5          # the fifth term's multiplier is 32 bits wide (b200tfhe_wave_op.scale4)
 
     def __init__(self, pool):
         self.pool = pool
@@ -91,6 +91,10 @@ class OpGraph:
         terms = [(s, c) for s, c in merged.items() if c != 0]
         if len(terms) > self.MAX_TERMS:
             raise B200TfheError(f"an operation takes at most {self.MAX_TERMS} source terms, got {len(terms)}")
+        if len(terms) == self.MAX_TERMS:         # the narrow multiplier goes last
+            terms.sort(key=lambda sc: -(2 ** 31) <= sc[1] < 2 ** 31)
+            if not -(2 ** 31) <= terms[-1][1] < 2 ** 31:
+                raise B200TfheError("the fifth term of an operation takes a 32-bit multiplier")
         cap = self.pool.capacity
         if not (0 <= dst < cap) or any(not (0 <= s < cap) for s, _ in terms):
             raise B200TfheError("pool slot out of range")
@@ -138,8 +142,12 @@ class OpGraph:
             for (_, dst, terms, pt, lut) in wave:
                 arr[i].dst = dst
                 for k, (s, c) in enumerate(terms):
-                    arr[i].src[k] = s
-                    arr[i].scale[k] = c
+                    if k < 4:
+                        arr[i].src[k] = s
+                        arr[i].scale[k] = c
+                    else:
+                        arr[i].src4 = s
+                        arr[i].scale4 = c
                 arr[i].plaintext = pt
                 arr[i].lut = -1 if lut is None else lut
                 i += 1
