@@ -427,12 +427,13 @@ def test_partial_last_wave_runs_on_the_latency_kernel(ctx):
 
 @pytest.mark.gpu
 def test_pair_kernel_dispatch_and_ragged_last_cta(ctx):
-    """1_1 shape: batches of at least 740 ciphertexts go to blind_rotate_pair_kernel (six per CTA); a batch that does not fill the
-    last CTA must give, ciphertext by ciphertext, what the forced pair kernel and (within f64 summation order) the generic kernel give."""
+    """1_1 shape: batches of at least 740 ciphertexts go to blind_rotate_pair_kernel (six per CTA in full rounds of one CTA per SM, the
+    remainder spread over all SMs in CTAs of one or two pairs); every split must give, ciphertext by ciphertext, what the forced pair
+    kernel and (within f64 summation order) the generic kernel give."""
     import tfhe_rs_odd_b200 as t
     o = get_oracle("TOY_1_1")
     p, bsk, ksk = _keys(ctx, o)
-    B = 745                                   # 124 full CTAs + one with a single live ciphertext
+    B = 895                                   # one full round (148 CTAs x 6) + a tail of 7 in CTAs of one pair, the last one half empty
     msgs = np.arange(B) % o.pmod
     cts = o.encrypt(o.encode(msgs), "small", seed=0x7A12)
     lut = o.lut(lambda x: (x + 1) % o.pmod)
@@ -442,11 +443,13 @@ def test_pair_kernel_dispatch_and_ragged_last_cta(ctx):
         ctx.set_option("br_kernel", 7)
         pair = t.programmable_bootstrap_lwe_ciphertext(cts, lut, bsk)
         small = t.programmable_bootstrap_lwe_ciphertext(cts[:5], lut, bsk)       # fewer than one CTA
+        tails = {b: t.programmable_bootstrap_lwe_ciphertext(cts[:b], lut, bsk) for b in (301, 745)}   # tail CTAs of two and three pairs
         ctx.set_option("br_kernel", 1)
         gen = t.programmable_bootstrap_lwe_ciphertext(cts, lut, bsk)
     finally:
         ctx.set_option("br_kernel", 0)
     assert np.array_equal(auto, pair) and np.array_equal(small, pair[:5])
+    assert all(np.array_equal(v, pair[:b]) for b, v in tails.items())
     d = np.abs((o.phase(pair, "big") - o.phase(gen, "big")).astype(np.int64).astype(np.float64)) / 2.0 ** 64
     assert d.max() < phase_bound(o)
     assert np.array_equal(o.decode(o.phase(gen, "big")), o.decode(o.phase(pair, "big")))

@@ -42,7 +42,7 @@ __global__ void __launch_bounds__(PR_THREADS, 1)
 blind_rotate_pair_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const T *__restrict__ luts,
                          const uint32_t *__restrict__ lut_idx, const cplx *__restrict__ bsk, T *__restrict__ out,
                          size_t out_stride, int n, int batch, int mode, const cplx *__restrict__ tw_fwd_,
-                         const cplx *__restrict__ tw_inv_) {
+                         const cplx *__restrict__ tw_inv_, int full_ctas, int tail_cts) {
 #if defined(__CUDA_ARCH__)
     typedef PairConfig<T, BL> CFG;
     typedef typename CFG::C C;
@@ -52,9 +52,13 @@ blind_rotate_pair_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const 
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & (R - 1), half = (threadIdx.x >> 4) & 1;
     const int r = warp & 3, pair = warp >> 2, ct_local = 2 * pair + half;
-    int ct = blockIdx.x * PR_CTS + ct_local;
-    const bool live = ct < batch;
-    if (!live) ct = batch - 1;      // ghost ciphertext: same work, no output (keeps barriers uniform)
+    // CTAs below full_ctas carry six ciphertexts; the rest -- the partial last round -- carry tail_cts (2 or 4) each, so that the
+    // remainder is spread over all SMs: a CTA with one pair of ciphertexts takes well under half the time of a full one
+    const int b = (int)blockIdx.x, cts_here = b < full_ctas ? PR_CTS : tail_cts;
+    int ct = (b < full_ctas ? b * PR_CTS : full_ctas * PR_CTS + (b - full_ctas) * tail_cts) + ct_local;
+    const bool pair_used = 2 * pair < cts_here && ct - half < batch;      // the pair's first ciphertext exists
+    const bool live = ct_local < cts_here && ct < batch;
+    if (!live) ct = batch - 1;      // ghost ciphertext (odd batch): same work, no output (keeps the pair's barriers uniform)
 
     const size_t ahat_bytes = (((size_t)(n + 1) * sizeof(uint16_t)) + 15) & ~(size_t)15;
     cplx *fbuf_ct = reinterpret_cast<cplx *>(smem_raw) + (size_t)ct_local * K1 * REGION;
@@ -74,6 +78,7 @@ blind_rotate_pair_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const 
     const T *lwe = lwe_in + (size_t)ct * lwe_stride;
     for (int i = r * R + lane; i <= n; i += K1 * R) ahat[i] = (uint16_t)(modswitch<T>(lwe[i], C::LOGN) & (2 * N - 1));
     __syncthreads();
+    if (!pair_used) return;         // an unused pair slot of a tail CTA: its four warps leave (the pairs only meet at their own barriers)
     {
         const T *lut = luts + (size_t)(lut_idx ? lut_idx[ct] : 0) * K1 * N + (size_t)r * N;
         const int a0 = (2 * N - (int)ahat[n]) & (2 * N - 1);
@@ -172,9 +177,17 @@ int br_pair_launch(const Params &p, const BRLaunch &a, cudaStream_t st) {
     auto kern = blind_rotate_pair_kernel<uint64_t, 18>;
     const size_t smem = CFG::smem_bytes(a.n);
     if (cudaError_t e = ensure_dynamic_smem((const void *)kern, smem)) return (int)e;
-    const int grid = (a.batch + PR_CTS - 1) / PR_CTS;
+    // full rounds of six ciphertexts per SM, then the remainder in CTAs of one or two pairs over all SMs (a partial round of full CTAs
+    // costs a whole round: 8 % of a Trivium wave of 8192)
+    int sms = 148, dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int full_ctas = a.batch / (PR_CTS * sms) * sms, rem = a.batch - full_ctas * PR_CTS;
+    int tail_cts = 2 * ((rem + 2 * sms - 1) / (2 * sms));
+    if (tail_cts < 2) tail_cts = 2;
+    const int grid = full_ctas + (rem + tail_cts - 1) / tail_cts;
     kern<<<grid, PR_THREADS, smem, st>>>((const uint64_t *)a.lwe_in, a.lwe_stride, (const uint64_t *)a.luts, a.lut_idx, (const cplx *)a.bsk,
-                                         (uint64_t *)a.out, a.out_stride, a.n, a.batch, a.mode, (const cplx *)a.tw_fwd, (const cplx *)a.tw_inv);
+                                         (uint64_t *)a.out, a.out_stride, a.n, a.batch, a.mode, (const cplx *)a.tw_fwd, (const cplx *)a.tw_inv,
+                                         full_ctas, tail_cts);
     return (int)cudaGetLastError();
 }
 
