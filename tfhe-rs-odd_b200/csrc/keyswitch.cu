@@ -112,11 +112,10 @@ int ks_colsum_launch(const void *ksk, void *colsum, int n_in, int n_out, int lev
 
 // ---- a handful of ciphertexts (the single-bootstrap latency path): split the key ROWS over the whole GPU -------------------------
 // ks_kernel gives a batch of <= 32 ciphertexts to six CTAs (one per 128 output columns), each walking all n_in*l key rows: 0.12 ms for ONE
-// ciphertext at PARAM_MESSAGE_2_CARRY_2, 6 % of a single KS+PBS.  Here a CTA owns KS_SK_IC input coefficients x 128 columns for all (<= 8)
+// ciphertext at PARAM_MESSAGE_2_CARRY_2, 6 % of a single KS+PBS.  Here a CTA owns a few (KS_SK_IC) input coefficients x 128 columns for all (<= 8)
 // ciphertexts and adds its partial sums into the output with atomic adds: wrapping addition is associative and commutative, so the
 // result is bit-identical to the serial loop whatever the order.  The output is pre-set to body + B/2 * colsum by ks_splitk_init_kernel.
 constexpr int KS_SK_MAX = 8;       // ciphertexts
-constexpr int KS_SK_IC = 16;       // input coefficients per CTA
 
 template <typename T>
 __global__ void ks_splitk_init_kernel(const T *__restrict__ in, size_t in_stride, T *__restrict__ out, size_t out_stride,
@@ -128,11 +127,11 @@ __global__ void ks_splitk_init_kernel(const T *__restrict__ in, size_t in_stride
     out[(size_t)b * out_stride + j] = v;
 }
 
-template <typename T>
+template <typename T, int KS_SK_IC, int UNR>
 __global__ void __launch_bounds__(128)
 ks_splitk_kernel(const T *__restrict__ in, size_t in_stride, T *__restrict__ out, size_t out_stride, const T *__restrict__ ksk,
                  int n_in, int width, int level, int base_log, int batch) {
-    __shared__ unsigned char dig[KS_SK_IC * 8 * KS_SK_MAX];     // [(ii*level + t)][b], level <= 8
+    __shared__ __align__(8) unsigned char dig[KS_SK_IC * 8 * KS_SK_MAX];     // [(ii*level + t)][b], level <= 8
     const int tid = threadIdx.x, i0 = blockIdx.x * KS_SK_IC, j = blockIdx.y * 128 + tid;
     const uint32_t half_b = 1u << (base_log - 1);
     const int ni = min(KS_SK_IC, n_in - i0);
@@ -150,7 +149,7 @@ ks_splitk_kernel(const T *__restrict__ in, size_t in_stride, T *__restrict__ out
     const int rows = ni * level;
     uint64_t pol;
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
-#pragma unroll 4
+#pragma unroll UNR
     for (int rr = 0; rr < rows; rr++, krow += width) {
         // the key is read once: evict-first, so that streaming its 61 MB does not push the bootstrap key of the bootstrap that follows out of L2
         T kv;
@@ -173,8 +172,12 @@ template <typename T> static int ks_splitk_launch(const KSLaunch &a, cudaStream_
     const int width = a.n_out + 1, body = a.body_col < 0 ? a.n_out : a.body_col;
     ks_splitk_init_kernel<T><<<dim3((width + 127) / 128, a.batch), 128, 0, st>>>((const T *)a.in, a.in_stride, (T *)a.out, a.out_stride, (const T *)a.colsum,
                                                                                a.n_in, width, a.base_log, a.batch, body);
-    ks_splitk_kernel<T><<<dim3((a.n_in + KS_SK_IC - 1) / KS_SK_IC, (width + 127) / 128), 128, 0, st>>>((const T *)a.in, a.in_stride, (T *)a.out, a.out_stride,
-                                                                                                   (const T *)a.ksk, a.n_in, width, a.level, a.base_log, a.batch);
+    // 4 input coefficients (20 key rows at l_ks = 5) per CTA, every load of a thread in flight at once: 3072 CTAs at PARAM_MESSAGE_2_CARRY_2.
+    // Measured for one ciphertext (keyswitch alone / KS+PBS, us): 16 coefficients, unroll 4: 45.6 / 1756; 8, 8: 40.4 / 1750; 4, 20: 35.0 / 1738;
+    // 3, 15: 33.2 / 1738; 2, 10: 41.1 / 1749; 1, 8: 59.6 / 1788.
+    constexpr int IC = 4, UNR = 20;
+    ks_splitk_kernel<T, IC, UNR><<<dim3((a.n_in + IC - 1) / IC, (width + 127) / 128), 128, 0, st>>>((const T *)a.in, a.in_stride, (T *)a.out, a.out_stride,
+                                                                                                (const T *)a.ksk, a.n_in, width, a.level, a.base_log, a.batch);
     return (int)cudaGetLastError();
 }
 
