@@ -363,7 +363,9 @@ blind_rotate_lat2_kernel(const uint64_t *__restrict__ lwe_in, size_t lwe_stride,
                 // through distributed shared memory that signals the PEER's mbarrier with the bytes it delivered.  The sender never waits
                 // (no fence, no staging, no barrier); the receiver waits for 16 KB on its own mbarrier.  No cluster barrier in the loop: "the
                 // peer's D of iteration i+1 has landed" implies the peer has consumed what this CTA sent in iteration i, so the two landing
-                // slots are safe to reuse two iterations later.
+                // slots are safe to reuse two iterations later.  The same chain keeps the phases of the landing barrier apart: the peer issues
+                // its stores of iteration i+1 only after it has consumed this CTA's D of iteration i, a whole iteration (> 2 us) after its own
+                // stores of iteration i left -- they cannot be counted into the wrong phase.
 #ifndef LAT2_EXP_NO_SEND
                 if (t == 0) mbarrier_expect_tx(bar_din, (uint32_t)(M * sizeof(cplx)));   // arm this CTA's own landing barrier
 #endif
