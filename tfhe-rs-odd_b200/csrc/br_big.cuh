@@ -200,9 +200,16 @@ template <typename T, int K, int L, int BASE_LOG> struct BigCore {
 
     // ---- inverse: (x[pp] = F[brev(pp)]) invA | team sync | invB_load | team sync | invB_store | CTA sync | invC
     HD static void invA(int tid, cplx (&x)[P], cplx *S1, const BigTables *tb) {
-        const int team = tid >> 4, lane = tid & 15;
+        invA_compute(tid, x, tb);
+        invA_store(tid, x, S1);
+    }
+    // the two halves of invA: registers only, and the exchange store
+    HD static void invA_compute(int tid, cplx (&x)[P], const BigTables *tb) {
         fft_dit<P, +1>(x);
-        team_twiddle<+1>(lane, x, tb->pi);
+        team_twiddle<+1>(tid & 15, x, tb->pi);
+    }
+    HD static void invA_store(int tid, const cplx (&x)[P], cplx *S1) {
+        const int team = tid >> 4, lane = tid & 15;
         static_for<0, P>([&](auto l) { S1[team * TH + swz(decltype(l)::value, lane)] = x[decltype(l)::value]; });
     }
     HD static void invB_load(int tid, cplx (&x)[P], const cplx *S1) {
