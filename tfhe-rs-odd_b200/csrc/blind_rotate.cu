@@ -117,8 +117,9 @@ blind_rotate_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const T *__
         if constexpr (R > C::CH) C::template mac_prefetch_part<1>(lane, r, ggsw_i, F);
         ct_barrier();
         C::mac_finish(lane, r, ggsw_i, fbuf_ct, F);
+        TeamFFT<R>::inv_pass1_compute(lane, F, twi);   // butterflies and middle twiddle BEFORE the barrier: only the store needs the region free
         ct_barrier();
-        C::inv_pass1(lane, F, fbuf_r, twi);
+        TeamFFT<R>::pass1_store(lane, F, fbuf_r);
         __syncwarp();
         C::inv_pass2_accumulate(lane, fbuf_r, acc_r);
         __syncwarp();

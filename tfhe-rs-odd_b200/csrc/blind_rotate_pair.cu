@@ -136,8 +136,9 @@ blind_rotate_pair_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const 
         apply_row(r2);
         load_row(r3);
         apply_row(r3);
+        FFT::inv_pass1_compute(lane, F, twi);       // butterflies and middle twiddle BEFORE the barrier: only the store needs the region free
         named_bar_sync(bar_pair, 128);              // every team has read every D: the regions are free for the inverse transform
-        FFT::inv_pass1(lane, F, fbuf_r, twi);
+        FFT::pass1_store(lane, F, fbuf_r);
         __syncwarp();
         FFT::inv_pass2(lane, x, fbuf_r);
         static_for<0, R>([&](auto m) {

@@ -432,10 +432,11 @@ blind_rotate_x16b_kernel(const T *__restrict__ lwe_in, size_t lwe_stride, const 
                 }
             }
         });
+        FFT::inv_pass1_compute(l16, F, twi);     // butterflies and middle twiddle BEFORE the barrier: only the store needs the region free
         tmem_fence_before();
         named_bar_sync(bar_q, K1 * 32);          // every team is done with the D slots and regions of this iteration
         tmem_fence_after();
-        C::inv_pass1(l16, F, region, twi);
+        FFT::pass1_store(l16, F, region);
         __syncwarp();
         C::inv_pass2_accumulate(l16, region, acc_r);
         __syncwarp();
